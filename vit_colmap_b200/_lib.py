@@ -1,0 +1,75 @@
+"""ctypes binding of the C-ABI library (include/vc_b200.h).
+
+The library is the product: if it is missing, or no sm_100 device is present, calls fail loudly.
+There is no CPU or PyTorch fallback anywhere in this package.
+"""
+from __future__ import annotations
+
+import ctypes
+from ctypes import (POINTER, c_char_p, c_float, c_int, c_int32, c_int64, c_size_t, c_uint8, c_uint32,
+                    c_void_p)
+from pathlib import Path
+
+PKG = Path(__file__).resolve().parent
+LIB_PATH = PKG / "_vc_b200.so"
+
+
+class VcError(RuntimeError):
+    pass
+
+
+class MatchOptions(ctypes.Structure):
+    """vc_match_options (include/vc_b200.h)."""
+    _fields_ = [("max_ratio", c_float), ("max_distance", c_float), ("cross_check", c_int32),
+                ("inv_norm", c_float)]
+
+
+# name -> (restype, argtypes); kept in one table so tests can check every exported symbol
+SIGNATURES = {
+    "vc_last_error": (c_char_p, []),
+    "vc_version": (c_char_p, []),
+    "vc_launch_count": (c_int64, [c_int]),
+    "vc_create": (c_int, [c_int, POINTER(c_void_p)]),
+    "vc_destroy": (c_int, [c_void_p]),
+    "vc_match_workspace_bytes": (c_size_t, [c_int, c_int]),
+    "vc_match_pairs": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_void_p, c_int,
+                               POINTER(MatchOptions), c_void_p, c_void_p, c_void_p, c_size_t,
+                               c_void_p]),
+    "vc_match_pairs_top2": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_void_p, c_int,
+                                    POINTER(MatchOptions), c_void_p, c_void_p, c_void_p, c_void_p,
+                                    c_size_t, c_void_p]),
+    "vc_debug_scores": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_int,
+                                c_void_p, c_int, c_void_p]),
+    "vc_match_pairs_host": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int,
+                                    c_void_p, c_int, POINTER(MatchOptions), c_void_p, c_void_p]),
+    "vc_convert_u8_to_bf16": (c_int, [c_void_p, c_void_p, c_size_t, c_void_p]),
+    "vc_convert_f32_to_bf16": (c_int, [c_void_p, c_void_p, c_size_t, c_void_p]),
+}
+
+_lib = None
+
+
+def load() -> ctypes.CDLL:
+    """Load _vc_b200.so (built by vit_colmap_b200.build).  Raises if it is absent."""
+    global _lib
+    if _lib is None:
+        if not LIB_PATH.exists():
+            raise VcError(f"{LIB_PATH} not found: run `python -m vit_colmap_b200.build` "
+                          "(there is no fallback implementation)")
+        lib = ctypes.CDLL(str(LIB_PATH))
+        for name, (res, args) in SIGNATURES.items():
+            fn = getattr(lib, name)
+            fn.restype = res
+            fn.argtypes = args
+        _lib = lib
+    return _lib
+
+
+def check(rc: int) -> None:
+    if rc != 0:
+        msg = load().vc_last_error()
+        raise VcError(f"vc_b200 error {rc}: {msg.decode() if msg else '?'}")
+
+
+def launch_count(reset: bool = False) -> int:
+    return int(load().vc_launch_count(1 if reset else 0))

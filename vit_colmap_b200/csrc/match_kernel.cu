@@ -1,0 +1,371 @@
+// Fused exhaustive descriptor matcher for sm_100a (B200).
+//
+// One persistent CTA per SM.  A work item is (pair, direction, 128-row block): the rows of the
+// "M" image of the pair sit on the 128 TMEM lanes, the CTA sweeps the "N" image in 256-column
+// tiles.  Per tile: TMA (128B swizzle) stages bf16 operands in shared memory, one thread issues
+// tcgen05.mma (M=128, N=256, K=16) into a double-buffered fp32 TMEM accumulator, four epilogue
+// warps pull the tile with tcgen05.ld and fold it into a per-row running (best, second, index).
+// The score matrix never leaves TMEM.  Direction 1 swaps the roles of the two images and yields
+// the column results, so the cross check (COLMAP/feature/sift.cc:803-813) needs no transpose.
+//
+// Semantics restated from the reference (not copied):
+//   COLMAP/feature/sift.cc:733-787  one-way best/second, init 0, strict '>', acos tests
+//   COLMAP/feature/sift.cc:789-825  cross check, ascending idx1 emit order
+//   SIFTGPU/ProgramCU.cu:1411-1495,1696-1797  (the reference GPU kernels this replaces; they
+//   write the int32 dot matrix to HBM and re-read it twice)
+#include "match_kernel.cuh"
+
+#include <math.h>
+
+#include "vc_ptx.cuh"
+
+namespace vc {
+
+namespace {
+
+constexpr int BM = 128;            // rows per work item (TMEM lanes)
+constexpr int BN = 256;            // columns per tile (UMMA N)
+constexpr int BK = 64;             // bf16 per k-block = one 128-byte swizzle row
+constexpr int kStages = 4;         // smem ring depth
+constexpr int kABytes = BM * BK * 2;
+constexpr int kBBytes = BN * BK * 2;
+constexpr int kStageBytes = kABytes + kBBytes;
+constexpr int kThreads = 256;      // warp0 TMA, warp1 MMA, warp2 TMEM alloc, warps4-7 epilogue
+constexpr int kTmemCols = 512;     // 2 accumulator stages x 256 fp32 columns
+constexpr int kSmemBytes = kStages * kStageBytes + 1024 /*align slack*/ + 256 /*barriers*/;
+
+struct Item {
+  int pair, dir, rb, img_m, img_n, n_m, n_n;
+  bool valid;
+};
+
+__device__ __forceinline__ Item decode_item(const MatchParams& p, int item) {
+  Item it;
+  const int per_pair = 2 * p.rb_per_img;
+  it.pair = item / per_pair;
+  const int r = item - it.pair * per_pair;
+  it.dir = r / p.rb_per_img;
+  it.rb = r - it.dir * p.rb_per_img;
+  const int i0 = __ldg(p.pairs + 2 * it.pair), i1 = __ldg(p.pairs + 2 * it.pair + 1);
+  it.img_m = it.dir ? i1 : i0;
+  it.img_n = it.dir ? i0 : i1;
+  it.n_m = min(__ldg(p.counts + it.img_m), p.kmax);
+  it.n_n = min(__ldg(p.counts + it.img_n), p.kmax);
+  it.valid = it.rb * BM < it.n_m;
+  return it;
+}
+
+// COLMAP/feature/sift.cc:759-783.  acos is evaluated in double and rounded once so the float
+// result agrees with a correctly rounded host acosf.
+__device__ __forceinline__ int accept_top2(float best, float second, int idx, float inv_norm,
+                                           float max_ratio, float max_distance) {
+  if (idx < 0) return -1;
+  const float t1 = (float)acos((double)fminf(inv_norm * best, 1.0f));
+  if (t1 > max_distance) return -1;
+  const float t2 = (float)acos((double)fminf(inv_norm * second, 1.0f));
+  if (t1 >= max_ratio * t2) return -1;
+  return idx;
+}
+
+}  // namespace
+
+template <bool kDebug>
+__global__ void __launch_bounds__(kThreads, 1)
+match_top2_kernel(const __grid_constant__ CUtensorMap tmap, const MatchParams p) {
+  extern __shared__ uint8_t smem_raw[];
+  const uint32_t raw_addr = smem_u32(smem_raw);
+  const uint32_t base = (raw_addr + 1023u) & ~1023u;  // 128B swizzle atoms need 1024B alignment
+  uint8_t* smem = smem_raw + (base - raw_addr);
+  const uint32_t sA = base;
+  const uint32_t sB = base + kStages * kABytes;
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + kStages * kStageBytes);
+  const uint32_t bar0 = smem_u32(bars);
+  auto full_bar = [&](int s) { return bar0 + 8u * s; };
+  auto empty_bar = [&](int s) { return bar0 + 8u * (kStages + s); };
+  auto tfull_bar = [&](int s) { return bar0 + 8u * (2 * kStages + s); };
+  auto tempty_bar = [&](int s) { return bar0 + 8u * (2 * kStages + 2 + s); };
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * kStages + 4);
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+  const int nkb = (p.d + BK - 1) / BK;
+
+  if (warp == 0 && lane == 0) tma_prefetch_desc(&tmap);
+  if (warp == 1 && lane == 0) {
+    for (int s = 0; s < kStages; ++s) {
+      mbar_init(full_bar(s), 1);
+      mbar_init(empty_bar(s), 1);
+    }
+    for (int s = 0; s < 2; ++s) {
+      mbar_init(tfull_bar(s), 1);
+      mbar_init(tempty_bar(s), 128);
+    }
+    fence_mbar_init();
+  }
+  if (warp == 2) {
+    tmem_alloc(smem_u32(tmem_slot), kTmemCols);
+    tmem_relinquish();
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp == 0 && lane == 0) {
+    // ------------------------------------------------------------ TMA producer
+    uint32_t stage = 0, phase = 0;
+    for (int item = blockIdx.x; item < p.n_items; item += gridDim.x) {
+      const Item it = decode_item(p, item);
+      if (!it.valid) continue;
+      const int ntiles = (it.n_n + BN - 1) / BN;
+      for (int ct = 0; ct < ntiles; ++ct) {
+        for (int kb = 0; kb < nkb; ++kb) {
+          mbar_wait(empty_bar(stage), phase ^ 1);
+          mbar_arrive_expect_tx(full_bar(stage), kStageBytes);
+          tma_load_3d(sA + stage * kABytes, &tmap, full_bar(stage), kb * BK, it.rb * BM, it.img_m);
+          tma_load_3d(sB + stage * kBBytes, &tmap, full_bar(stage), kb * BK, ct * BN, it.img_n);
+          tma_load_3d(sB + stage * kBBytes + kABytes, &tmap, full_bar(stage), kb * BK,
+                      ct * BN + 128, it.img_n);
+          if (++stage == kStages) {
+            stage = 0;
+            phase ^= 1;
+          }
+        }
+      }
+    }
+  } else if (warp == 1 && lane == 0) {
+    // ------------------------------------------------------------ MMA issuer
+    constexpr uint32_t idesc = umma_idesc_bf16(BM, BN);
+    uint32_t stage = 0, phase = 0, tile = 0;
+    for (int item = blockIdx.x; item < p.n_items; item += gridDim.x) {
+      const Item it = decode_item(p, item);
+      if (!it.valid) continue;
+      const int ntiles = (it.n_n + BN - 1) / BN;
+      for (int ct = 0; ct < ntiles; ++ct, ++tile) {
+        const uint32_t as = tile & 1, aph = (tile >> 1) & 1;
+        mbar_wait(tempty_bar(as), aph ^ 1);
+        tc_fence_after();
+        const uint32_t d_tmem = tmem_base + as * BN;
+        for (int kb = 0; kb < nkb; ++kb) {
+          mbar_wait(full_bar(stage), phase);
+          tc_fence_after();
+          const uint64_t da = umma_desc_k_sw128(sA + stage * kABytes);
+          const uint64_t db = umma_desc_k_sw128(sB + stage * kBBytes);
+#pragma unroll
+          for (int k = 0; k < BK / 16; ++k) {
+            // +32 bytes per K=16 step inside the 128-byte swizzle row (address field is >>4)
+            tc_mma_bf16(d_tmem, da + 2 * k, db + 2 * k, idesc, (kb | k) != 0);
+          }
+          tc_commit(empty_bar(stage));  // frees the smem slot when these MMAs retire
+          if (kb == nkb - 1) tc_commit(tfull_bar(as));
+          if (++stage == kStages) {
+            stage = 0;
+            phase ^= 1;
+          }
+        }
+      }
+    }
+  } else if (warp >= 4) {
+    // ------------------------------------------------------------ epilogue: running top-2
+    const int q = warp - 4;  // TMEM lane quarter this warp may access (warp % 4)
+    uint32_t tile = 0;
+    for (int item = blockIdx.x; item < p.n_items; item += gridDim.x) {
+      const Item it = decode_item(p, item);
+      if (!it.valid) continue;
+      const int ntiles = (it.n_n + BN - 1) / BN;
+      const int row = it.rb * BM + q * 32 + lane;
+      float best = 0.f, second = 0.f;  // sift.cc:742-743
+      int bidx = -1;                   // sift.cc:741
+      for (int ct = 0; ct < ntiles; ++ct, ++tile) {
+        const uint32_t as = tile & 1, aph = (tile >> 1) & 1;
+        mbar_wait(tfull_bar(as), aph);
+        tc_fence_after();
+        const uint32_t t_addr = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + as * BN;
+#pragma unroll 1
+        for (int c = 0; c < BN / 32; ++c) {
+          const int colbase = ct * BN + c * 32;
+          if (colbase >= it.n_n) break;  // warp-uniform
+          uint32_t vr[32];
+          tmem_ld_32x32(t_addr + c * 32, vr);
+          tmem_wait_ld();
+          float v[32];
+#pragma unroll
+          for (int e = 0; e < 32; ++e) v[e] = __uint_as_float(vr[e]);
+          if (colbase + 32 > it.n_n) {  // ragged last chunk: padding rows never match
+#pragma unroll
+            for (int e = 0; e < 32; ++e)
+              if (colbase + e >= it.n_n) v[e] = 0.f;
+          }
+          if (kDebug) {
+            if (p.dbg_scores != nullptr && it.pair == 0 && it.dir == 0 && row < it.n_m) {
+#pragma unroll
+              for (int e = 0; e < 32; ++e)
+                if (colbase + e < it.n_n)
+                  p.dbg_scores[(size_t)row * p.dbg_ld + colbase + e] = v[e];
+            }
+          }
+#pragma unroll
+          for (int g = 0; g < 4; ++g) {
+            float m = v[8 * g];
+#pragma unroll
+            for (int e = 1; e < 8; ++e) m = fmaxf(m, v[8 * g + e]);
+            // Nothing in this group can change (best, second, idx) unless it beats `second`.
+            if (__any_sync(0xffffffffu, m > second)) {
+#pragma unroll
+              for (int e = 0; e < 8; ++e) {
+                const float s = v[8 * g + e];
+                if (s > best) {  // strict '>' keeps the lowest index on ties (sift.cc:747-751)
+                  second = best;
+                  best = s;
+                  bidx = colbase + 8 * g + e;
+                } else if (s > second) {
+                  second = s;
+                }
+              }
+            }
+          }
+        }
+        tc_fence_before();
+        mbar_arrive(tempty_bar(as));
+      }
+      if (row < it.n_m) {
+        const size_t o = ((size_t)it.pair * 2 + it.dir) * p.kmax + row;
+        p.m_out[o] = accept_top2(best, second, bidx, p.inv_norm, p.max_ratio, p.max_distance);
+        if (p.top_best != nullptr) {
+          p.top_best[o] = best;
+          p.top_second[o] = second;
+          p.top_idx[o] = bidx;
+        }
+      }
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 2) tmem_dealloc(tmem_base, kTmemCols);
+}
+
+// ---------------------------------------------------------------------------------------------
+// Cross check + ordered emit (COLMAP/feature/sift.cc:803-823; replaces the host loop
+// SIFTGPU/SiftMatchCU.cpp:183-191).  One CTA per pair; a block-wide exclusive scan keeps the
+// output sorted by idx1.
+__global__ void __launch_bounds__(1024, 1) emit_matches_kernel(const MatchParams p, uint32_t* matches,
+                                                               int32_t* n_matches) {
+  __shared__ int warp_tot[32];
+  __shared__ int running;
+  const int pair = blockIdx.x;
+  const int i0 = p.pairs[2 * pair], i1 = p.pairs[2 * pair + 1];
+  const int n1 = min(p.counts[i0], p.kmax), n2 = min(p.counts[i1], p.kmax);
+  const int32_t* m12 = p.m_out + ((size_t)pair * 2) * p.kmax;
+  const int32_t* m21 = m12 + p.kmax;
+  uint32_t* out = matches + (size_t)pair * p.kmax * 2;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  if (threadIdx.x == 0) running = 0;
+  __syncthreads();
+  if (n2 > 0) {
+    for (int base = 0; base < n1; base += blockDim.x) {
+      const int i = base + threadIdx.x;
+      int j = -1;
+      if (i < n1) {
+        j = m12[i];
+        if (j >= 0 && p.cross_check && m21[j] != i) j = -1;
+      }
+      const unsigned bal = __ballot_sync(0xffffffffu, j >= 0);
+      if (lane == 0) warp_tot[warp] = __popc(bal);
+      __syncthreads();
+      int prefix = running;
+      for (int w = 0; w < warp; ++w) prefix += warp_tot[w];
+      if (j >= 0) {
+        const int pos = prefix + __popc(bal & ((1u << lane) - 1u));
+        out[2 * pos] = (uint32_t)i;
+        out[2 * pos + 1] = (uint32_t)j;
+      }
+      __syncthreads();
+      if (threadIdx.x == 0) {
+        int tot = 0;
+        for (int w = 0; w < (int)(blockDim.x >> 5); ++w) tot += warp_tot[w];
+        running += tot;
+      }
+      __syncthreads();
+    }
+  }
+  if (threadIdx.x == 0) n_matches[pair] = running;
+}
+
+__global__ void u8_to_bf16_kernel(const uint8_t* __restrict__ src, __nv_bfloat16* __restrict__ dst,
+                                  size_t n) {
+  // 16 elements per thread: one 16-byte load, two 16-byte stores
+  const size_t i = ((size_t)blockIdx.x * blockDim.x + threadIdx.x) * 16;
+  if (i + 16 <= n) {
+    const uint4 in = *reinterpret_cast<const uint4*>(src + i);
+    const uint32_t w[4] = {in.x, in.y, in.z, in.w};
+    __align__(16) __nv_bfloat16 o[16];
+#pragma unroll
+    for (int k = 0; k < 16; ++k) o[k] = __float2bfloat16_rn((float)((w[k >> 2] >> (8 * (k & 3))) & 0xFF));
+    *reinterpret_cast<uint4*>(dst + i) = *reinterpret_cast<const uint4*>(o);
+    *reinterpret_cast<uint4*>(dst + i + 8) = *reinterpret_cast<const uint4*>(o + 8);
+  } else {
+    for (size_t k = i; k < n; ++k) dst[k] = __float2bfloat16_rn((float)src[k]);
+  }
+}
+
+__global__ void f32_to_bf16_kernel(const float* __restrict__ src, __nv_bfloat16* __restrict__ dst,
+                                   size_t n) {
+  const size_t i = ((size_t)blockIdx.x * blockDim.x + threadIdx.x) * 8;
+  if (i + 8 <= n) {
+    const float4 a = *reinterpret_cast<const float4*>(src + i);
+    const float4 b = *reinterpret_cast<const float4*>(src + i + 4);
+    __align__(16) __nv_bfloat16 o[8] = {
+        __float2bfloat16_rn(a.x), __float2bfloat16_rn(a.y), __float2bfloat16_rn(a.z),
+        __float2bfloat16_rn(a.w), __float2bfloat16_rn(b.x), __float2bfloat16_rn(b.y),
+        __float2bfloat16_rn(b.z), __float2bfloat16_rn(b.w)};
+    *reinterpret_cast<uint4*>(dst + i) = *reinterpret_cast<const uint4*>(o);
+  } else {
+    for (size_t k = i; k < n; ++k) dst[k] = __float2bfloat16_rn(src[k]);
+  }
+}
+
+// ---------------------------------------------------------------------------------------------
+// Host launchers
+
+int match_smem_bytes() { return kSmemBytes; }
+
+cudaError_t launch_match_top2(const CUtensorMap& tmap, const MatchParams& p, int num_sms, bool debug,
+                              cudaStream_t stream) {
+  static bool configured[2] = {false, false};
+  auto kern = debug ? match_top2_kernel<true> : match_top2_kernel<false>;
+  if (!configured[debug]) {
+    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes);
+    if (e != cudaSuccess) return e;
+    configured[debug] = true;
+  }
+  if (p.n_items <= 0) return cudaSuccess;
+  const int grid = p.n_items < num_sms ? p.n_items : num_sms;
+  kern<<<grid, kThreads, kSmemBytes, stream>>>(tmap, p);
+  return cudaGetLastError();
+}
+
+cudaError_t launch_emit_matches(const MatchParams& p, uint32_t* matches, int32_t* n_matches,
+                                cudaStream_t stream) {
+  if (p.n_pairs <= 0) return cudaSuccess;
+  emit_matches_kernel<<<p.n_pairs, 1024, 0, stream>>>(p, matches, n_matches);
+  return cudaGetLastError();
+}
+
+cudaError_t launch_u8_to_bf16(const uint8_t* src, void* dst, size_t n, cudaStream_t stream) {
+  if (n == 0) return cudaSuccess;
+  const size_t threads = (n + 15) / 16;
+  u8_to_bf16_kernel<<<(unsigned)((threads + 255) / 256), 256, 0, stream>>>(
+      src, reinterpret_cast<__nv_bfloat16*>(dst), n);
+  return cudaGetLastError();
+}
+
+cudaError_t launch_f32_to_bf16(const float* src, void* dst, size_t n, cudaStream_t stream) {
+  if (n == 0) return cudaSuccess;
+  const size_t threads = (n + 7) / 8;
+  f32_to_bf16_kernel<<<(unsigned)((threads + 255) / 256), 256, 0, stream>>>(
+      src, reinterpret_cast<__nv_bfloat16*>(dst), n);
+  return cudaGetLastError();
+}
+
+}  // namespace vc

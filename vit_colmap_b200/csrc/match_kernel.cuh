@@ -1,0 +1,37 @@
+// Internal interface between the C ABI (vc_api.cu) and the matcher kernels (match_kernel.cu).
+#pragma once
+#include <cstddef>
+#include <cstdint>
+#include <cuda.h>
+#include <cuda_bf16.h>
+#include <cuda_runtime.h>
+
+namespace vc {
+
+struct MatchParams {
+  const int32_t* counts;  // [n_images] valid descriptors per image
+  const int32_t* pairs;   // [n_pairs, 2] image indices
+  int n_pairs;
+  int kmax;               // padded descriptors per image (tensor-map extent)
+  int d;                  // descriptor dimension
+  int rb_per_img;         // ceil(kmax / 128)
+  int n_items;            // n_pairs * 2 * rb_per_img
+  float inv_norm, max_ratio, max_distance;
+  int cross_check;
+  int32_t* m_out;         // [n_pairs, 2, kmax] accepted best index or -1
+  float* top_best;        // optional diagnostics [n_pairs, 2, kmax]
+  float* top_second;
+  int32_t* top_idx;
+  float* dbg_scores;      // optional dense scores of pair 0 (debug kernel only)
+  int dbg_ld;
+};
+
+int match_smem_bytes();
+cudaError_t launch_match_top2(const CUtensorMap& tmap, const MatchParams& p, int num_sms, bool debug,
+                              cudaStream_t stream);
+cudaError_t launch_emit_matches(const MatchParams& p, uint32_t* matches, int32_t* n_matches,
+                                cudaStream_t stream);
+cudaError_t launch_u8_to_bf16(const uint8_t* src, void* dst, size_t n, cudaStream_t stream);
+cudaError_t launch_f32_to_bf16(const float* src, void* dst, size_t n, cudaStream_t stream);
+
+}  // namespace vc

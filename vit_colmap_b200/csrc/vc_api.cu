@@ -1,0 +1,330 @@
+// C ABI of libvc_b200 (see include/vc_b200.h).  Host-side glue only: argument checks, TMA
+// descriptor creation, workspace carving, launches.  No CPU compute path exists here: without an
+// sm_100 device every entry point fails with VC_ERR_NO_DEVICE.
+#include "../../include/vc_b200.h"
+
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+#include <string>
+#include <vector>
+
+#include "match_kernel.cuh"
+
+namespace {
+
+thread_local std::string g_err;
+thread_local int64_t g_launches = 0;
+
+int fail(int code, const char* fmt, ...) {
+  char buf[512];
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(buf, sizeof(buf), fmt, ap);
+  va_end(ap);
+  g_err = buf;
+  return code;
+}
+
+#define VC_CUDA(expr)                                                                         \
+  do {                                                                                        \
+    cudaError_t _e = (expr);                                                                  \
+    if (_e != cudaSuccess)                                                                    \
+      return fail(VC_ERR_CUDA, "%s failed: %s (%s:%d)", #expr, cudaGetErrorString(_e), __FILE__, \
+                  __LINE__);                                                                  \
+  } while (0)
+
+using EncodeTiledFn = CUresult (*)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*,
+                                   const cuuint64_t*, const cuuint64_t*, const cuuint32_t*,
+                                   const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                   CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
+
+}  // namespace
+
+struct vc_handle {
+  int device = 0;
+  int num_sms = 0;
+  EncodeTiledFn encode = nullptr;
+  // cached descriptor for the last (ptr, n_images, kmax, d)
+  const void* map_ptr = nullptr;
+  int map_n = 0, map_k = 0, map_d = 0;
+  CUtensorMap map;
+  // device staging owned by the host-buffer entry point
+  void* stage = nullptr;
+  size_t stage_bytes = 0;
+};
+
+namespace {
+
+int make_desc_map(vc_handle* h, const void* desc, int n_images, int kmax, int d) {
+  if (h->map_ptr == desc && h->map_n == n_images && h->map_k == kmax && h->map_d == d) return VC_OK;
+  if ((reinterpret_cast<uintptr_t>(desc) & 15) != 0)
+    return fail(VC_ERR_INVALID, "descriptor base must be 16-byte aligned");
+  if (d <= 0 || d % 8 != 0) return fail(VC_ERR_INVALID, "d=%d must be a positive multiple of 8", d);
+  // dims fastest-first: (d, kmax, n_images); box = 64 bf16 (128 B, one swizzle row) x 128 rows
+  cuuint64_t gdim[3] = {(cuuint64_t)d, (cuuint64_t)kmax, (cuuint64_t)n_images};
+  cuuint64_t gstride[2] = {(cuuint64_t)d * 2, (cuuint64_t)d * 2 * (cuuint64_t)kmax};
+  cuuint32_t box[3] = {64, 128, 1};
+  cuuint32_t estr[3] = {1, 1, 1};
+  CUresult r = h->encode(&h->map, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 3, const_cast<void*>(desc), gdim,
+                         gstride, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                         CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                         CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) {
+    h->map_ptr = nullptr;
+    return fail(VC_ERR_CUDA, "cuTensorMapEncodeTiled failed with CUresult %d", (int)r);
+  }
+  h->map_ptr = desc;
+  h->map_n = n_images;
+  h->map_k = kmax;
+  h->map_d = d;
+  return VC_OK;
+}
+
+struct MatchWs {
+  int32_t* m_out;
+  size_t bytes;
+};
+
+size_t m_out_bytes(int n_pairs, int kmax) {
+  return align_up((size_t)n_pairs * 2 * (size_t)kmax * sizeof(int32_t), 256);
+}
+
+int check_match_args(vc_handle* h, const void* desc, const int32_t* counts, int n_images, int kmax,
+                     int d, const int32_t* pairs, int n_pairs, const vc_match_options* opt) {
+  if (!h) return fail(VC_ERR_INVALID, "null handle");
+  if (!desc || !counts || !opt) return fail(VC_ERR_INVALID, "null pointer argument");
+  if (n_pairs > 0 && !pairs) return fail(VC_ERR_INVALID, "null pairs");
+  if (n_images <= 0 || kmax <= 0 || n_pairs < 0)
+    return fail(VC_ERR_INVALID, "bad sizes n_images=%d kmax=%d n_pairs=%d", n_images, kmax, n_pairs);
+  if (d <= 0 || d % 8 != 0) return fail(VC_ERR_INVALID, "d=%d must be a positive multiple of 8", d);
+  return VC_OK;
+}
+
+vc::MatchParams make_params(const int32_t* counts, const int32_t* pairs, int n_pairs, int kmax, int d,
+                            const vc_match_options* opt, int32_t* m_out) {
+  vc::MatchParams p{};
+  p.counts = counts;
+  p.pairs = pairs;
+  p.n_pairs = n_pairs;
+  p.kmax = kmax;
+  p.d = d;
+  p.rb_per_img = (kmax + 127) / 128;
+  p.n_items = n_pairs * 2 * p.rb_per_img;
+  p.inv_norm = opt->inv_norm;
+  p.max_ratio = opt->max_ratio;
+  p.max_distance = opt->max_distance;
+  p.cross_check = opt->cross_check;
+  p.m_out = m_out;
+  return p;
+}
+
+}  // namespace
+
+extern "C" {
+
+const char* vc_last_error(void) { return g_err.c_str(); }
+const char* vc_version(void) { return "vc_b200 0.1 (sm_100a)"; }
+
+int64_t vc_launch_count(int reset) {
+  const int64_t v = g_launches;
+  if (reset) g_launches = 0;
+  return v;
+}
+
+int vc_create(int device, vc_handle** out) {
+  if (!out) return fail(VC_ERR_INVALID, "null out");
+  *out = nullptr;
+  int n = 0;
+  if (cudaGetDeviceCount(&n) != cudaSuccess || n <= 0 || device < 0 || device >= n)
+    return fail(VC_ERR_NO_DEVICE, "no CUDA device %d (found %d); this library has no CPU fallback",
+                device, n);
+  cudaDeviceProp prop;
+  VC_CUDA(cudaGetDeviceProperties(&prop, device));
+  if (prop.major != 10)
+    return fail(VC_ERR_NO_DEVICE, "device %d is sm_%d%d; kernels are built for sm_100a only", device,
+                prop.major, prop.minor);
+  VC_CUDA(cudaSetDevice(device));
+  vc_handle* h = new vc_handle();
+  h->device = device;
+  h->num_sms = prop.multiProcessorCount;
+  void* fn = nullptr;
+  cudaDriverEntryPointQueryResult qres;
+  cudaError_t e = cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &qres);
+  if (e != cudaSuccess || fn == nullptr || qres != cudaDriverEntryPointSuccess) {
+    delete h;
+    return fail(VC_ERR_CUDA, "cuTensorMapEncodeTiled entry point unavailable");
+  }
+  h->encode = reinterpret_cast<EncodeTiledFn>(fn);
+  *out = h;
+  return VC_OK;
+}
+
+int vc_destroy(vc_handle* h) {
+  if (!h) return VC_OK;
+  cudaSetDevice(h->device);
+  cudaDeviceSynchronize();
+  if (h->stage) cudaFree(h->stage);
+  delete h;
+  return VC_OK;
+}
+
+size_t vc_match_workspace_bytes(int n_pairs, int kmax) {
+  if (n_pairs <= 0 || kmax <= 0) return 256;
+  return m_out_bytes(n_pairs, kmax);
+}
+
+static int match_impl(vc_handle* h, const void* desc, const int32_t* counts, int n_images, int kmax,
+                      int d, const int32_t* pairs, int n_pairs, const vc_match_options* opt,
+                      uint32_t* matches, int32_t* n_matches, float* best, float* second,
+                      int32_t* index, void* workspace, size_t workspace_bytes, void* stream) {
+  int rc = check_match_args(h, desc, counts, n_images, kmax, d, pairs, n_pairs, opt);
+  if (rc != VC_OK) return rc;
+  if (n_pairs == 0) return VC_OK;
+  if (!workspace || workspace_bytes < vc_match_workspace_bytes(n_pairs, kmax))
+    return fail(VC_ERR_WORKSPACE, "workspace %zu B < required %zu B", workspace_bytes,
+                vc_match_workspace_bytes(n_pairs, kmax));
+  VC_CUDA(cudaSetDevice(h->device));
+  rc = make_desc_map(h, desc, n_images, kmax, d);
+  if (rc != VC_OK) return rc;
+  cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
+  vc::MatchParams p = make_params(counts, pairs, n_pairs, kmax, d, opt,
+                                  reinterpret_cast<int32_t*>(workspace));
+  p.top_best = best;
+  p.top_second = second;
+  p.top_idx = index;
+  VC_CUDA(vc::launch_match_top2(h->map, p, h->num_sms, false, s));
+  ++g_launches;
+  if (matches && n_matches) {
+    VC_CUDA(vc::launch_emit_matches(p, matches, n_matches, s));
+    ++g_launches;
+  }
+  return VC_OK;
+}
+
+int vc_match_pairs(vc_handle* h, const void* desc, const int32_t* counts, int n_images, int kmax,
+                   int d, const int32_t* pairs, int n_pairs, const vc_match_options* opt,
+                   uint32_t* matches, int32_t* n_matches, void* workspace, size_t workspace_bytes,
+                   void* stream) {
+  if (!matches || !n_matches) return fail(VC_ERR_INVALID, "null output pointer");
+  return match_impl(h, desc, counts, n_images, kmax, d, pairs, n_pairs, opt, matches, n_matches,
+                    nullptr, nullptr, nullptr, workspace, workspace_bytes, stream);
+}
+
+int vc_match_pairs_top2(vc_handle* h, const void* desc, const int32_t* counts, int n_images,
+                        int kmax, int d, const int32_t* pairs, int n_pairs,
+                        const vc_match_options* opt, float* best, float* second, int32_t* index,
+                        void* workspace, size_t workspace_bytes, void* stream) {
+  if (!best || !second || !index) return fail(VC_ERR_INVALID, "null output pointer");
+  return match_impl(h, desc, counts, n_images, kmax, d, pairs, n_pairs, opt, nullptr, nullptr, best,
+                    second, index, workspace, workspace_bytes, stream);
+}
+
+int vc_debug_scores(vc_handle* h, const void* desc, const int32_t* counts, int n_images, int kmax,
+                    int d, int image1, int image2, float* scores, int ld, void* stream) {
+  vc_match_options opt{0.8f, 0.7f, 1, 1.0f};
+  int rc = check_match_args(h, desc, counts, n_images, kmax, d, nullptr, 0, &opt);
+  if (rc != VC_OK) return rc;
+  if (!scores || ld < kmax || image1 < 0 || image2 < 0 || image1 >= n_images || image2 >= n_images)
+    return fail(VC_ERR_INVALID, "bad debug arguments");
+  VC_CUDA(cudaSetDevice(h->device));
+  rc = make_desc_map(h, desc, n_images, kmax, d);
+  if (rc != VC_OK) return rc;
+  cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
+  int32_t host_pair[2] = {image1, image2};
+  int32_t* dev = nullptr;
+  const size_t mb = m_out_bytes(1, kmax);
+  VC_CUDA(cudaMalloc(&dev, 256 + mb));
+  VC_CUDA(cudaMemcpyAsync(dev, host_pair, sizeof(host_pair), cudaMemcpyHostToDevice, s));
+  vc::MatchParams p = make_params(counts, dev, 1, kmax, d, &opt, dev + 64);
+  p.dbg_scores = scores;
+  p.dbg_ld = ld;
+  cudaError_t e = vc::launch_match_top2(h->map, p, h->num_sms, true, s);
+  ++g_launches;
+  cudaError_t e2 = cudaStreamSynchronize(s);
+  cudaFree(dev);
+  VC_CUDA(e);
+  VC_CUDA(e2);
+  return VC_OK;
+}
+
+int vc_convert_u8_to_bf16(const uint8_t* src, void* dst_bf16, size_t n, void* stream) {
+  if (!src || !dst_bf16) return fail(VC_ERR_INVALID, "null pointer");
+  VC_CUDA(vc::launch_u8_to_bf16(src, dst_bf16, n, reinterpret_cast<cudaStream_t>(stream)));
+  ++g_launches;
+  return VC_OK;
+}
+
+int vc_convert_f32_to_bf16(const float* src, void* dst_bf16, size_t n, void* stream) {
+  if (!src || !dst_bf16) return fail(VC_ERR_INVALID, "null pointer");
+  VC_CUDA(vc::launch_f32_to_bf16(src, dst_bf16, n, reinterpret_cast<cudaStream_t>(stream)));
+  ++g_launches;
+  return VC_OK;
+}
+
+int vc_match_pairs_host(vc_handle* h, const uint8_t* desc_u8, const float* desc_f32,
+                        const int32_t* counts, int n_images, int kmax, int d, const int32_t* pairs,
+                        int n_pairs, const vc_match_options* opt, uint32_t* matches,
+                        int32_t* n_matches) {
+  if (!h) return fail(VC_ERR_INVALID, "null handle");
+  if ((!desc_u8 && !desc_f32) || !counts || !opt || !matches || !n_matches || (n_pairs > 0 && !pairs))
+    return fail(VC_ERR_INVALID, "null pointer argument");
+  if (n_images <= 0 || kmax <= 0 || n_pairs < 0 || d <= 0 || d % 8 != 0)
+    return fail(VC_ERR_INVALID, "bad sizes");
+  if (n_pairs == 0) return VC_OK;
+  VC_CUDA(cudaSetDevice(h->device));
+  const size_t n_el = (size_t)n_images * kmax * d;
+  const size_t src_bytes = align_up(desc_u8 ? n_el : n_el * 4, 256);
+  const size_t bf_bytes = align_up(n_el * 2, 256);
+  const size_t cnt_bytes = align_up((size_t)n_images * 4, 256);
+  const size_t pair_bytes = align_up((size_t)n_pairs * 8, 256);
+  const size_t out_bytes = align_up((size_t)n_pairs * kmax * 8, 256);
+  const size_t nm_bytes = align_up((size_t)n_pairs * 4, 256);
+  const size_t ws_bytes = vc_match_workspace_bytes(n_pairs, kmax);
+  const size_t total = src_bytes + bf_bytes + cnt_bytes + pair_bytes + out_bytes + nm_bytes + ws_bytes;
+  if (h->stage_bytes < total) {
+    if (h->stage) cudaFree(h->stage);
+    h->stage = nullptr;
+    h->stage_bytes = 0;
+    VC_CUDA(cudaMalloc(&h->stage, total));
+    h->stage_bytes = total;
+    h->map_ptr = nullptr;
+  }
+  uint8_t* base = static_cast<uint8_t*>(h->stage);
+  uint8_t* d_src = base;
+  uint8_t* d_bf = d_src + src_bytes;
+  int32_t* d_cnt = reinterpret_cast<int32_t*>(d_bf + bf_bytes);
+  int32_t* d_pairs = reinterpret_cast<int32_t*>(reinterpret_cast<uint8_t*>(d_cnt) + cnt_bytes);
+  uint32_t* d_out = reinterpret_cast<uint32_t*>(reinterpret_cast<uint8_t*>(d_pairs) + pair_bytes);
+  int32_t* d_nm = reinterpret_cast<int32_t*>(reinterpret_cast<uint8_t*>(d_out) + out_bytes);
+  void* d_ws = reinterpret_cast<uint8_t*>(d_nm) + nm_bytes;
+  cudaStream_t s = 0;
+  if (desc_u8) {
+    VC_CUDA(cudaMemcpyAsync(d_src, desc_u8, n_el, cudaMemcpyHostToDevice, s));
+    VC_CUDA(vc::launch_u8_to_bf16(d_src, d_bf, n_el, s));
+  } else {
+    VC_CUDA(cudaMemcpyAsync(d_src, desc_f32, n_el * 4, cudaMemcpyHostToDevice, s));
+    VC_CUDA(vc::launch_f32_to_bf16(reinterpret_cast<const float*>(d_src), d_bf, n_el, s));
+  }
+  ++g_launches;
+  VC_CUDA(cudaMemcpyAsync(d_cnt, counts, (size_t)n_images * 4, cudaMemcpyHostToDevice, s));
+  VC_CUDA(cudaMemcpyAsync(d_pairs, pairs, (size_t)n_pairs * 8, cudaMemcpyHostToDevice, s));
+  int rc = vc_match_pairs(h, d_bf, d_cnt, n_images, kmax, d, d_pairs, n_pairs, opt, d_out, d_nm, d_ws,
+                          ws_bytes, s);
+  if (rc != VC_OK) return rc;
+  VC_CUDA(cudaMemcpyAsync(n_matches, d_nm, (size_t)n_pairs * 4, cudaMemcpyDeviceToHost, s));
+  VC_CUDA(cudaStreamSynchronize(s));
+  // download only the filled prefix of every pair's slot
+  for (int i = 0; i < n_pairs; ++i) {
+    const int n = n_matches[i];
+    if (n > 0)
+      VC_CUDA(cudaMemcpyAsync(matches + (size_t)i * kmax * 2, d_out + (size_t)i * kmax * 2,
+                              (size_t)n * 8, cudaMemcpyDeviceToHost, s));
+  }
+  VC_CUDA(cudaStreamSynchronize(s));
+  return VC_OK;
+}
+
+}  // extern "C"

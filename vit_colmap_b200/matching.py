@@ -1,0 +1,201 @@
+"""Host-side mirror of the reference's matching interface, running on the sm_100a kernels.
+
+Reference boundary: ``pycolmap.match_exhaustive(database_path, matching_options, ...)``
+(PYCOLMAP/pipeline/match_features.cc:28-51,210-223) as called by
+``vit_colmap/pipeline/run_pipeline.py:351-363``; matcher semantics COLMAP/feature/sift.cc:733-825.
+PyTorch is used only for device memory and streams; every computation is a call into the C ABI
+(include/vc_b200.h).
+"""
+from __future__ import annotations
+
+import ctypes
+from dataclasses import dataclass
+from typing import Optional, Sequence
+
+import numpy as np
+
+from . import _lib
+from .pairing import ExhaustivePairGenerator
+
+SQ_SIFT_NORM = 512.0 * 512.0  # COLMAP/feature/sift.cc:63
+
+
+@dataclass
+class SiftMatchingOptions:
+    """COLMAP/feature/sift.h:108-126 (fields used on this path)."""
+    max_ratio: float = 0.8
+    max_distance: float = 0.7
+    cross_check: bool = True
+
+
+@dataclass
+class FeatureMatchingOptions:
+    """COLMAP/feature/matcher.h:53-91 (fields used on this path) with the nested SIFT options
+    flattened the way vit_colmap/utils/config.py:64-96 fills them."""
+    use_gpu: bool = True
+    gpu_index: str = "-1"
+    num_threads: int = -1
+    max_num_matches: int = 32768
+    guided_matching: bool = False
+    max_ratio: float = 0.8
+    max_distance: float = 0.7
+    cross_check: bool = True
+    # COLMAP/controllers/feature_matching_utils.cc:485-488 blanks pairs with fewer matches
+    min_num_matches: int = 15
+
+
+def _ptr(t) -> int:
+    return 0 if t is None else int(t.data_ptr())
+
+
+class Matcher:
+    """One per GPU (COLMAP creates one SiftMatchGPU per device,
+    controllers/feature_matching_utils.cc:66-84)."""
+
+    def __init__(self, device: int = 0):
+        import torch
+        if not torch.cuda.is_available():
+            raise _lib.VcError("no CUDA device: vit_colmap_b200 has no CPU fallback")
+        self.torch = torch
+        self.device = int(device)
+        self.lib = _lib.load()
+        h = ctypes.c_void_p()
+        _lib.check(self.lib.vc_create(self.device, ctypes.byref(h)))
+        self.handle = h
+        self._ws = None
+
+    def close(self):
+        if getattr(self, "handle", None):
+            self.lib.vc_destroy(self.handle)
+            self.handle = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    # ------------------------------------------------------------------ helpers
+    def _dev(self):
+        return self.torch.device("cuda", self.device)
+
+    def _stream(self) -> int:
+        return int(self.torch.cuda.current_stream(self._dev()).cuda_stream)
+
+    def _workspace(self, n_pairs: int, kmax: int):
+        need = int(self.lib.vc_match_workspace_bytes(n_pairs, kmax))
+        if self._ws is None or self._ws.numel() < need:
+            self._ws = self.torch.empty(need, dtype=self.torch.uint8, device=self._dev())
+        return self._ws, need
+
+    @staticmethod
+    def _opts(max_ratio, max_distance, cross_check, inv_norm) -> _lib.MatchOptions:
+        return _lib.MatchOptions(float(max_ratio), float(max_distance), int(bool(cross_check)),
+                                 float(inv_norm))
+
+    def to_bf16(self, desc):
+        """uint8 / float32 device tensor -> bf16 device tensor via the library's converters."""
+        torch = self.torch
+        desc = desc.contiguous()
+        out = torch.empty(desc.shape, dtype=torch.bfloat16, device=desc.device)
+        if desc.dtype == torch.uint8:
+            _lib.check(self.lib.vc_convert_u8_to_bf16(_ptr(desc), _ptr(out), desc.numel(), self._stream()))
+        elif desc.dtype == torch.float32:
+            _lib.check(self.lib.vc_convert_f32_to_bf16(_ptr(desc), _ptr(out), desc.numel(), self._stream()))
+        elif desc.dtype == torch.bfloat16:
+            return desc
+        else:
+            raise TypeError(f"unsupported descriptor dtype {desc.dtype}")
+        return out
+
+    # ------------------------------------------------------------------ device-resident path
+    def match_pairs(self, desc, counts, pairs, max_ratio=0.8, max_distance=0.7, cross_check=True,
+                    inv_norm=1.0, out=None):
+        """desc bf16 [n_images,kmax,d], counts int32 [n_images], pairs int32 [n_pairs,2]; all on
+        this device.  Returns (matches int32-viewed-uint32 [n_pairs,kmax,2], n_matches int32)."""
+        torch = self.torch
+        assert desc.dtype == torch.bfloat16 and desc.is_contiguous() and desc.dim() == 3
+        n_images, kmax, d = desc.shape
+        n_pairs = int(pairs.shape[0])
+        if out is None:
+            matches = torch.empty((n_pairs, kmax, 2), dtype=torch.int32, device=desc.device)
+            n_matches = torch.empty((n_pairs,), dtype=torch.int32, device=desc.device)
+        else:
+            matches, n_matches = out
+        ws, need = self._workspace(n_pairs, kmax)
+        opt = self._opts(max_ratio, max_distance, cross_check, inv_norm)
+        _lib.check(self.lib.vc_match_pairs(self.handle, _ptr(desc), _ptr(counts), n_images, kmax, d,
+                                           _ptr(pairs), n_pairs, ctypes.byref(opt), _ptr(matches),
+                                           _ptr(n_matches), _ptr(ws), need, self._stream()))
+        return matches, n_matches
+
+    def top2(self, desc, counts, pairs, max_ratio=0.8, max_distance=0.7, cross_check=True, inv_norm=1.0):
+        """Diagnostics: (best, second, index) [n_pairs,2,kmax] of the same launch."""
+        torch = self.torch
+        n_images, kmax, d = desc.shape
+        n_pairs = int(pairs.shape[0])
+        best = torch.zeros((n_pairs, 2, kmax), dtype=torch.float32, device=desc.device)
+        second = torch.zeros_like(best)
+        index = torch.full((n_pairs, 2, kmax), -1, dtype=torch.int32, device=desc.device)
+        ws, need = self._workspace(n_pairs, kmax)
+        opt = self._opts(max_ratio, max_distance, cross_check, inv_norm)
+        _lib.check(self.lib.vc_match_pairs_top2(self.handle, _ptr(desc), _ptr(counts), n_images, kmax, d,
+                                                _ptr(pairs), n_pairs, ctypes.byref(opt), _ptr(best),
+                                                _ptr(second), _ptr(index), _ptr(ws), need,
+                                                self._stream()))
+        return best, second, index
+
+    def debug_scores(self, desc, counts, image1: int, image2: int):
+        torch = self.torch
+        n_images, kmax, d = desc.shape
+        scores = torch.zeros((kmax, kmax), dtype=torch.float32, device=desc.device)
+        _lib.check(self.lib.vc_debug_scores(self.handle, _ptr(desc), _ptr(counts), n_images, kmax, d,
+                                            int(image1), int(image2), _ptr(scores), kmax, self._stream()))
+        return scores
+
+    # ------------------------------------------------------------------ host-buffer path
+    def match_pairs_host(self, desc: np.ndarray, counts: np.ndarray, pairs: np.ndarray, max_ratio=0.8,
+                         max_distance=0.7, cross_check=True, inv_norm: Optional[float] = None):
+        """desc: host uint8 or float32 [n_images,kmax,d].  Returns a list of [n,2] uint32 arrays."""
+        desc = np.ascontiguousarray(desc)
+        counts = np.ascontiguousarray(counts, dtype=np.int32)
+        pairs = np.ascontiguousarray(pairs, dtype=np.int32).reshape(-1, 2)
+        n_images, kmax, d = desc.shape
+        n_pairs = pairs.shape[0]
+        if desc.dtype == np.uint8:
+            u8, f32 = desc.ctypes.data, None
+            inv = 1.0 / SQ_SIFT_NORM if inv_norm is None else inv_norm
+        elif desc.dtype == np.float32:
+            u8, f32 = None, desc.ctypes.data
+            inv = 1.0 if inv_norm is None else inv_norm
+        else:
+            raise TypeError("descriptors must be uint8 or float32")
+        matches = np.empty((max(n_pairs, 1), kmax, 2), dtype=np.uint32)
+        n_matches = np.zeros((max(n_pairs, 1),), dtype=np.int32)
+        opt = self._opts(max_ratio, max_distance, cross_check, inv)
+        _lib.check(self.lib.vc_match_pairs_host(self.handle, u8, f32, counts.ctypes.data, n_images, kmax,
+                                                d, pairs.ctypes.data, n_pairs, ctypes.byref(opt),
+                                                matches.ctypes.data, n_matches.ctypes.data))
+        return [matches[i, :n_matches[i]].copy() for i in range(n_pairs)]
+
+
+def match_descriptor_sets(descriptors: Sequence[np.ndarray], pairs, options: Optional[FeatureMatchingOptions] = None,
+                          matcher: Optional[Matcher] = None, device: int = 0):
+    """Match host descriptor arrays (ragged list of [n_i, d] uint8 or float32) for the given index
+    pairs.  Pads to a common kmax, calls the host-buffer C entry, returns list of [n,2] uint32."""
+    options = options or FeatureMatchingOptions()
+    matcher = matcher or Matcher(device)
+    n_images = len(descriptors)
+    d = max((int(x.shape[1]) for x in descriptors if x.ndim == 2 and x.shape[0] > 0), default=128)
+    dtype = np.uint8 if all(x.dtype == np.uint8 for x in descriptors) else np.float32
+    kmax = max(max((int(x.shape[0]) for x in descriptors), default=0), 1)
+    kmax = min(kmax, options.max_num_matches)  # SIFTGPU/SiftMatchCU.cpp:108 clamps inputs likewise
+    buf = np.zeros((n_images, kmax, d), dtype=dtype)
+    counts = np.zeros((n_images,), dtype=np.int32)
+    for i, x in enumerate(descriptors):
+        n = min(int(x.shape[0]), kmax)
+        counts[i] = n
+        if n:
+            buf[i, :n] = x[:n]
+    return matcher.match_pairs_host(buf, counts, np.asarray(pairs, dtype=np.int32),
+                                    options.max_ratio, options.max_distance, options.cross_check)
