@@ -32,6 +32,8 @@ typedef enum {
 
 /* Matching thresholds: COLMAP/feature/sift.h:108-126 (SiftMatchingOptions: max_ratio 0.8,
  * max_distance 0.7, cross_check true), vit_colmap/utils/config.py:58-62. */
+typedef enum { VC_DTYPE_U8 = 0, VC_DTYPE_F32 = 1, VC_DTYPE_BF16 = 2 } vc_dtype;
+
 typedef struct {
   float max_ratio;
   float max_distance;
@@ -61,6 +63,8 @@ size_t vc_match_workspace_bytes(int n_pairs, int kmax);
  *   pairs     : device, int32 [n_pairs, 2], indices into the image axis (image1, image2)
  *   matches   : device, uint32 [n_pairs, kmax, 2] -> (idx1, idx2) ascending in idx1
  *   n_matches : device, int32 [n_pairs]
+ *   (matches == n_matches == NULL runs only the top-2 stage and leaves the accepted best
+ *    indices, int32 [n_pairs, 2, kmax], at the start of `workspace`.)
  * Semantics: FindBestMatchesBruteForce, COLMAP/feature/sift.cc:733-825 (score matrix
  * sift.cc:922-971); replaces SiftMatchGPU::GetSiftMatch (SIFTGPU/SiftMatchCU.cpp:161-199) and
  * the kernels SIFTGPU/ProgramCU.cu:1411-1495,1696-1797.  The N x M score matrix stays in
@@ -87,19 +91,18 @@ int vc_debug_scores(vc_handle* h, const void* desc, const int32_t* counts, int n
 /*
  * Host-buffer entry (what a pycolmap-style caller binds): descriptors and results live in host
  * memory; the call uploads, matches every pair and downloads, synchronising before it returns.
- *   desc_u8   : host uint8 [n_images, kmax, d] (COLMAP FeatureDescriptors, feature/types.h:80-81)
- *               or NULL if desc_f32 is given
- *   desc_f32  : host float [n_images, kmax, d] unit-norm rows (north-star float mode) or NULL
+ *   desc      : host [n_images, kmax, d] in `dtype`: VC_DTYPE_U8 (COLMAP FeatureDescriptors,
+ *               feature/types.h:80-81), VC_DTYPE_F32 or VC_DTYPE_BF16 (unit-norm rows,
+ *               north-star float mode).  Pinned memory makes the upload asynchronous.
  *   counts    : host int32 [n_images];  pairs: host int32 [n_pairs, 2]
  *   matches   : host uint32 [n_pairs, kmax, 2];  n_matches: host int32 [n_pairs]
  * Replaces: the matcher worker loop COLMAP/controllers/feature_matching_utils.cc:109-167
  * (GetDescriptors -> matcher->Match) as driven by pycolmap.match_exhaustive
  * (PYCOLMAP/pipeline/match_features.cc:28-51).
  */
-int vc_match_pairs_host(vc_handle* h, const uint8_t* desc_u8, const float* desc_f32,
-                        const int32_t* counts, int n_images, int kmax, int d, const int32_t* pairs,
-                        int n_pairs, const vc_match_options* opt, uint32_t* matches,
-                        int32_t* n_matches);
+int vc_match_pairs_host(vc_handle* h, const void* desc, int dtype, const int32_t* counts,
+                        int n_images, int kmax, int d, const int32_t* pairs, int n_pairs,
+                        const vc_match_options* opt, uint32_t* matches, int32_t* n_matches);
 
 /* Element-wise converters used by the host entry and the Python mirror (device pointers).
  * u8 -> bf16 is exact (0..255 fit bf16's 8-bit significand), so uint8 d<=258 matching through

@@ -33,7 +33,7 @@ def _make_set(rng, n_images, kmax, d, counts):
             m = min(n, counts[j - 1]) // 2
             src = rng.permutation(counts[j - 1])[:m]
             dst = rng.permutation(n)[:m]
-            y = desc[j - 1, src] + 0.05 * rng.standard_normal((m, d)).astype(np.float32)
+            y = desc[j - 1, src] + (0.35 / d ** 0.5) * rng.standard_normal((m, d)).astype(np.float32)
             x[dst] = y / np.linalg.norm(y, axis=1, keepdims=True)
         desc[j, :n] = x
     return _bf16_round(desc)

@@ -1,0 +1,97 @@
+"""CPU-side tests: C-ABI exports, COLMAP database layout, pair generation / sharding."""
+import ctypes
+import re
+import sqlite3
+import struct
+from pathlib import Path
+
+import numpy as np
+import pytest
+
+ROOT = Path(__file__).resolve().parent.parent
+
+
+def test_c_abi_exports_every_declared_symbol():
+    from vit_colmap_b200 import _lib, build
+    build.build()
+    header = (ROOT / "include" / "vc_b200.h").read_text()
+    declared = set(re.findall(r"\b(vc_[a-z0-9_]+)\s*\(", header))
+    assert declared, "no declarations parsed"
+    lib = ctypes.CDLL(str(_lib.LIB_PATH))
+    for name in declared:
+        assert hasattr(lib, name), f"{name} declared in vc_b200.h but not exported"
+    assert declared == set(_lib.SIGNATURES), "ctypes table out of sync with the header"
+    assert b"sm_100a" in _lib.load().vc_version()
+
+
+def test_no_device_fails_loudly():
+    import torch
+    if torch.cuda.is_available():
+        pytest.skip("GPU present")
+    from vit_colmap_b200 import _lib
+    from vit_colmap_b200.matching import Matcher
+    with pytest.raises(_lib.VcError):
+        Matcher(0)
+    h = ctypes.c_void_p()
+    rc = _lib.load().vc_create(0, ctypes.byref(h))
+    assert rc == -3 and b"no CPU fallback" in _lib.load().vc_last_error()
+
+
+def test_database_layout(tmp_path):
+    from vit_colmap_b200.database import ColmapDatabase, make_camera
+    from vit_colmap_b200.pairing import image_pair_to_pair_id
+    path = tmp_path / "db.db"
+    cdb = ColmapDatabase(str(path))
+    cam = cdb.db.write_camera(make_camera("PINHOLE", 640, 480, [640.0, 640.0, 320.0, 240.0]))
+    ids = [cdb.add_image(f"im{i}.png", cam) for i in range(3)]
+    assert ids == [1, 2, 3]
+    kp = np.arange(12, dtype=np.float64).reshape(6, 2)
+    desc = (np.arange(6 * 128) % 251).reshape(6, 128)
+    cdb.add_keypoints(1, kp)
+    cdb.add_descriptors(1, desc)
+    m = np.array([[0, 5], [3, 1]], dtype=np.int64)
+    cdb.add_matches(2, 1, m)          # id1 > id2 -> stored swapped (database_sqlite.cc:1115-1121)
+    cdb.add_matches(1, 3, np.zeros((0, 2)))
+    assert cdb.get_db_count(cdb.db, "num_images") == 3
+    assert cdb.get_db_count(cdb.db, "num_cameras") == 1
+    assert cdb.get_db_count(cdb.db, "num_matched_image_pairs") == 2  # empty rows count
+    assert cdb.db.exists_keypoints(1) and cdb.db.exists_descriptors(1) and not cdb.db.exists_keypoints(2)
+    assert cdb.db.read_matches(2, 1).tolist() == m.tolist()
+    assert cdb.db.read_matches(1, 2).tolist() == m[:, ::-1].tolist()
+    cdb.db.close()
+    con = sqlite3.connect(str(path))
+    assert con.execute("PRAGMA user_version").fetchone()[0] == 3900
+    tables = {r[0] for r in con.execute("SELECT name FROM sqlite_master WHERE type='table'")}
+    assert {"cameras", "images", "keypoints", "descriptors", "matches", "two_view_geometries", "rigs",
+            "rig_sensors", "frames", "frame_data", "pose_priors"} <= tables
+    rows, cols, data = con.execute("SELECT rows, cols, data FROM keypoints WHERE image_id=1").fetchone()
+    assert (rows, cols) == (6, 2) and data == kp.astype(np.float32).tobytes()
+    rows, cols, data = con.execute("SELECT rows, cols, data FROM descriptors WHERE image_id=1").fetchone()
+    assert (rows, cols) == (6, 128) and data == desc.astype(np.uint8).tobytes()
+    pid = image_pair_to_pair_id(2, 1)
+    assert pid == 2147483647 * 1 + 2
+    rows, cols, data = con.execute("SELECT rows, cols, data FROM matches WHERE pair_id=?", (pid,)).fetchone()
+    assert (rows, cols) == (2, 2) and struct.unpack("<4I", data) == (5, 0, 1, 3)
+    model, w, h, params, prior = con.execute("SELECT model,width,height,params,prior_focal_length FROM cameras").fetchone()
+    assert (model, w, h, prior) == (1, 640, 480, 0) and struct.unpack("<4d", params) == (640.0, 640.0, 320.0, 240.0)
+    with ColmapDatabase.open_database(str(path)) as db:
+        assert ColmapDatabase.get_db_count(db, "num_images") == 3
+
+
+def test_pair_generator_matches_oracle_and_shards():
+    from oracle import matching as om
+    from vit_colmap_b200.pairing import ExhaustivePairGenerator, shard_blocks, shard_pairs
+    for n, bs in [(34, 10), (49, 50), (8, 3), (1, 50), (0, 50), (101, 50)]:
+        ids = list(range(1, n + 1))
+        gen = ExhaustivePairGenerator(ids, bs)
+        blocks = list(gen.blocks())
+        ref, sizes = om.exhaustive_pairs(np.array(ids, np.uint32), bs) if n else (np.zeros((0, 2)), [])
+        flat = [p for b in blocks for p in b]
+        assert flat == [tuple(x) for x in np.asarray(ref).tolist()]
+        assert [len(b) for b in blocks] == list(sizes)
+        assert len({(min(a, b), max(a, b)) for a, b in flat}) == n * (n - 1) // 2
+        for world in (1, 2, 8):
+            assign = shard_blocks([len(b) for b in blocks], world)
+            assert sorted(x for a in assign for x in a) == list(range(len(blocks)))
+            parts = [shard_pairs(flat, r, world) for r in range(world)]
+            assert [p for part in parts for p in part] == flat

@@ -40,11 +40,13 @@ SIGNATURES = {
                                     c_size_t, c_void_p]),
     "vc_debug_scores": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_int,
                                 c_void_p, c_int, c_void_p]),
-    "vc_match_pairs_host": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int,
+    "vc_match_pairs_host": (c_int, [c_void_p, c_void_p, c_int, c_void_p, c_int, c_int, c_int,
                                     c_void_p, c_int, POINTER(MatchOptions), c_void_p, c_void_p]),
     "vc_convert_u8_to_bf16": (c_int, [c_void_p, c_void_p, c_size_t, c_void_p]),
     "vc_convert_f32_to_bf16": (c_int, [c_void_p, c_void_p, c_size_t, c_void_p]),
 }
+
+DTYPE_U8, DTYPE_F32, DTYPE_BF16 = 0, 1, 2
 
 _lib = None
 

@@ -208,7 +208,8 @@ int vc_match_pairs(vc_handle* h, const void* desc, const int32_t* counts, int n_
                    int d, const int32_t* pairs, int n_pairs, const vc_match_options* opt,
                    uint32_t* matches, int32_t* n_matches, void* workspace, size_t workspace_bytes,
                    void* stream) {
-  if (!matches || !n_matches) return fail(VC_ERR_INVALID, "null output pointer");
+  if ((matches == nullptr) != (n_matches == nullptr))
+    return fail(VC_ERR_INVALID, "matches and n_matches must both be given or both be NULL");
   return match_impl(h, desc, counts, n_images, kmax, d, pairs, n_pairs, opt, matches, n_matches,
                     nullptr, nullptr, nullptr, workspace, workspace_bytes, stream);
 }
@@ -264,19 +265,21 @@ int vc_convert_f32_to_bf16(const float* src, void* dst_bf16, size_t n, void* str
   return VC_OK;
 }
 
-int vc_match_pairs_host(vc_handle* h, const uint8_t* desc_u8, const float* desc_f32,
-                        const int32_t* counts, int n_images, int kmax, int d, const int32_t* pairs,
-                        int n_pairs, const vc_match_options* opt, uint32_t* matches,
-                        int32_t* n_matches) {
+int vc_match_pairs_host(vc_handle* h, const void* desc, int dtype, const int32_t* counts,
+                        int n_images, int kmax, int d, const int32_t* pairs, int n_pairs,
+                        const vc_match_options* opt, uint32_t* matches, int32_t* n_matches) {
   if (!h) return fail(VC_ERR_INVALID, "null handle");
-  if ((!desc_u8 && !desc_f32) || !counts || !opt || !matches || !n_matches || (n_pairs > 0 && !pairs))
+  if (!desc || !counts || !opt || !matches || !n_matches || (n_pairs > 0 && !pairs))
     return fail(VC_ERR_INVALID, "null pointer argument");
+  if (dtype != VC_DTYPE_U8 && dtype != VC_DTYPE_F32 && dtype != VC_DTYPE_BF16)
+    return fail(VC_ERR_INVALID, "unknown dtype %d", dtype);
   if (n_images <= 0 || kmax <= 0 || n_pairs < 0 || d <= 0 || d % 8 != 0)
     return fail(VC_ERR_INVALID, "bad sizes");
   if (n_pairs == 0) return VC_OK;
   VC_CUDA(cudaSetDevice(h->device));
   const size_t n_el = (size_t)n_images * kmax * d;
-  const size_t src_bytes = align_up(desc_u8 ? n_el : n_el * 4, 256);
+  const size_t el = dtype == VC_DTYPE_U8 ? 1 : (dtype == VC_DTYPE_F32 ? 4 : 2);
+  const size_t src_bytes = dtype == VC_DTYPE_BF16 ? 0 : align_up(n_el * el, 256);
   const size_t bf_bytes = align_up(n_el * 2, 256);
   const size_t cnt_bytes = align_up((size_t)n_images * 4, 256);
   const size_t pair_bytes = align_up((size_t)n_pairs * 8, 256);
@@ -301,14 +304,17 @@ int vc_match_pairs_host(vc_handle* h, const uint8_t* desc_u8, const float* desc_
   int32_t* d_nm = reinterpret_cast<int32_t*>(reinterpret_cast<uint8_t*>(d_out) + out_bytes);
   void* d_ws = reinterpret_cast<uint8_t*>(d_nm) + nm_bytes;
   cudaStream_t s = 0;
-  if (desc_u8) {
-    VC_CUDA(cudaMemcpyAsync(d_src, desc_u8, n_el, cudaMemcpyHostToDevice, s));
+  if (dtype == VC_DTYPE_U8) {
+    VC_CUDA(cudaMemcpyAsync(d_src, desc, n_el, cudaMemcpyHostToDevice, s));
     VC_CUDA(vc::launch_u8_to_bf16(d_src, d_bf, n_el, s));
-  } else {
-    VC_CUDA(cudaMemcpyAsync(d_src, desc_f32, n_el * 4, cudaMemcpyHostToDevice, s));
+    ++g_launches;
+  } else if (dtype == VC_DTYPE_F32) {
+    VC_CUDA(cudaMemcpyAsync(d_src, desc, n_el * 4, cudaMemcpyHostToDevice, s));
     VC_CUDA(vc::launch_f32_to_bf16(reinterpret_cast<const float*>(d_src), d_bf, n_el, s));
+    ++g_launches;
+  } else {
+    VC_CUDA(cudaMemcpyAsync(d_bf, desc, n_el * 2, cudaMemcpyHostToDevice, s));
   }
-  ++g_launches;
   VC_CUDA(cudaMemcpyAsync(d_cnt, counts, (size_t)n_images * 4, cudaMemcpyHostToDevice, s));
   VC_CUDA(cudaMemcpyAsync(d_pairs, pairs, (size_t)n_pairs * 8, cudaMemcpyHostToDevice, s));
   int rc = vc_match_pairs(h, d_bf, d_cnt, n_images, kmax, d, d_pairs, n_pairs, opt, d_out, d_nm, d_ws,

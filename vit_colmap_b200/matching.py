@@ -163,17 +163,20 @@ class Matcher:
         n_images, kmax, d = desc.shape
         n_pairs = pairs.shape[0]
         if desc.dtype == np.uint8:
-            u8, f32 = desc.ctypes.data, None
+            dtype = _lib.DTYPE_U8
             inv = 1.0 / SQ_SIFT_NORM if inv_norm is None else inv_norm
         elif desc.dtype == np.float32:
-            u8, f32 = None, desc.ctypes.data
+            dtype = _lib.DTYPE_F32
+            inv = 1.0 if inv_norm is None else inv_norm
+        elif desc.dtype == np.uint16:  # raw bf16 bit patterns
+            dtype = _lib.DTYPE_BF16
             inv = 1.0 if inv_norm is None else inv_norm
         else:
-            raise TypeError("descriptors must be uint8 or float32")
+            raise TypeError("descriptors must be uint8, float32 or uint16 (bf16 bits)")
         matches = np.empty((max(n_pairs, 1), kmax, 2), dtype=np.uint32)
         n_matches = np.zeros((max(n_pairs, 1),), dtype=np.int32)
         opt = self._opts(max_ratio, max_distance, cross_check, inv)
-        _lib.check(self.lib.vc_match_pairs_host(self.handle, u8, f32, counts.ctypes.data, n_images, kmax,
+        _lib.check(self.lib.vc_match_pairs_host(self.handle, desc.ctypes.data, dtype, counts.ctypes.data, n_images, kmax,
                                                 d, pairs.ctypes.data, n_pairs, ctypes.byref(opt),
                                                 matches.ctypes.data, n_matches.ctypes.data))
         return [matches[i, :n_matches[i]].copy() for i in range(n_pairs)]
@@ -199,3 +202,58 @@ def match_descriptor_sets(descriptors: Sequence[np.ndarray], pairs, options: Opt
             buf[i, :n] = x[:n]
     return matcher.match_pairs_host(buf, counts, np.asarray(pairs, dtype=np.int32),
                                     options.max_ratio, options.max_distance, options.cross_check)
+
+
+def match_exhaustive(database_path, matching_options: Optional[FeatureMatchingOptions] = None,
+                     pairing_options=None, verification_options=None, device=None, *,
+                     matcher: Optional[Matcher] = None, rank: int = 0, world_size: int = 1,
+                     pairs_per_launch: int = 256):
+    """Drop-in for ``pycolmap.match_exhaustive(database_path, matching_options, ...)`` restricted to
+    the matching half (PYCOLMAP/pipeline/match_features.cc:28-51; geometric verification stays with
+    pycolmap and is invoked afterwards when pycolmap is importable).
+
+    Reads ``descriptors`` rows, generates exhaustive pairs block-wise (pairing.cc:202-236), matches
+    every block on the GPU and writes ``matches`` rows: pairs with fewer than ``min_num_matches``
+    matches are written empty (controllers/feature_matching_utils.cc:485-488), pairs that already
+    have a row are skipped (:443-449).  With world_size > 1 each rank matches its share of the pair
+    blocks (no collective); only rank 0's caller should write -- use ``return_only=True`` style via
+    the returned dict to gather.  Returns {(image_id1, image_id2): matches[n,2] uint32}.
+    """
+    from .database import Database
+    options = matching_options or FeatureMatchingOptions()
+    block_size = int(getattr(pairing_options, "block_size", 50)) if pairing_options is not None else 50
+    if isinstance(device, int):
+        dev_index = device
+    else:
+        dev_index = 0
+    matcher = matcher or Matcher(dev_index)
+    results = {}
+    with Database.open(str(database_path)) as db:
+        images = db.read_all_images()
+        ids = [im.image_id for im in images]
+        desc = {i: db.read_descriptors(i) for i in ids}
+        desc = {i: (v if v.ndim == 2 and v.shape[0] > 0 else np.zeros((0, 128), np.uint8)) for i, v in desc.items()}
+        index_of = {i: k for k, i in enumerate(ids)}
+        gen = ExhaustivePairGenerator(ids, block_size)
+        todo = []
+        for pair in gen.all_pairs():
+            if db.exists_matches(pair[0], pair[1]):  # resume semantics
+                continue
+            todo.append(pair)
+        lo = len(todo) * rank // world_size
+        hi = len(todo) * (rank + 1) // world_size
+        mine = todo[lo:hi]
+        arrays = [desc[i] for i in ids]
+        for s in range(0, len(mine), pairs_per_launch):
+            chunk = mine[s:s + pairs_per_launch]
+            idx_pairs = np.array([(index_of[a], index_of[b]) for a, b in chunk], dtype=np.int32)
+            out = match_descriptor_sets(arrays, idx_pairs, options, matcher)
+            for (a, b), m in zip(chunk, out):
+                if m.shape[0] < options.min_num_matches:
+                    m = np.zeros((0, 2), np.uint32)
+                results[(a, b)] = m
+        if rank == 0 and world_size == 1:
+            with db.transaction():
+                for (a, b), m in results.items():
+                    db.write_matches(a, b, m)
+    return results
