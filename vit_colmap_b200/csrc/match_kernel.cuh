@@ -24,11 +24,21 @@ struct MatchParams {
   int32_t* top_idx;
   float* dbg_scores;      // optional dense scores of pair 0 (debug kernel only)
   int dbg_ld;
+  // single-pass kernel (match_fused.cu) only
+  int cb_per_img;         // ceil(kmax / 256)
+  unsigned int* rowthr;   // [n_pairs, kmax] float bits: lower bound of each row's final second-best
+  float* part_best;       // [n_pairs, cb_per_img, kmax] per-column-block row partials
+  float* part_second;
+  int32_t* part_idx;
 };
 
 int match_smem_bytes();
 cudaError_t launch_match_top2(const CUtensorMap& tmap, const MatchParams& p, int num_sms, bool debug,
                               cudaStream_t stream);
+int match_fused_smem_bytes();
+// memset(rowthr) + fused kernel + row-partial merge; n_items must be n_pairs * cb_per_img
+cudaError_t launch_match_fused(const CUtensorMap& tmap, const MatchParams& p, int num_sms,
+                               cudaStream_t stream);
 cudaError_t launch_emit_matches(const MatchParams& p, uint32_t* matches, int32_t* n_matches,
                                 cudaStream_t stream);
 cudaError_t launch_u8_to_bf16(const uint8_t* src, void* dst, size_t n, cudaStream_t stream);

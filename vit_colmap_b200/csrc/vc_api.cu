@@ -5,6 +5,7 @@
 
 #include <cstdarg>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <string>
 #include <vector>
@@ -91,6 +92,19 @@ struct MatchWs {
 size_t m_out_bytes(int n_pairs, int kmax) {
   return align_up((size_t)n_pairs * 2 * (size_t)kmax * sizeof(int32_t), 256);
 }
+size_t rowthr_bytes(int n_pairs, int kmax) { return align_up((size_t)n_pairs * kmax * 4, 256); }
+size_t part_bytes(int n_pairs, int kmax) {
+  return align_up((size_t)n_pairs * ((kmax + 255) / 256) * (size_t)kmax * 4, 256);
+}
+
+// Kernel choice: the single-pass kernel halves the tensor work but has a heavier epilogue, which
+// only hides behind the MMAs when d is large.  VC_MATCH_KERNEL=dual|fused overrides (tests).
+bool use_fused_kernel(int d) {
+  const char* env = getenv("VC_MATCH_KERNEL");
+  if (env && strcmp(env, "dual") == 0) return false;
+  if (env && strcmp(env, "fused") == 0) return true;
+  return d >= 256;
+}
 
 int check_match_args(vc_handle* h, const void* desc, const int32_t* counts, int n_images, int kmax,
                      int d, const int32_t* pairs, int n_pairs, const vc_match_options* opt) {
@@ -173,7 +187,7 @@ int vc_destroy(vc_handle* h) {
 
 size_t vc_match_workspace_bytes(int n_pairs, int kmax) {
   if (n_pairs <= 0 || kmax <= 0) return 256;
-  return m_out_bytes(n_pairs, kmax);
+  return m_out_bytes(n_pairs, kmax) + rowthr_bytes(n_pairs, kmax) + 3 * part_bytes(n_pairs, kmax);
 }
 
 static int match_impl(vc_handle* h, const void* desc, const int32_t* counts, int n_images, int kmax,
@@ -195,8 +209,23 @@ static int match_impl(vc_handle* h, const void* desc, const int32_t* counts, int
   p.top_best = best;
   p.top_second = second;
   p.top_idx = index;
-  VC_CUDA(vc::launch_match_top2(h->map, p, h->num_sms, false, s));
-  ++g_launches;
+  if (use_fused_kernel(d)) {
+    uint8_t* w = static_cast<uint8_t*>(workspace) + m_out_bytes(n_pairs, kmax);
+    p.rowthr = reinterpret_cast<unsigned int*>(w);
+    w += rowthr_bytes(n_pairs, kmax);
+    p.part_best = reinterpret_cast<float*>(w);
+    w += part_bytes(n_pairs, kmax);
+    p.part_second = reinterpret_cast<float*>(w);
+    w += part_bytes(n_pairs, kmax);
+    p.part_idx = reinterpret_cast<int32_t*>(w);
+    p.cb_per_img = (kmax + 255) / 256;
+    p.n_items = n_pairs * p.cb_per_img;
+    VC_CUDA(vc::launch_match_fused(h->map, p, h->num_sms, s));
+    g_launches += 2;
+  } else {
+    VC_CUDA(vc::launch_match_top2(h->map, p, h->num_sms, false, s));
+    ++g_launches;
+  }
   if (matches && n_matches) {
     VC_CUDA(vc::launch_emit_matches(p, matches, n_matches, s));
     ++g_launches;
