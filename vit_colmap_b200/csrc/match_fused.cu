@@ -27,7 +27,7 @@ namespace {
 
 constexpr int BM = 128, BN = 256, BK = 64, kStages = 4;
 constexpr int kABytes = BM * BK * 2, kBBytes = BN * BK * 2, kStageBytes = kABytes + kBBytes;
-constexpr int kThreads = 256;
+constexpr int kThreads = 384;  // warp0 TMA, warp1 MMA, warp2 TMEM alloc, warps 4-11 epilogue
 constexpr int kTmemCols = 512;
 constexpr int kColStateBytes = BN * 8 + BN * 4;
 constexpr int kSmemBytes = kStages * kStageBytes + 1024 + 256 + kColStateBytes;
@@ -63,7 +63,7 @@ __device__ __forceinline__ int accept_top2f(float best, float second, int idx, f
   return idx;
 }
 
-__device__ __forceinline__ void epi_bar_sync() { asm volatile("bar.sync 1, 128;" ::: "memory"); }
+__device__ __forceinline__ void epi_bar_sync() { asm volatile("bar.sync 1, 256;" ::: "memory"); }
 
 }  // namespace
 
@@ -97,7 +97,7 @@ match_fused_kernel(const __grid_constant__ CUtensorMap tmap, const MatchParams p
     }
     for (int s = 0; s < 2; ++s) {
       mbar_init(tfull_bar(s), 1);
-      mbar_init(tempty_bar(s), 128);
+      mbar_init(tempty_bar(s), 256);
     }
     fence_mbar_init();
   }
@@ -163,30 +163,32 @@ match_fused_kernel(const __grid_constant__ CUtensorMap tmap, const MatchParams p
       }
     }
   } else if (warp >= 4) {
-    // ------------------------------------------------------------ epilogue
-    const int q = warp - 4;
-    const int et = threadIdx.x - 128;  // 0..127
+    // ------------------------------------------------------------ epilogue (8 warps)
+    // warp -> TMEM lane quarter q = warp % 4 (hardware rule) and column half h of the tile
+    const int q = warp & 3;
+    const int h = (warp - 4) >> 2;
+    const int et = threadIdx.x - 128;  // 0..255
     uint32_t tile = 0;
     for (int item = blockIdx.x; item < p.n_items; item += gridDim.x) {
       const FItem it = decode_fitem(p, item);
       if (!it.valid) continue;
       colkey[et] = 0ull;
-      colkey[et + 128] = 0ull;
       colsec[et] = 0u;
-      colsec[et + 128] = 0u;
       epi_bar_sync();
       const int ncols = min(BN, it.n2 - it.cb * BN);  // valid columns of this block
-      const int nchunks = (ncols + 31) >> 5;
+      // this warp's chunks: columns [h*128, h*128+128) of the block, 32 per chunk
+      const int c_begin = h * 4;
+      const int c_end = min(c_begin + 4, (ncols + 31) >> 5);
       const size_t pair_row0 = (size_t)it.pair * p.kmax;
       for (int s = 0; s < it.nrt; ++s, ++tile) {
         int rt = it.start + s;
         if (rt >= it.nrt) rt -= it.nrt;
-        const int warp_row0 = rt * BM + q * 32;
-        const int row = warp_row0 + lane;
+        const int row = rt * BM + q * 32 + lane;
         const bool row_ok = row < it.n1;
         // hint: lower bound of this row's final second-best (L2 load, may be stale)
         float thr = 0.f;
         if (row_ok) thr = __uint_as_float(__ldcg(p.rowthr + pair_row0 + row));
+        const unsigned long long row_tag = 0xFFFFFFFFu - (unsigned)row;
         float best = 0.f, second = 0.f;
         int bidx = -1;
         const uint32_t as = tile & 1, aph = (tile >> 1) & 1;
@@ -194,7 +196,7 @@ match_fused_kernel(const __grid_constant__ CUtensorMap tmap, const MatchParams p
         tc_fence_after();
         const uint32_t t_addr = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + as * BN;
 #pragma unroll 1
-        for (int c = 0; c < nchunks; ++c) {
+        for (int c = c_begin; c < c_end; ++c) {
           uint32_t vr[32];
           tmem_ld_32x32(t_addr + c * 32, vr);
           tmem_wait_ld();
@@ -210,49 +212,64 @@ match_fused_kernel(const __grid_constant__ CUtensorMap tmap, const MatchParams p
             for (int e = 0; e < 32; ++e)
               if (c * 32 + e >= ncols) v[e] = 0.f;
           }
-          // ---- columns: touch shared state only where a score beats the current second-best
+          // ---- columns: per-lane mask of scores that beat the column's current second-best
           const uint4* thr4 = reinterpret_cast<const uint4*>(colsec + c * 32);
+          unsigned cm = 0;
 #pragma unroll
           for (int g = 0; g < 8; ++g) {
             const uint4 t4 = thr4[g];
-            const uint32_t tw[4] = {t4.x, t4.y, t4.z, t4.w};
-#pragma unroll
-            for (int e = 0; e < 4; ++e) {
-              const float x = v[4 * g + e];
-              if (__any_sync(0xffffffffu, x > __uint_as_float(tw[e]))) {
-                const unsigned xb = __float_as_uint(fmaxf(x, 0.f));
-                const unsigned m = __reduce_max_sync(0xffffffffu, xb);
-                const unsigned bal = __ballot_sync(0xffffffffu, xb == m);
-                const int l1 = __ffs(bal) - 1;  // lowest row wins ties
-                const unsigned m2 = __reduce_max_sync(0xffffffffu, lane == l1 ? 0u : xb);
-                if (lane == 0) {
-                  const int jl = c * 32 + 4 * g + e;
-                  const unsigned long long key =
-                      ((unsigned long long)m << 32) | (0xFFFFFFFFu - (unsigned)(warp_row0 + l1));
-                  const unsigned long long old = atomicMax(colkey + jl, key);
-                  const unsigned cand = key > old ? max(m2, (unsigned)(old >> 32)) : m;
-                  atomicMax(colsec + jl, cand);
-                }
-              }
-            }
+            cm |= (v[4 * g + 0] > __uint_as_float(t4.x)) ? (1u << (4 * g + 0)) : 0u;
+            cm |= (v[4 * g + 1] > __uint_as_float(t4.y)) ? (1u << (4 * g + 1)) : 0u;
+            cm |= (v[4 * g + 2] > __uint_as_float(t4.z)) ? (1u << (4 * g + 2)) : 0u;
+            cm |= (v[4 * g + 3] > __uint_as_float(t4.w)) ? (1u << (4 * g + 3)) : 0u;
           }
-          // ---- rows: per-thread running top-2 over this tile's 256 columns
-          const int colbase = it.cb * BN + c * 32;
+          // ---- rows: group maxima decide whether the running top-2 can change
+          float gm[4];
 #pragma unroll
           for (int g = 0; g < 4; ++g) {
             float m = v[8 * g];
 #pragma unroll
             for (int e = 1; e < 8; ++e) m = fmaxf(m, v[8 * g + e]);
-            if (__any_sync(0xffffffffu, m > second && m >= thr)) {
+            gm[g] = m;
+          }
+          const float cmax = fmaxf(fmaxf(gm[0], gm[1]), fmaxf(gm[2], gm[3]));
+          const unsigned any_col = __reduce_or_sync(0xffffffffu, cm);
+          const bool any_row = __any_sync(0xffffffffu, cmax > second && cmax >= thr);
+          if (any_col) {
 #pragma unroll
-              for (int e = 0; e < 8; ++e) {
-                const float sc = v[8 * g + e];
-                if (sc > best) {
-                  second = best;
-                  best = sc;
-                  bidx = colbase + 8 * g + e;
-                } else if (sc > second) {
-                  second = sc;
+            for (int g = 0; g < 8; ++g) {
+              if (any_col & (0xFu << (4 * g))) {  // warp-uniform
+#pragma unroll
+                for (int e = 0; e < 4; ++e) {
+                  if (cm & (1u << (4 * g + e))) {
+                    // every score above the threshold is merged: the key keeps the best score
+                    // and, on ties, the lowest row; each loser's score feeds the second-best
+                    const int jl = c * 32 + 4 * g + e;
+                    const unsigned xb = __float_as_uint(v[4 * g + e]);
+                    const unsigned long long key = ((unsigned long long)xb << 32) | row_tag;
+                    const unsigned long long old = atomicMax(colkey + jl, key);
+                    const unsigned cand = key > old ? (unsigned)(old >> 32) : xb;
+                    atomicMax(colsec + jl, cand);
+                  }
+                }
+              }
+            }
+          }
+          if (any_row) {
+            const int colbase = it.cb * BN + c * 32;
+#pragma unroll
+            for (int g = 0; g < 4; ++g) {
+              if (gm[g] > second && gm[g] >= thr) {
+#pragma unroll
+                for (int e = 0; e < 8; ++e) {
+                  const float sc = v[8 * g + e];
+                  if (sc > best) {
+                    second = best;
+                    best = sc;
+                    bidx = colbase + 8 * g + e;
+                  } else if (sc > second) {
+                    second = sc;
+                  }
                 }
               }
             }
@@ -261,7 +278,7 @@ match_fused_kernel(const __grid_constant__ CUtensorMap tmap, const MatchParams p
         tc_fence_before();
         mbar_arrive(tempty_bar(as));
         if (row_ok) {
-          const size_t o = ((size_t)it.pair * p.cb_per_img + it.cb) * p.kmax + row;
+          const size_t o = ((size_t)it.pair * p.cb_per_img * 2 + it.cb * 2 + h) * p.kmax + row;
           p.part_best[o] = best;
           p.part_second[o] = second;
           p.part_idx[o] = bidx;
@@ -270,21 +287,17 @@ match_fused_kernel(const __grid_constant__ CUtensorMap tmap, const MatchParams p
       }
       // ---- column block finished: every row of image 1 has been seen
       epi_bar_sync();
-#pragma unroll
-      for (int h = 0; h < 2; ++h) {
-        const int jl = et + 128 * h;
-        if (jl < ncols) {
-          const unsigned long long key = colkey[jl];
-          const float cbest = __uint_as_float((unsigned)(key >> 32));
-          const float csec = __uint_as_float(colsec[jl]);
-          const int cidx = key ? (int)(0xFFFFFFFFu - (unsigned)(key & 0xFFFFFFFFull)) : -1;
-          const size_t o = ((size_t)it.pair * 2 + 1) * p.kmax + it.cb * BN + jl;
-          p.m_out[o] = accept_top2f(cbest, csec, cidx, p.inv_norm, p.max_ratio, p.max_distance);
-          if (p.top_best != nullptr) {
-            p.top_best[o] = cbest;
-            p.top_second[o] = csec;
-            p.top_idx[o] = cidx;
-          }
+      if (et < ncols) {
+        const unsigned long long key = colkey[et];
+        const float cbest = __uint_as_float((unsigned)(key >> 32));
+        const float csec = __uint_as_float(colsec[et]);
+        const int cidx = key ? (int)(0xFFFFFFFFu - (unsigned)(key & 0xFFFFFFFFull)) : -1;
+        const size_t o = ((size_t)it.pair * 2 + 1) * p.kmax + it.cb * BN + et;
+        p.m_out[o] = accept_top2f(cbest, csec, cidx, p.inv_norm, p.max_ratio, p.max_distance);
+        if (p.top_best != nullptr) {
+          p.top_best[o] = cbest;
+          p.top_second[o] = csec;
+          p.top_idx[o] = cidx;
         }
       }
       epi_bar_sync();  // state is re-initialised at the top of the next item
@@ -304,11 +317,11 @@ __global__ void merge_rows_kernel(const MatchParams p) {
   const int i0 = p.pairs[2 * pair], i1 = p.pairs[2 * pair + 1];
   const int n1 = min(p.counts[i0], p.kmax), n2 = min(p.counts[i1], p.kmax);
   if (row >= n1) return;
-  const int ncb = (n2 + BN - 1) / BN;
+  const int nparts = (n2 + 127) / 128;  // one partial per 128 columns (epilogue warp half)
   float best = 0.f, second = 0.f;
   int idx = -1;
-  for (int cb = 0; cb < ncb; ++cb) {
-    const size_t o = ((size_t)pair * p.cb_per_img + cb) * p.kmax + row;
+  for (int cb = 0; cb < nparts; ++cb) {
+    const size_t o = ((size_t)pair * p.cb_per_img * 2 + cb) * p.kmax + row;
     const float pb = p.part_best[o], ps = p.part_second[o];
     const int pi = p.part_idx[o];
     if (pi < 0) continue;

@@ -27,7 +27,7 @@ struct MatchParams {
   // single-pass kernel (match_fused.cu) only
   int cb_per_img;         // ceil(kmax / 256)
   unsigned int* rowthr;   // [n_pairs, kmax] float bits: lower bound of each row's final second-best
-  float* part_best;       // [n_pairs, cb_per_img, kmax] per-column-block row partials
+  float* part_best;       // [n_pairs, 2*cb_per_img, kmax] row partials, one per 128 columns
   float* part_second;
   int32_t* part_idx;
 };

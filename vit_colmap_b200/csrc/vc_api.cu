@@ -94,7 +94,7 @@ size_t m_out_bytes(int n_pairs, int kmax) {
 }
 size_t rowthr_bytes(int n_pairs, int kmax) { return align_up((size_t)n_pairs * kmax * 4, 256); }
 size_t part_bytes(int n_pairs, int kmax) {
-  return align_up((size_t)n_pairs * ((kmax + 255) / 256) * (size_t)kmax * 4, 256);
+  return align_up((size_t)n_pairs * 2 * ((kmax + 255) / 256) * (size_t)kmax * 4, 256);
 }
 
 // Kernel choice: the single-pass kernel halves the tensor work but has a heavier epilogue, which
