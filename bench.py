@@ -27,6 +27,8 @@ METRIC = "matched_pairs_per_sec@8192kpts_d768"
 UNIT = "pairs/s"
 N_IMAGES, KPTS, DIM = 32, 8192, 768
 FLOP_PER_PAIR = 2.0 * KPTS * KPTS * DIM  # 2*N*M*d
+# dram__bytes_read.sum + dram__bytes_write.sum of one match_fused_kernel launch (496 pairs), ncu --set full
+NCU_TRAFFIC_BYTES = 8.593394e9 + 3.149852e9
 
 
 def _peaks():
@@ -298,10 +300,12 @@ def run_ours(args):
                        "l2": "inputs 403 MB > 126 MB L2", "mean_matches_per_pair": float(n_matches.float().mean().item())},
             "e2e": e2e, "gpu_launches": int(launches),
             "roofline": {"bound": "tensor", "achieved": achieved_tf, "peak": peak_tf, "unit": "TFLOP/s",
-                         "frac": achieved_tf / peak_tf, "traffic": None, "peak_source": f"{peak_src} sustained bf16",
-                         "kernel": "match_top2_kernel", "kernel_ms": kern_ms,
-                         "note": "achieved counts 2*N*M*d per pair once; the kernel currently runs the MMA "
-                                 "twice (rows and columns as separate directions)"},
+                         "frac": achieved_tf / peak_tf, "traffic": NCU_TRAFFIC_BYTES,
+                         "peak_source": f"{peak_src} sustained bf16",
+                         "kernel": "match_fused_kernel", "kernel_ms": kern_ms,
+                         "note": "achieved = 2*N*M*d per pair (one MMA sweep gives row and column top-2) "
+                                 "over the top-2 stage (memset + fused kernel + row-partial merge); traffic "
+                                 "from profiles/r01_v2_fused_ncu_summary.json (dram read+write per launch)"},
             "clocks": clocks,
         }
         if allgather_ms is not None:
