@@ -110,6 +110,65 @@ int vc_match_pairs_host(vc_handle* h, const void* desc, int dtype, const int32_t
 int vc_convert_u8_to_bf16(const uint8_t* src, void* dst_bf16, size_t n, void* stream);
 int vc_convert_f32_to_bf16(const float* src, void* dst_bf16, size_t n, void* stream);
 
+/* ------------------------------------------------------------------------------------------
+ * Extraction post-processing (vit_colmap/features/vit_extractor.py ViTExtractor._dense_to_sparse
+ * :168-252).  All buffers are device memory; every call is batched over n_images feature maps of
+ * one patch grid (grid_h x grid_w <= 16384 cells, channels <= 1024 and a multiple of 4).
+ * `tokens` is the backbone output in its native token-major layout [n_images, grid_h*grid_w,
+ * channels] (x_norm_patchtokens, vit_extractor.py:135-146), f32 or bf16, image_stride elements
+ * apart; the NCHW view of vit_extractor.py:150-156 is never materialised.
+ * ------------------------------------------------------------------------------------------ */
+
+/* Detection methods of ViTExtractor(detection_method=...), vit_extractor.py:254-279. */
+typedef enum { VC_DETECT_HARRIS = 0, VC_DETECT_DOG = 1, VC_DETECT_COMBINED = 2 } vc_detect_method;
+
+size_t vc_score_workspace_bytes(int n_images, int grid_h, int grid_w);
+
+/* Distinctiveness map.  score: f32 [n_images, grid_h, grid_w], min-max normalised per image.
+ * Replaces: _compute_distinctiveness / _harris_response / _dog_response,
+ * vit_extractor.py:254-394 (forward-difference structure tensor averaged over channels, 3x3
+ * Gaussian, 0.7*(det - 0.04 tr^2) + 0.3*sqrt(tr); |G7 - G11| of the channel mean). */
+int vc_score_map(vc_handle* h, const void* tokens, int dtype, int n_images, int grid_h, int grid_w,
+                 int channels, int64_t image_stride, int method, float* score, void* workspace,
+                 size_t workspace_bytes, void* stream);
+
+/* Keypoint selection.  coords: int32 [n_images, capacity, 2] as (y, x) grid cells, scores: f32
+ * [n_images, capacity], counts: int32 [n_images]; rows come out in descending score order, ties
+ * by the reference's concatenation order.  capacity >= min(num_keypoints, grid cells).
+ * Replaces: _spatial_binning_selection (bin_size 16, per-bin topk, global topk)
+ * vit_extractor.py:404-485 and the greedy _apply_nms (radius 1.5) :500-543. */
+int vc_select_keypoints(vc_handle* h, const float* score, int n_images, int grid_h, int grid_w,
+                        int num_keypoints, int bin_size, float nms_radius, int32_t* coords,
+                        float* scores, int32_t* counts, int capacity, void* stream);
+
+/* Descriptor quantisation rules of the byte blob written to the database. */
+typedef enum {
+  VC_QUANT_VIT = 0,       /* trunc(clip(512 v, 0, 255)), vit_extractor.py:250 */
+  VC_QUANT_COLMAP = 1,    /* min(255, round(512 v)), COLMAP/feature/utils.cc:56-71 */
+  VC_QUANT_TRAINABLE = 2  /* trunc(clip((v + 1) * 127.5, 0, 255)), trainable_vit_extractor.py:265-267 */
+} vc_quant_mode;
+
+/* Sample, (project,) L2-normalise and pack descriptors at the selected keypoints.
+ *   coords      : [n_images, capacity, 2] (y, x); int32 grid cells, or float32 grid units when
+ *                 coords_are_float != 0 (bilinear between cells, border clamp)
+ *   projection  : f32 [channels, d] applied before normalisation (PCA of
+ *                 vit_extractor.py:588-653, fitted by the caller), or NULL with d == channels
+ *   kp_scale    : host float[4] = {w_res/W, w_orig/w_res, h_res/H, h_orig/h_res} so that
+ *                 x = (col + 0.5) * kp_scale[0] * kp_scale[1] (vit_extractor.py:229-236)
+ *   keypoints   : f32 [n_images, capacity, 2] (x, y) pixel coordinates           (may be NULL)
+ *   desc_bf16   : bf16 [n_images, capacity, d], unit rows = matcher input         (may be NULL)
+ *   desc_u8     : uint8 [n_images, capacity, d], database blob rows              (may be NULL)
+ *   desc_f32    : f32 [n_images, capacity, d], unit rows                         (may be NULL)
+ * Rows >= counts[i] are left untouched.
+ * Replaces: _extract_descriptors_interp (F.grid_sample bilinear/border/align_corners=True)
+ * vit_extractor.py:545-586, the projection apply :651, F.normalize :243 and the uint8
+ * conversion :246-250. */
+int vc_sample_pack(vc_handle* h, const void* tokens, int dtype, int n_images, int grid_h, int grid_w,
+                   int channels, int64_t image_stride, const void* coords, int coords_are_float,
+                   const int32_t* counts, int capacity, const float* projection, int d, int quant_mode,
+                   const float* kp_scale, float* keypoints, void* desc_bf16, uint8_t* desc_u8,
+                   float* desc_f32, void* stream);
+
 /* Number of kernels launched by this library on the calling thread since the last reset
  * (bench.py reports it as gpu_launches). */
 int64_t vc_launch_count(int reset);

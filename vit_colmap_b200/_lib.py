@@ -44,6 +44,14 @@ SIGNATURES = {
                                     c_void_p, c_int, POINTER(MatchOptions), c_void_p, c_void_p]),
     "vc_convert_u8_to_bf16": (c_int, [c_void_p, c_void_p, c_size_t, c_void_p]),
     "vc_convert_f32_to_bf16": (c_int, [c_void_p, c_void_p, c_size_t, c_void_p]),
+    "vc_score_workspace_bytes": (c_size_t, [c_int, c_int, c_int]),
+    "vc_score_map": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_int, c_int64, c_int,
+                             c_void_p, c_void_p, c_size_t, c_void_p]),
+    "vc_select_keypoints": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_int, c_float,
+                                    c_void_p, c_void_p, c_void_p, c_int, c_void_p]),
+    "vc_sample_pack": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_int, c_int64,
+                               c_void_p, c_int, c_void_p, c_int, c_void_p, c_int, c_int,
+                               POINTER(c_float), c_void_p, c_void_p, c_void_p, c_void_p, c_void_p]),
 }
 
 DTYPE_U8, DTYPE_F32, DTYPE_BF16 = 0, 1, 2

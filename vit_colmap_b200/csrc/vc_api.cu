@@ -12,8 +12,9 @@
 
 #include "match_kernel.cuh"
 
-namespace {
+#include "vc_internal.cuh"
 
+namespace vc {
 thread_local std::string g_err;
 thread_local int64_t g_launches = 0;
 
@@ -26,36 +27,13 @@ int fail(int code, const char* fmt, ...) {
   g_err = buf;
   return code;
 }
+void add_launches(int n) { g_launches += n; }
+}  // namespace vc
 
-#define VC_CUDA(expr)                                                                         \
-  do {                                                                                        \
-    cudaError_t _e = (expr);                                                                  \
-    if (_e != cudaSuccess)                                                                    \
-      return fail(VC_ERR_CUDA, "%s failed: %s (%s:%d)", #expr, cudaGetErrorString(_e), __FILE__, \
-                  __LINE__);                                                                  \
-  } while (0)
-
-using EncodeTiledFn = CUresult (*)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*,
-                                   const cuuint64_t*, const cuuint64_t*, const cuuint32_t*,
-                                   const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
-                                   CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
-
-size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
-
-}  // namespace
-
-struct vc_handle {
-  int device = 0;
-  int num_sms = 0;
-  EncodeTiledFn encode = nullptr;
-  // cached descriptor for the last (ptr, n_images, kmax, d)
-  const void* map_ptr = nullptr;
-  int map_n = 0, map_k = 0, map_d = 0;
-  CUtensorMap map;
-  // device staging owned by the host-buffer entry point
-  void* stage = nullptr;
-  size_t stage_bytes = 0;
-};
+using vc::fail;
+using vc::g_launches;
+using vc::g_err;
+using vc::align_up;
 
 namespace {
 
@@ -171,7 +149,7 @@ int vc_create(int device, vc_handle** out) {
     delete h;
     return fail(VC_ERR_CUDA, "cuTensorMapEncodeTiled entry point unavailable");
   }
-  h->encode = reinterpret_cast<EncodeTiledFn>(fn);
+  h->encode = reinterpret_cast<vc::EncodeTiledFn>(fn);
   *out = h;
   return VC_OK;
 }

@@ -1,0 +1,170 @@
+// C ABI, extraction post-processing half (see include/vc_b200.h): argument checks and launches
+// for the score map, keypoint selection and descriptor sampling / packing kernels.
+#include <cmath>
+
+#include "extract_kernels.cuh"
+#include "vc_internal.cuh"
+
+using vc::fail;
+
+namespace {
+
+// 1-D taps of vit_extractor.py:396-402: exp(-x^2 / (2 sigma^2)) normalised to sum 1, in fp32
+void gaussian_taps(int k, float sigma, float* out) {
+  float sum = 0.f;
+  for (int i = 0; i < k; ++i) {
+    const float x = (float)(i - k / 2);
+    out[i] = expf(-(x * x) / (2.0f * sigma * sigma));
+    sum += out[i];
+  }
+  for (int i = 0; i < k; ++i) out[i] /= sum;
+}
+
+int check_grid(vc_handle* h, int B, int H, int W) {
+  if (!h) return fail(VC_ERR_INVALID, "null handle");
+  if (B <= 0 || H <= 0 || W <= 0) return fail(VC_ERR_INVALID, "bad sizes B=%d H=%d W=%d", B, H, W);
+  if ((long long)H * W > vc::kMaxGridCells)
+    return fail(VC_ERR_INVALID, "patch grid %dx%d exceeds %d cells", H, W, vc::kMaxGridCells);
+  return VC_OK;
+}
+
+int check_tokens(const void* tokens, int dtype, int C) {
+  if (!tokens) return fail(VC_ERR_INVALID, "null tokens");
+  if (dtype != VC_DTYPE_F32 && dtype != VC_DTYPE_BF16)
+    return fail(VC_ERR_INVALID, "tokens must be f32 or bf16");
+  if (C <= 0 || C % 4 != 0 || C > vc::kMaxChannels)
+    return fail(VC_ERR_INVALID, "C=%d must be a multiple of 4 and <= %d", C, vc::kMaxChannels);
+  if ((reinterpret_cast<uintptr_t>(tokens) & 15) != 0)
+    return fail(VC_ERR_INVALID, "tokens must be 16-byte aligned");
+  return VC_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+size_t vc_score_workspace_bytes(int n_images, int grid_h, int grid_w) {
+  if (n_images <= 0 || grid_h <= 0 || grid_w <= 0) return 256;
+  return vc::align_up((size_t)n_images * 5 * grid_h * grid_w * sizeof(float), 256);
+}
+
+int vc_score_map(vc_handle* h, const void* tokens, int dtype, int n_images, int grid_h, int grid_w,
+                 int channels, int64_t image_stride, int method, float* score, void* workspace,
+                 size_t workspace_bytes, void* stream) {
+  int rc = check_grid(h, n_images, grid_h, grid_w);
+  if (rc != VC_OK) return rc;
+  rc = check_tokens(tokens, dtype, channels);
+  if (rc != VC_OK) return rc;
+  if (!score || !workspace) return fail(VC_ERR_INVALID, "null output / workspace");
+  if (method < 0 || method > 2) return fail(VC_ERR_INVALID, "unknown detection method %d", method);
+  if (workspace_bytes < vc_score_workspace_bytes(n_images, grid_h, grid_w))
+    return fail(VC_ERR_WORKSPACE, "workspace %zu B < required %zu B", workspace_bytes,
+                vc_score_workspace_bytes(n_images, grid_h, grid_w));
+  const int el = dtype == VC_DTYPE_F32 ? 4 : 2;
+  if (image_stride < (int64_t)grid_h * grid_w * channels || (image_stride * el) % 16 != 0)
+    return fail(VC_ERR_INVALID, "bad image_stride");
+  VC_CUDA(cudaSetDevice(h->device));
+  vc::ScoreParams p{};
+  p.tokens = tokens;
+  p.is_bf16 = dtype == VC_DTYPE_BF16;
+  p.image_stride = image_stride;
+  p.B = n_images;
+  p.H = grid_h;
+  p.W = grid_w;
+  p.C = channels;
+  p.method = method;
+  p.moments = static_cast<float*>(workspace);
+  p.scratch = p.moments + (size_t)n_images * 4 * grid_h * grid_w;
+  p.score = score;
+  gaussian_taps(3, 1.0f, p.g3);
+  gaussian_taps(7, 1.0f, p.g7);
+  gaussian_taps(11, 1.6f, p.g11);
+  VC_CUDA(vc::launch_score_map(p, reinterpret_cast<cudaStream_t>(stream)));
+  vc::add_launches(2);
+  return VC_OK;
+}
+
+int vc_select_keypoints(vc_handle* h, const float* score, int n_images, int grid_h, int grid_w,
+                        int num_keypoints, int bin_size, float nms_radius, int32_t* coords,
+                        float* scores, int32_t* counts, int capacity, void* stream) {
+  int rc = check_grid(h, n_images, grid_h, grid_w);
+  if (rc != VC_OK) return rc;
+  if (!score || !coords || !scores || !counts) return fail(VC_ERR_INVALID, "null pointer argument");
+  if (num_keypoints <= 0 || bin_size <= 0 || !(nms_radius >= 0.f) || nms_radius > 8.f)
+    return fail(VC_ERR_INVALID, "bad selection parameters");
+  const int most = std::min(num_keypoints, grid_h * grid_w);
+  if (capacity < most)
+    return fail(VC_ERR_INVALID, "capacity %d < min(num_keypoints, grid cells) = %d", capacity, most);
+  if (vc::select_smem_bytes(grid_h, grid_w, num_keypoints, bin_size) > 227 * 1024)
+    return fail(VC_ERR_INVALID, "selection state does not fit in shared memory");
+  VC_CUDA(cudaSetDevice(h->device));
+  vc::SelectParams p{};
+  p.score = score;
+  p.B = n_images;
+  p.H = grid_h;
+  p.W = grid_w;
+  p.num_keypoints = num_keypoints;
+  p.bin_size = bin_size;
+  p.nms_radius = nms_radius;
+  p.cap = capacity;
+  p.coords = coords;
+  p.scores = scores;
+  p.counts = counts;
+  VC_CUDA(vc::launch_select_keypoints(p, reinterpret_cast<cudaStream_t>(stream)));
+  vc::add_launches(1);
+  return VC_OK;
+}
+
+int vc_sample_pack(vc_handle* h, const void* tokens, int dtype, int n_images, int grid_h, int grid_w,
+                   int channels, int64_t image_stride, const void* coords, int coords_are_float,
+                   const int32_t* counts, int capacity, const float* projection, int d, int quant_mode,
+                   const float* kp_scale, float* keypoints, void* desc_bf16, uint8_t* desc_u8,
+                   float* desc_f32, void* stream) {
+  int rc = check_grid(h, n_images, grid_h, grid_w);
+  if (rc != VC_OK) return rc;
+  rc = check_tokens(tokens, dtype, channels);
+  if (rc != VC_OK) return rc;
+  if (!coords || !counts) return fail(VC_ERR_INVALID, "null coords / counts");
+  if (capacity <= 0) return fail(VC_ERR_INVALID, "bad capacity");
+  if (projection == nullptr && d != channels)
+    return fail(VC_ERR_INVALID, "d=%d must equal C=%d when no projection is given", d, channels);
+  if (d <= 0 || d % 4 != 0 || d > vc::kMaxChannels) return fail(VC_ERR_INVALID, "bad d=%d", d);
+  if (quant_mode < 0 || quant_mode > 2) return fail(VC_ERR_INVALID, "bad quant_mode");
+  if (keypoints && !kp_scale) return fail(VC_ERR_INVALID, "keypoints requested without kp_scale");
+  const int el = dtype == VC_DTYPE_F32 ? 4 : 2;
+  if (image_stride < (int64_t)grid_h * grid_w * channels || (image_stride * el) % 16 != 0)
+    return fail(VC_ERR_INVALID, "bad image_stride");
+  if (projection && (size_t)(channels * 16 + 16 * d) * 4 > 227 * 1024)
+    return fail(VC_ERR_INVALID, "projection tile does not fit in shared memory");
+  VC_CUDA(cudaSetDevice(h->device));
+  vc::SampleParams p{};
+  p.tokens = tokens;
+  p.is_bf16 = dtype == VC_DTYPE_BF16;
+  p.image_stride = image_stride;
+  p.B = n_images;
+  p.H = grid_h;
+  p.W = grid_w;
+  p.C = channels;
+  p.coords = coords;
+  p.coords_f32 = coords_are_float;
+  p.counts = counts;
+  p.cap = capacity;
+  p.projection = projection;
+  p.d = d;
+  p.quant_mode = quant_mode;
+  if (kp_scale) {
+    p.sx1 = kp_scale[0];
+    p.sx2 = kp_scale[1];
+    p.sy1 = kp_scale[2];
+    p.sy2 = kp_scale[3];
+  }
+  p.keypoints = keypoints;
+  p.desc_bf16 = static_cast<__nv_bfloat16*>(desc_bf16);
+  p.desc_u8 = desc_u8;
+  p.desc_f32 = desc_f32;
+  VC_CUDA(vc::launch_sample_pack(p, reinterpret_cast<cudaStream_t>(stream)));
+  vc::add_launches(1);
+  return VC_OK;
+}
+
+}  // extern "C"
