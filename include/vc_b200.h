@@ -169,6 +169,61 @@ int vc_sample_pack(vc_handle* h, const void* tokens, int dtype, int n_images, in
                    const float* kp_scale, float* keypoints, void* desc_bf16, uint8_t* desc_u8,
                    float* desc_f32, void* stream);
 
+/* ------------------------------------------------------------------------------------------
+ * DINOv2 ViT-S/B/L/14 forward (the backbone the reference pulls through torch.hub,
+ * vit_colmap/features/vit_extractor.py:95-98, and calls as
+ * model.forward_features(x)["x_norm_patchtokens"], :135-146; preprocessing :117-132).
+ * Linear weights are bf16 in PyTorch's [out, in] layout, everything else f32; all device memory.
+ * ------------------------------------------------------------------------------------------ */
+typedef struct {
+  const float *ln1_w, *ln1_b;
+  const void* qkv_w;   /* bf16 [3C, C] */
+  const float* qkv_b;  /* [3C] */
+  const void* proj_w;  /* bf16 [C, C] */
+  const float* proj_b;
+  const float* ls1;    /* LayerScale gamma [C] */
+  const float *ln2_w, *ln2_b;
+  const void* fc1_w;   /* bf16 [4C, C] */
+  const float* fc1_b;
+  const void* fc2_w;   /* bf16 [C, 4C] */
+  const float* fc2_b;
+  const float* ls2;
+} vc_vit_block;
+
+typedef struct {
+  int32_t embed_dim;   /* C: 384 / 768 / 1024 */
+  int32_t depth;       /* 12 / 12 / 24 */
+  int32_t num_heads;   /* C / 64 */
+  int32_t patch_kpad;  /* 640: 3*14*14 = 588 patch values zero-padded to a multiple of 64 */
+  const void* patch_w;     /* bf16 [C, patch_kpad], conv weight [C,3,14,14] flattened (c,dy,dx) */
+  const float* patch_b;    /* [C] */
+  const float* cls_token;  /* [C] */
+  const float* pos_embed;  /* f32 [1 + grid_h*grid_w, C], interpolated to this grid by the caller */
+  const float *norm_w, *norm_b;
+  const vc_vit_block* blocks; /* HOST array [depth] of device pointers */
+} vc_vit_weights;
+
+size_t vc_vit_workspace_bytes(int n_images, int grid_h, int grid_w, int embed_dim);
+
+/* images: device uint8 [n_images, 14*grid_h, 14*grid_w, 3] (HWC; channel order RGB, or BGR as
+ * cv2.imread delivers when bgr != 0), already at a multiple-of-14 size.
+ * tokens: device f32 [n_images, grid_h*grid_w, C] = x_norm_patchtokens (cls token dropped). */
+int vc_vit_forward(vc_handle* h, const vc_vit_weights* w, const uint8_t* images, int bgr, int n_images,
+                   int grid_h, int grid_w, float* tokens, void* workspace, size_t workspace_bytes,
+                   void* stream);
+
+/* Building blocks of the forward, exposed for the per-op parity tests.
+ * vc_vit_linear: out = epilogue(A[M,K] bf16 * W[N,K]^T bf16 + bias); epilogue 0: bf16 out,
+ * 1: bf16 GELU(erf) out, 2: f32 out += gamma * (.).  K % 64 == 0, N % 32 == 0. */
+int vc_vit_linear(vc_handle* h, const void* a, const void* w, const float* bias, const float* gamma,
+                  int m, int n, int k, int epilogue, void* out, void* stream);
+/* vc_vit_attention: qkv bf16 [n_images, tokens, 3*heads*64] -> out bf16 [n_images, tokens, heads*64] */
+int vc_vit_attention(vc_handle* h, const void* qkv, int n_images, int tokens, int heads, void* out,
+                     void* stream);
+/* vc_vit_layernorm: f32 [rows, C] -> bf16 [rows, C], eps 1e-6 */
+int vc_vit_layernorm(vc_handle* h, const float* x, const float* w, const float* b, int rows, int channels,
+                     void* out_bf16, void* stream);
+
 /* Number of kernels launched by this library on the calling thread since the last reset
  * (bench.py reports it as gpu_launches). */
 int64_t vc_launch_count(int reset);

@@ -52,7 +52,29 @@ SIGNATURES = {
     "vc_sample_pack": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_int, c_int64,
                                c_void_p, c_int, c_void_p, c_int, c_void_p, c_int, c_int,
                                POINTER(c_float), c_void_p, c_void_p, c_void_p, c_void_p, c_void_p]),
+    "vc_vit_workspace_bytes": (c_size_t, [c_int, c_int, c_int, c_int]),
+    "vc_vit_forward": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_void_p,
+                               c_void_p, c_size_t, c_void_p]),
+    "vc_vit_linear": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int,
+                              c_int, c_void_p, c_void_p]),
+    "vc_vit_attention": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_void_p, c_void_p]),
+    "vc_vit_layernorm": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_void_p,
+                                 c_void_p]),
 }
+
+
+class VitBlock(ctypes.Structure):
+    """vc_vit_block (include/vc_b200.h)."""
+    _fields_ = [(n, c_void_p) for n in ("ln1_w", "ln1_b", "qkv_w", "qkv_b", "proj_w", "proj_b", "ls1",
+                                        "ln2_w", "ln2_b", "fc1_w", "fc1_b", "fc2_w", "fc2_b", "ls2")]
+
+
+class VitWeights(ctypes.Structure):
+    """vc_vit_weights (include/vc_b200.h)."""
+    _fields_ = [("embed_dim", c_int32), ("depth", c_int32), ("num_heads", c_int32), ("patch_kpad", c_int32),
+                ("patch_w", c_void_p), ("patch_b", c_void_p), ("cls_token", c_void_p),
+                ("pos_embed", c_void_p), ("norm_w", c_void_p), ("norm_b", c_void_p),
+                ("blocks", POINTER(VitBlock))]
 
 DTYPE_U8, DTYPE_F32, DTYPE_BF16 = 0, 1, 2
 

@@ -1,0 +1,220 @@
+// C ABI, ViT forward half (see include/vc_b200.h): tensor-map creation, workspace carving and the
+// per-layer launch sequence.  No CPU path.
+#include "vc_internal.cuh"
+#include "vit_kernels.cuh"
+
+using vc::fail;
+
+namespace {
+
+// 2-D bf16 row-major [rows, cols] map with a {64, box_rows} box, 128-byte swizzle
+int make_map_2d(vc_handle* h, CUtensorMap* map, const void* ptr, uint64_t rows, uint64_t cols,
+                uint32_t box_rows) {
+  if ((reinterpret_cast<uintptr_t>(ptr) & 15) != 0 || cols % 8 != 0)
+    return fail(VC_ERR_INVALID, "GEMM operand must be 16-byte aligned with a multiple-of-8 row length");
+  cuuint64_t gdim[2] = {cols, rows};
+  cuuint64_t gstride[1] = {cols * 2};
+  cuuint32_t box[2] = {64, box_rows};
+  cuuint32_t estr[2] = {1, 1};
+  CUresult r = h->encode(map, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(ptr), gdim, gstride,
+                         box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
+                         CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) return fail(VC_ERR_CUDA, "cuTensorMapEncodeTiled failed with CUresult %d", (int)r);
+  return VC_OK;
+}
+
+// 3-D map over qkv bf16 [B, T, 3C]: box {64, 128, 1}
+int make_map_qkv(vc_handle* h, CUtensorMap* map, const void* ptr, int B, int T, int C3) {
+  if ((reinterpret_cast<uintptr_t>(ptr) & 15) != 0) return fail(VC_ERR_INVALID, "qkv must be 16-byte aligned");
+  cuuint64_t gdim[3] = {(cuuint64_t)C3, (cuuint64_t)T, (cuuint64_t)B};
+  cuuint64_t gstride[2] = {(cuuint64_t)C3 * 2, (cuuint64_t)C3 * 2 * (cuuint64_t)T};
+  cuuint32_t box[3] = {64, 128, 1};
+  cuuint32_t estr[3] = {1, 1, 1};
+  CUresult r = h->encode(map, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 3, const_cast<void*>(ptr), gdim, gstride,
+                         box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
+                         CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) return fail(VC_ERR_CUDA, "cuTensorMapEncodeTiled failed with CUresult %d", (int)r);
+  return VC_OK;
+}
+
+int run_linear(vc_handle* h, const void* a, const void* w, int m, int n, int k, vc::GemmParams p,
+               cudaStream_t s) {
+  CUtensorMap ma, mw;
+  int rc = make_map_2d(h, &ma, a, (uint64_t)m, (uint64_t)k, 128);
+  if (rc != VC_OK) return rc;
+  rc = make_map_2d(h, &mw, w, (uint64_t)n, (uint64_t)k, 256);
+  if (rc != VC_OK) return rc;
+  p.M = m;
+  p.N = n;
+  p.K = k;
+  VC_CUDA(vc::launch_gemm(ma, mw, p, h->num_sms, s));
+  vc::add_launches(1);
+  return VC_OK;
+}
+
+struct VitWs {
+  float* x;                // [B*T, C] residual stream
+  __nv_bfloat16* y;        // [B*T, C] LayerNorm output / attention output
+  __nv_bfloat16* wide;     // [B*T, 4C] qkv (3C) / MLP hidden (4C) / patch rows (kpad)
+};
+
+size_t ws_bytes(int B, int T, int C, VitWs* out, void* base) {
+  const size_t rows = (size_t)B * T;
+  const size_t bx = vc::align_up(rows * C * 4, 1024), by = vc::align_up(rows * C * 2, 1024);
+  const size_t bw = vc::align_up(rows * (size_t)(4 * C > 640 ? 4 * C : 640) * 2, 1024);
+  if (out) {
+    uint8_t* p = static_cast<uint8_t*>(base);
+    out->x = reinterpret_cast<float*>(p);
+    out->y = reinterpret_cast<__nv_bfloat16*>(p + bx);
+    out->wide = reinterpret_cast<__nv_bfloat16*>(p + bx + by);
+  }
+  return bx + by + bw;
+}
+
+}  // namespace
+
+extern "C" {
+
+size_t vc_vit_workspace_bytes(int n_images, int grid_h, int grid_w, int embed_dim) {
+  if (n_images <= 0 || grid_h <= 0 || grid_w <= 0 || embed_dim <= 0) return 1024;
+  return ws_bytes(n_images, grid_h * grid_w + 1, embed_dim, nullptr, nullptr) + 1024;
+}
+
+int vc_vit_linear(vc_handle* h, const void* a, const void* w, const float* bias, const float* gamma,
+                  int m, int n, int k, int epilogue, void* out, void* stream) {
+  if (!h) return fail(VC_ERR_INVALID, "null handle");
+  if (!a || !w || !bias || !out) return fail(VC_ERR_INVALID, "null pointer argument");
+  if (m <= 0 || n <= 0 || k <= 0 || k % 64 != 0 || n % 32 != 0)
+    return fail(VC_ERR_INVALID, "bad GEMM shape m=%d n=%d k=%d (k %% 64, n %% 32)", m, n, k);
+  if (epilogue < 0 || epilogue > 2) return fail(VC_ERR_INVALID, "bad epilogue %d", epilogue);
+  if (epilogue == 2 && !gamma) return fail(VC_ERR_INVALID, "residual epilogue needs gamma");
+  VC_CUDA(cudaSetDevice(h->device));
+  vc::GemmParams p{};
+  p.epilogue = epilogue;
+  p.bias = bias;
+  p.gamma = gamma;
+  p.out = out;
+  p.ldo = n;
+  return run_linear(h, a, w, m, n, k, p, reinterpret_cast<cudaStream_t>(stream));
+}
+
+int vc_vit_attention(vc_handle* h, const void* qkv, int n_images, int tokens, int heads, void* out,
+                     void* stream) {
+  if (!h) return fail(VC_ERR_INVALID, "null handle");
+  if (!qkv || !out) return fail(VC_ERR_INVALID, "null pointer argument");
+  if (n_images <= 0 || tokens <= 0 || heads <= 0) return fail(VC_ERR_INVALID, "bad attention shape");
+  VC_CUDA(cudaSetDevice(h->device));
+  CUtensorMap map;
+  int rc = make_map_qkv(h, &map, qkv, n_images, tokens, 3 * heads * 64);
+  if (rc != VC_OK) return rc;
+  vc::AttnParams p{};
+  p.B = n_images;
+  p.T = tokens;
+  p.heads = heads;
+  p.scale = 0.125f;
+  p.out = static_cast<__nv_bfloat16*>(out);
+  VC_CUDA(vc::launch_attention(map, p, reinterpret_cast<cudaStream_t>(stream)));
+  vc::add_launches(1);
+  return VC_OK;
+}
+
+int vc_vit_layernorm(vc_handle* h, const float* x, const float* w, const float* b, int rows, int channels,
+                     void* out_bf16, void* stream) {
+  if (!h) return fail(VC_ERR_INVALID, "null handle");
+  if (!x || !w || !b || !out_bf16) return fail(VC_ERR_INVALID, "null pointer argument");
+  if (rows <= 0 || channels <= 0 || channels % 4 != 0 || channels > 1024)
+    return fail(VC_ERR_INVALID, "bad LayerNorm shape");
+  VC_CUDA(cudaSetDevice(h->device));
+  VC_CUDA(vc::launch_layernorm_bf16(x, w, b, static_cast<__nv_bfloat16*>(out_bf16), rows, channels,
+                                    reinterpret_cast<cudaStream_t>(stream)));
+  vc::add_launches(1);
+  return VC_OK;
+}
+
+int vc_vit_forward(vc_handle* h, const vc_vit_weights* w, const uint8_t* images, int bgr, int n_images,
+                   int grid_h, int grid_w, float* tokens, void* workspace, size_t workspace_bytes,
+                   void* stream) {
+  if (!h) return fail(VC_ERR_INVALID, "null handle");
+  if (!w || !images || !tokens || !workspace) return fail(VC_ERR_INVALID, "null pointer argument");
+  if (n_images <= 0 || grid_h <= 0 || grid_w <= 0) return fail(VC_ERR_INVALID, "bad sizes");
+  const int C = w->embed_dim, heads = w->num_heads, kpad = w->patch_kpad;
+  if (C <= 0 || C % 64 != 0 || C > 1024 || heads * 64 != C || w->depth <= 0 || !w->blocks)
+    return fail(VC_ERR_INVALID, "bad model (embed_dim=%d heads=%d depth=%d)", C, heads, w->depth);
+  if (kpad < 588 || kpad % 64 != 0) return fail(VC_ERR_INVALID, "patch_kpad=%d must be >= 588 and %% 64", kpad);
+  if (workspace_bytes < vc_vit_workspace_bytes(n_images, grid_h, grid_w, C))
+    return fail(VC_ERR_WORKSPACE, "workspace %zu B < required %zu B", workspace_bytes,
+                vc_vit_workspace_bytes(n_images, grid_h, grid_w, C));
+  VC_CUDA(cudaSetDevice(h->device));
+  cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
+  const int HW = grid_h * grid_w, T = HW + 1, rows = n_images * T;
+  VitWs ws;
+  uint8_t* base = reinterpret_cast<uint8_t*>(vc::align_up(reinterpret_cast<uintptr_t>(workspace), 1024));
+  ws_bytes(n_images, T, C, &ws, base);
+
+  // patch embedding: u8 image -> normalised bf16 patch rows -> GEMM (+bias +pos) into x[:, 1:, :]
+  VC_CUDA(vc::launch_patchify(images, n_images, grid_h * 14, grid_w * 14, bgr, ws.wide, kpad, w->cls_token,
+                              w->pos_embed, ws.x, C, s));
+  vc::add_launches(1);
+  {
+    vc::GemmParams p{};
+    p.epilogue = vc::kEpiPatchEmbed;
+    p.bias = w->patch_b;
+    p.pos = w->pos_embed;
+    p.tokens_per_image = HW;
+    p.out = ws.x;
+    p.ldo = C;
+    int rc = run_linear(h, ws.wide, w->patch_w, n_images * HW, C, kpad, p, s);
+    if (rc != VC_OK) return rc;
+  }
+  CUtensorMap map_qkv;
+  int rc = make_map_qkv(h, &map_qkv, ws.wide, n_images, T, 3 * C);
+  if (rc != VC_OK) return rc;
+  for (int l = 0; l < w->depth; ++l) {
+    const vc_vit_block& b = w->blocks[l];
+    VC_CUDA(vc::launch_layernorm_bf16(ws.x, b.ln1_w, b.ln1_b, ws.y, rows, C, s));
+    vc::GemmParams p{};
+    p.epilogue = vc::kEpiBiasBf16;
+    p.bias = b.qkv_b;
+    p.out = ws.wide;
+    p.ldo = 3 * C;
+    rc = run_linear(h, ws.y, b.qkv_w, rows, 3 * C, C, p, s);
+    if (rc != VC_OK) return rc;
+    vc::AttnParams ap{};
+    ap.B = n_images;
+    ap.T = T;
+    ap.heads = heads;
+    ap.scale = 0.125f;
+    ap.out = ws.y;
+    VC_CUDA(vc::launch_attention(map_qkv, ap, s));
+    p = vc::GemmParams{};
+    p.epilogue = vc::kEpiResidualF32;
+    p.bias = b.proj_b;
+    p.gamma = b.ls1;
+    p.out = ws.x;
+    p.ldo = C;
+    rc = run_linear(h, ws.y, b.proj_w, rows, C, C, p, s);
+    if (rc != VC_OK) return rc;
+    VC_CUDA(vc::launch_layernorm_bf16(ws.x, b.ln2_w, b.ln2_b, ws.y, rows, C, s));
+    p = vc::GemmParams{};
+    p.epilogue = vc::kEpiBiasGeluBf16;
+    p.bias = b.fc1_b;
+    p.out = ws.wide;
+    p.ldo = 4 * C;
+    rc = run_linear(h, ws.y, b.fc1_w, rows, 4 * C, C, p, s);
+    if (rc != VC_OK) return rc;
+    p = vc::GemmParams{};
+    p.epilogue = vc::kEpiResidualF32;
+    p.bias = b.fc2_b;
+    p.gamma = b.ls2;
+    p.out = ws.x;
+    p.ldo = C;
+    rc = run_linear(h, ws.wide, b.fc2_w, rows, C, 4 * C, p, s);
+    if (rc != VC_OK) return rc;
+    vc::add_launches(3);
+  }
+  VC_CUDA(vc::launch_layernorm_final(ws.x, w->norm_w, w->norm_b, tokens, n_images, T, C, s));
+  vc::add_launches(1);
+  return VC_OK;
+}
+
+}  // extern "C"

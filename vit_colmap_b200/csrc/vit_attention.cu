@@ -1,0 +1,282 @@
+// Multi-head self-attention of the ViT blocks (head_dim 64) on tcgen05: softmax(Q K^T / 8) V per
+// (image, head), straight from the packed QKV GEMM output, without materialising the T x T scores.
+//
+// CTA = (image, head, pair of 128-row query tiles).  Roles:
+//   warp 0  TMA: both Q tiles once, then a 3-stage ring of (K_j, V_j) 128-key tiles (128B swizzle)
+//   warp 1  tcgen05.mma issuer: S_w = Q_w K_j^T (M128 N128 K64) into TMEM, and, once the softmax
+//           warps have published P_w (bf16, written to shared memory in the K-major swizzled
+//           operand layout), O_w^(j) = P_w V_j (M128 N64 K128; V is consumed as an MN-major operand
+//           exactly as TMA delivered it, so no transposed copy of V exists anywhere)
+//   warp 2  TMEM allocator (S_0, S_1: 2 x 128 columns, O tiles: 2 x 64 columns)
+//   warps 4-7 / 8-11  softmax warpgroup of query tile 0 / 1: thread = one query row.  Online
+//           softmax in the exp2 domain; the running output row lives in 64 registers and is rescaled
+//           when the row maximum moves, so TMEM is never read-modified-written.
+// The two warpgroups share every K/V tile and keep the tensor core busy for each other.
+#include "vit_kernels.cuh"
+
+#include <math.h>
+
+#include "vc_ptx.cuh"
+
+namespace vc {
+
+namespace {
+
+constexpr int kTile = 128, kHd = 64, kKvStages = 3;
+constexpr int kQBytes = kTile * kHd * 2;          // 16 KB
+constexpr int kKvBytes = 2 * kTile * kHd * 2;     // K + V of one stage, 32 KB
+constexpr int kPBytes = kTile * kTile * 2;        // 32 KB per warpgroup
+constexpr int kThreads = 384;
+constexpr int kTmemCols = 512;
+constexpr int kSmemBytes = 2 * kQBytes + kKvStages * kKvBytes + 2 * kPBytes + 1024 + 256;
+
+// K-major A (bits 15 = 0), MN-major B (bit 16 = 1): B = V tile [keys, 64] with the head dim contiguous
+__host__ __device__ constexpr uint32_t idesc_pv() { return umma_idesc_bf16(128, 64) | (1u << 16); }
+
+__device__ __forceinline__ float ex2(float x) {
+  float y;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
+
+__device__ __forceinline__ uint32_t pack_bf16(float a, float b) {
+  __nv_bfloat162 v = __floats2bfloat162_rn(a, b);
+  return *reinterpret_cast<uint32_t*>(&v);
+}
+
+}  // namespace
+
+__global__ void __launch_bounds__(kThreads, 1)
+vit_attention_kernel(const __grid_constant__ CUtensorMap map_qkv, const AttnParams p) {
+  extern __shared__ uint8_t smem_raw[];
+  const uint32_t raw_addr = smem_u32(smem_raw);
+  const uint32_t base = (raw_addr + 1023u) & ~1023u;
+  uint8_t* smem = smem_raw + (base - raw_addr);
+  const uint32_t sQ = base;                                    // 2 x 16 KB
+  const uint32_t sKV = sQ + 2 * kQBytes;                       // stages x (K 16 KB, V 16 KB)
+  const uint32_t sP = sKV + kKvStages * kKvBytes;              // 2 x 32 KB
+  uint8_t* sP_gen = smem + 2 * kQBytes + kKvStages * kKvBytes;
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + 2 * kQBytes + kKvStages * kKvBytes + 2 * kPBytes);
+  const uint32_t bar0 = smem_u32(bars);
+  const uint32_t q_full = bar0;
+  auto kv_full = [&](int s) { return bar0 + 8u * (1 + s); };
+  auto kv_empty = [&](int s) { return bar0 + 8u * (1 + kKvStages + s); };
+  auto s_full = [&](int w) { return bar0 + 8u * (1 + 2 * kKvStages + w); };
+  auto p_full = [&](int w) { return bar0 + 8u * (3 + 2 * kKvStages + w); };
+  auto o_full = [&](int w) { return bar0 + 8u * (5 + 2 * kKvStages + w); };
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 7 + 2 * kKvStages);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int C = p.heads * kHd;
+  const int q_pairs = (p.T + 2 * kTile - 1) / (2 * kTile);
+  const int qp = blockIdx.x % q_pairs;
+  const int bh = blockIdx.x / q_pairs;
+  const int head = bh % p.heads, img = bh / p.heads;
+  const int q0 = qp * 2 * kTile;
+  const int nw = (q0 + kTile < p.T) ? 2 : 1;
+  const int nkv = (p.T + kTile - 1) / kTile;
+
+  if (warp == 0 && lane == 0) tma_prefetch_desc(&map_qkv);
+  if (warp == 1 && lane == 0) {
+    mbar_init(q_full, 1);
+    for (int s = 0; s < kKvStages; ++s) {
+      mbar_init(kv_full(s), 1);
+      mbar_init(kv_empty(s), 1);
+    }
+    for (int w = 0; w < 2; ++w) {
+      mbar_init(s_full(w), 1);
+      mbar_init(p_full(w), 128);
+      mbar_init(o_full(w), 1);
+    }
+    fence_mbar_init();
+  }
+  if (warp == 2) {
+    tmem_alloc(smem_u32(tmem_slot), kTmemCols);
+    tmem_relinquish();
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp == 0 && lane == 0) {
+    // ------------------------------------------------------------ TMA producer
+    mbar_arrive_expect_tx(q_full, 2 * kQBytes);
+    tma_load_3d(sQ, &map_qkv, q_full, head * kHd, q0, img);
+    tma_load_3d(sQ + kQBytes, &map_qkv, q_full, head * kHd, q0 + kTile, img);
+    for (int j = 0; j < nkv; ++j) {
+      const int s = j % kKvStages;
+      const uint32_t ph = (j / kKvStages) & 1;
+      mbar_wait(kv_empty(s), ph ^ 1);
+      mbar_arrive_expect_tx(kv_full(s), kKvBytes);
+      tma_load_3d(sKV + s * kKvBytes, &map_qkv, kv_full(s), C + head * kHd, j * kTile, img);
+      tma_load_3d(sKV + s * kKvBytes + kKvBytes / 2, &map_qkv, kv_full(s), 2 * C + head * kHd, j * kTile,
+                  img);
+    }
+  } else if (warp == 1 && lane == 0) {
+    // ------------------------------------------------------------ MMA issuer
+    constexpr uint32_t idesc_s = umma_idesc_bf16(128, 128);
+    constexpr uint32_t idesc_o = idesc_pv();
+    auto issue_s = [&](int w, int s) {
+      const uint64_t da = umma_desc_k_sw128(sQ + w * kQBytes);
+      const uint64_t db = umma_desc_k_sw128(sKV + s * kKvBytes);
+#pragma unroll
+      for (int k = 0; k < kHd / 16; ++k)
+        tc_mma_bf16(tmem_base + w * 128, da + 2 * k, db + 2 * k, idesc_s, k != 0);
+      tc_commit(s_full(w));
+    };
+    mbar_wait(q_full, 0);
+    mbar_wait(kv_full(0), 0);
+    tc_fence_after();
+    for (int w = 0; w < nw; ++w) issue_s(w, 0);
+    for (int j = 0; j < nkv; ++j) {
+      const int s = j % kKvStages;
+      const bool more = j + 1 < nkv;
+      const int s1 = (j + 1) % kKvStages;
+      if (more) {
+        mbar_wait(kv_full(s1), ((j + 1) / kKvStages) & 1);
+        tc_fence_after();
+      }
+      for (int w = 0; w < nw; ++w) {
+        mbar_wait(p_full(w), j & 1);
+        tc_fence_after();
+        // O_w^(j) = P_w (128 x 128, two 64-key halves, K-major) * V_j (128 keys x 64, MN-major)
+        const uint32_t pw = sP + w * kPBytes;
+        const uint64_t dv = umma_desc_k_sw128(sKV + s * kKvBytes + kKvBytes / 2);
+#pragma unroll
+        for (int k = 0; k < kTile / 16; ++k) {
+          const uint64_t dp = umma_desc_k_sw128(pw + (k >> 2) * (kPBytes / 2)) + 2 * (k & 3);
+          tc_mma_bf16(tmem_base + 256 + w * 64, dp, dv + 128 * k, idesc_o, k != 0);
+        }
+        tc_commit(o_full(w));
+        if (more) issue_s(w, s1);
+      }
+      tc_commit(kv_empty(s));
+    }
+  } else if (warp >= 4 && (warp - 4) / 4 < nw) {
+    // ------------------------------------------------------------ softmax warpgroups
+    const int w = (warp - 4) >> 2;
+    const int quarter = warp & 3;
+    const int r = quarter * 32 + lane;  // row inside the query tile == TMEM lane
+    const uint32_t t_s = tmem_base + (static_cast<uint32_t>(quarter * 32) << 16) + w * 128;
+    const uint32_t t_o = tmem_base + (static_cast<uint32_t>(quarter * 32) << 16) + 256 + w * 64;
+    const float sc = p.scale * 1.4426950408889634f;  // scores are handled in the exp2 domain
+    uint8_t* prow = sP_gen + w * kPBytes + r * 128;
+    float o[kHd];
+#pragma unroll
+    for (int e = 0; e < kHd; ++e) o[e] = 0.f;
+    float m_run = -1e30f, l_run = 0.f;
+    for (int j = 0; j < nkv; ++j) {
+      const int valid = min(kTile, p.T - j * kTile);  // keys of this tile inside the image
+      mbar_wait(s_full(w), j & 1);
+      tc_fence_after();
+      // pass 1: row maximum
+      float mx = -1e30f;
+#pragma unroll 1
+      for (int c = 0; c < 4; ++c) {
+        uint32_t vr[32];
+        tmem_ld_32x32(t_s + c * 32, vr);
+        tmem_wait_ld();
+#pragma unroll
+        for (int e = 0; e < 32; ++e) {
+          const float v = __uint_as_float(vr[e]);
+          if (c * 32 + e < valid) mx = fmaxf(mx, v);
+        }
+      }
+      const float m_new = fmaxf(m_run, mx * sc);
+      const float alpha = ex2(m_run - m_new);
+      m_run = m_new;
+      // fold the previous tile's P V into the running output, then rescale to the new maximum
+      if (j > 0) {
+        mbar_wait(o_full(w), (j - 1) & 1);
+        tc_fence_after();
+#pragma unroll
+        for (int c = 0; c < 2; ++c) {
+          uint32_t vr[32];
+          tmem_ld_32x32(t_o + c * 32, vr);
+          tmem_wait_ld();
+#pragma unroll
+          for (int e = 0; e < 32; ++e) o[c * 32 + e] = (o[c * 32 + e] + __uint_as_float(vr[e])) * alpha;
+        }
+      }
+      // pass 2: probabilities -> bf16 operand tile in shared memory
+      float sum = 0.f;
+#pragma unroll 1
+      for (int c = 0; c < 4; ++c) {
+        uint32_t vr[32];
+        tmem_ld_32x32(t_s + c * 32, vr);
+        tmem_wait_ld();
+        float pv[32];
+#pragma unroll
+        for (int e = 0; e < 32; ++e) {
+          const float x = ex2(fmaf(__uint_as_float(vr[e]), sc, -m_new));
+          pv[e] = (c * 32 + e < valid) ? x : 0.f;
+          sum += pv[e];
+        }
+        // chunk c covers keys [32c, 32c+32): half c>>1, 16-byte chunks (c&1)*4 .. +3 of the row
+        uint8_t* half = prow + (c >> 1) * (kPBytes / 2);
+#pragma unroll
+        for (int g = 0; g < 4; ++g) {
+          uint4 pk;
+          pk.x = pack_bf16(pv[8 * g + 0], pv[8 * g + 1]);
+          pk.y = pack_bf16(pv[8 * g + 2], pv[8 * g + 3]);
+          pk.z = pack_bf16(pv[8 * g + 4], pv[8 * g + 5]);
+          pk.w = pack_bf16(pv[8 * g + 6], pv[8 * g + 7]);
+          const int chunk = ((c & 1) * 4 + g) ^ (r & 7);
+          *reinterpret_cast<uint4*>(half + chunk * 16) = pk;
+        }
+      }
+      l_run = l_run * alpha + sum;
+      fence_proxy_async_smem();
+      tc_fence_before();
+      mbar_arrive(p_full(w));
+    }
+    // last tile's P V
+    mbar_wait(o_full(w), (nkv - 1) & 1);
+    tc_fence_after();
+#pragma unroll
+    for (int c = 0; c < 2; ++c) {
+      uint32_t vr[32];
+      tmem_ld_32x32(t_o + c * 32, vr);
+      tmem_wait_ld();
+#pragma unroll
+      for (int e = 0; e < 32; ++e) o[c * 32 + e] += __uint_as_float(vr[e]);
+    }
+    const int t = q0 + w * kTile + r;
+    if (t < p.T) {
+      const float inv = 1.0f / l_run;
+      uint4* dst = reinterpret_cast<uint4*>(p.out + ((size_t)img * p.T + t) * C + head * kHd);
+#pragma unroll
+      for (int g = 0; g < 8; ++g) {
+        uint4 pk;
+        pk.x = pack_bf16(o[8 * g + 0] * inv, o[8 * g + 1] * inv);
+        pk.y = pack_bf16(o[8 * g + 2] * inv, o[8 * g + 3] * inv);
+        pk.z = pack_bf16(o[8 * g + 4] * inv, o[8 * g + 5] * inv);
+        pk.w = pack_bf16(o[8 * g + 6] * inv, o[8 * g + 7] * inv);
+        dst[g] = pk;
+      }
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 2) tmem_dealloc(tmem_base, kTmemCols);
+}
+
+int attn_smem_bytes() { return kSmemBytes; }
+
+cudaError_t launch_attention(const CUtensorMap& map_qkv, const AttnParams& p, cudaStream_t stream) {
+  static bool configured = false;
+  if (!configured) {
+    cudaError_t e = cudaFuncSetAttribute(vit_attention_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                         kSmemBytes);
+    if (e != cudaSuccess) return e;
+    configured = true;
+  }
+  if (p.B <= 0 || p.T <= 0) return cudaSuccess;
+  const int q_pairs = (p.T + 2 * kTile - 1) / (2 * kTile);
+  vit_attention_kernel<<<p.B * p.heads * q_pairs, kThreads, kSmemBytes, stream>>>(map_qkv, p);
+  return cudaGetLastError();
+}
+
+}  // namespace vc

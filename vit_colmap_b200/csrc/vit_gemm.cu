@@ -1,0 +1,243 @@
+// Persistent tcgen05 GEMM for the ViT linear layers: D[M,N] = A[M,K] * W[N,K]^T with the
+// bias / GELU / LayerScale+residual / position-embedding work fused into the epilogue.
+//   - one CTA per SM, tiles of 128 x 256 x 64 handed out round-robin (n fastest, so the CTAs that
+//     run together share the same rows of A in L2; W stays L2-resident: <= 9.4 MB)
+//   - warp 0: TMA producer (4-stage ring, 128-byte swizzle), warp 1: tcgen05.mma issuer
+//     (M=128, N=256, K=16 per instruction), warp 2: TMEM allocator
+//   - fp32 accumulators double-buffered in TMEM (2 x 256 columns): the 8 epilogue warps drain tile
+//     i with tcgen05.ld while the tensor core fills tile i+1
+//   - epilogue thread = one output row x 32 consecutive columns -> 16-byte vector stores
+// Activations are bf16, accumulation and the residual stream are fp32.
+#include "vit_kernels.cuh"
+
+#include <math.h>
+
+#include "vc_ptx.cuh"
+
+namespace vc {
+
+namespace {
+
+constexpr int BM = 128, BN = 256, BK = 64, kStages = 4;
+constexpr int kABytes = BM * BK * 2, kBBytes = BN * BK * 2, kStageBytes = kABytes + kBBytes;
+constexpr int kThreads = 384;
+constexpr int kTmemCols = 512;
+constexpr int kSmemBytes = kStages * kStageBytes + 1024 + 256;
+
+__device__ __forceinline__ float gelu_erf(float x) {
+  return 0.5f * x * (1.0f + erff(x * 0.70710678118654752440f));
+}
+
+__device__ __forceinline__ uint32_t pack_bf16(float a, float b) {
+  __nv_bfloat162 v = __floats2bfloat162_rn(a, b);
+  return *reinterpret_cast<uint32_t*>(&v);
+}
+
+template <int EPI>
+__global__ void __launch_bounds__(kThreads, 1)
+vit_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_w,
+                const GemmParams p) {
+  extern __shared__ uint8_t smem_raw[];
+  const uint32_t raw_addr = smem_u32(smem_raw);
+  const uint32_t base = (raw_addr + 1023u) & ~1023u;
+  uint8_t* smem = smem_raw + (base - raw_addr);
+  const uint32_t sA = base;
+  const uint32_t sB = base + kStages * kABytes;
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + kStages * kStageBytes);
+  const uint32_t bar0 = smem_u32(bars);
+  auto full_bar = [&](int s) { return bar0 + 8u * s; };
+  auto empty_bar = [&](int s) { return bar0 + 8u * (kStages + s); };
+  auto tfull_bar = [&](int s) { return bar0 + 8u * (2 * kStages + s); };
+  auto tempty_bar = [&](int s) { return bar0 + 8u * (2 * kStages + 2 + s); };
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * kStages + 4);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int nkb = p.K / BK;
+  const int tiles_n = (p.N + BN - 1) / BN;
+  const int tiles_m = (p.M + BM - 1) / BM;
+  const int n_tiles = tiles_m * tiles_n;
+
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&map_a);
+    tma_prefetch_desc(&map_w);
+  }
+  if (warp == 1 && lane == 0) {
+    for (int s = 0; s < kStages; ++s) {
+      mbar_init(full_bar(s), 1);
+      mbar_init(empty_bar(s), 1);
+    }
+    for (int s = 0; s < 2; ++s) {
+      mbar_init(tfull_bar(s), 1);
+      mbar_init(tempty_bar(s), 256);
+    }
+    fence_mbar_init();
+  }
+  if (warp == 2) {
+    tmem_alloc(smem_u32(tmem_slot), kTmemCols);
+    tmem_relinquish();
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp == 0 && lane == 0) {
+    uint32_t stage = 0, phase = 0;
+    for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+      const int tm = tile / tiles_n, tn = tile - tm * tiles_n;
+      for (int kb = 0; kb < nkb; ++kb) {
+        mbar_wait(empty_bar(stage), phase ^ 1);
+        mbar_arrive_expect_tx(full_bar(stage), kStageBytes);
+        tma_load_2d(sA + stage * kABytes, &map_a, full_bar(stage), kb * BK, tm * BM);
+        tma_load_2d(sB + stage * kBBytes, &map_w, full_bar(stage), kb * BK, tn * BN);
+        if (++stage == kStages) {
+          stage = 0;
+          phase ^= 1;
+        }
+      }
+    }
+  } else if (warp == 1 && lane == 0) {
+    constexpr uint32_t idesc = umma_idesc_bf16(BM, BN);
+    uint32_t stage = 0, phase = 0, it = 0;
+    for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x, ++it) {
+      const uint32_t as = it & 1, aph = (it >> 1) & 1;
+      mbar_wait(tempty_bar(as), aph ^ 1);
+      tc_fence_after();
+      const uint32_t d_tmem = tmem_base + as * BN;
+      for (int kb = 0; kb < nkb; ++kb) {
+        mbar_wait(full_bar(stage), phase);
+        tc_fence_after();
+        const uint64_t da = umma_desc_k_sw128(sA + stage * kABytes);
+        const uint64_t db = umma_desc_k_sw128(sB + stage * kBBytes);
+#pragma unroll
+        for (int k = 0; k < BK / 16; ++k) tc_mma_bf16(d_tmem, da + 2 * k, db + 2 * k, idesc, (kb | k) != 0);
+        tc_commit(empty_bar(stage));
+        if (kb == nkb - 1) tc_commit(tfull_bar(as));
+        if (++stage == kStages) {
+          stage = 0;
+          phase ^= 1;
+        }
+      }
+    }
+  } else if (warp >= 4) {
+    const int q = warp & 3;
+    const int h = (warp - 4) >> 2;
+    uint32_t it = 0;
+    for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x, ++it) {
+      const int tm = tile / tiles_n, tn = tile - tm * tiles_n;
+      const int m = tm * BM + q * 32 + lane;
+      const bool row_ok = m < p.M;
+      const uint32_t as = it & 1, aph = (it >> 1) & 1;
+      mbar_wait(tfull_bar(as), aph);
+      tc_fence_after();
+      const uint32_t t_addr = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + as * BN;
+      size_t out_row = (size_t)m;
+      const float* pos_row = nullptr;
+      if (EPI == kEpiPatchEmbed) {
+        const int img = m / p.tokens_per_image, t = m - img * p.tokens_per_image;
+        out_row = (size_t)img * (p.tokens_per_image + 1) + 1 + t;
+        pos_row = p.pos + (size_t)(1 + t) * p.N;
+      }
+#pragma unroll 1
+      for (int c = 0; c < 4; ++c) {
+        const int n0 = tn * BN + h * 128 + c * 32;
+        if (n0 >= p.N) break;  // warp-uniform
+        uint32_t vr[32];
+        tmem_ld_32x32(t_addr + h * 128 + c * 32, vr);
+        tmem_wait_ld();
+        if (!row_ok) continue;
+        float v[32];
+#pragma unroll
+        for (int e = 0; e < 32; ++e) v[e] = __uint_as_float(vr[e]);
+        const float4* b4 = reinterpret_cast<const float4*>(p.bias + n0);
+#pragma unroll
+        for (int g = 0; g < 8; ++g) {
+          const float4 b = __ldg(b4 + g);
+          v[4 * g + 0] += b.x;
+          v[4 * g + 1] += b.y;
+          v[4 * g + 2] += b.z;
+          v[4 * g + 3] += b.w;
+        }
+        if (EPI == kEpiBiasBf16 || EPI == kEpiBiasGeluBf16) {
+          if (EPI == kEpiBiasGeluBf16) {
+#pragma unroll
+            for (int e = 0; e < 32; ++e) v[e] = gelu_erf(v[e]);
+          }
+          uint4* o = reinterpret_cast<uint4*>(static_cast<__nv_bfloat16*>(p.out) + out_row * p.ldo + n0);
+#pragma unroll
+          for (int g = 0; g < 4; ++g) {
+            uint4 w;
+            w.x = pack_bf16(v[8 * g + 0], v[8 * g + 1]);
+            w.y = pack_bf16(v[8 * g + 2], v[8 * g + 3]);
+            w.z = pack_bf16(v[8 * g + 4], v[8 * g + 5]);
+            w.w = pack_bf16(v[8 * g + 6], v[8 * g + 7]);
+            o[g] = w;
+          }
+        } else if (EPI == kEpiResidualF32) {
+          float4* o = reinterpret_cast<float4*>(static_cast<float*>(p.out) + out_row * p.ldo + n0);
+          const float4* g4 = reinterpret_cast<const float4*>(p.gamma + n0);
+#pragma unroll
+          for (int g = 0; g < 8; ++g) {
+            const float4 ga = __ldg(g4 + g);
+            float4 r = o[g];
+            r.x = fmaf(ga.x, v[4 * g + 0], r.x);
+            r.y = fmaf(ga.y, v[4 * g + 1], r.y);
+            r.z = fmaf(ga.z, v[4 * g + 2], r.z);
+            r.w = fmaf(ga.w, v[4 * g + 3], r.w);
+            o[g] = r;
+          }
+        } else {
+          float4* o = reinterpret_cast<float4*>(static_cast<float*>(p.out) + out_row * p.ldo + n0);
+          const float4* p4 = reinterpret_cast<const float4*>(pos_row + n0);
+#pragma unroll
+          for (int g = 0; g < 8; ++g) {
+            const float4 pe = __ldg(p4 + g);
+            o[g] = make_float4(v[4 * g + 0] + pe.x, v[4 * g + 1] + pe.y, v[4 * g + 2] + pe.z,
+                               v[4 * g + 3] + pe.w);
+          }
+        }
+      }
+      tc_fence_before();
+      mbar_arrive(tempty_bar(as));
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 2) tmem_dealloc(tmem_base, kTmemCols);
+}
+
+template <int EPI>
+cudaError_t launch_one(const CUtensorMap& map_a, const CUtensorMap& map_w, const GemmParams& p, int grid,
+                       cudaStream_t stream) {
+  static bool configured = false;
+  if (!configured) {
+    cudaError_t e = cudaFuncSetAttribute(vit_gemm_kernel<EPI>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                         kSmemBytes);
+    if (e != cudaSuccess) return e;
+    configured = true;
+  }
+  vit_gemm_kernel<EPI><<<grid, kThreads, kSmemBytes, stream>>>(map_a, map_w, p);
+  return cudaGetLastError();
+}
+
+}  // namespace
+
+int gemm_smem_bytes() { return kSmemBytes; }
+
+cudaError_t launch_gemm(const CUtensorMap& map_a, const CUtensorMap& map_w, const GemmParams& p,
+                        int num_sms, cudaStream_t stream) {
+  if (p.M <= 0 || p.N <= 0) return cudaSuccess;
+  if (p.K <= 0 || p.K % BK != 0 || p.N % 32 != 0) return cudaErrorInvalidValue;
+  const int n_tiles = ((p.M + BM - 1) / BM) * ((p.N + BN - 1) / BN);
+  const int grid = n_tiles < num_sms ? n_tiles : num_sms;
+  switch (p.epilogue) {
+    case kEpiBiasBf16: return launch_one<kEpiBiasBf16>(map_a, map_w, p, grid, stream);
+    case kEpiBiasGeluBf16: return launch_one<kEpiBiasGeluBf16>(map_a, map_w, p, grid, stream);
+    case kEpiResidualF32: return launch_one<kEpiResidualF32>(map_a, map_w, p, grid, stream);
+    case kEpiPatchEmbed: return launch_one<kEpiPatchEmbed>(map_a, map_w, p, grid, stream);
+    default: return cudaErrorInvalidValue;
+  }
+}
+
+}  // namespace vc

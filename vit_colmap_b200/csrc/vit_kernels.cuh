@@ -1,0 +1,55 @@
+// Internal interface of the DINOv2 ViT forward kernels (vit_gemm.cu, vit_attention.cu,
+// vit_pointwise.cu).  The backbone is external to the reference (torch.hub facebookresearch/dinov2,
+// called at vit_colmap/features/vit_extractor.py:95-98,135-146); SURVEY.md Appendix A restates it.
+#pragma once
+#include <cstddef>
+#include <cstdint>
+#include <cuda.h>
+#include <cuda_bf16.h>
+#include <cuda_runtime.h>
+
+namespace vc {
+
+enum GemmEpilogue {
+  kEpiBiasBf16 = 0,      // out_bf16 = acc + bias                       (QKV)
+  kEpiBiasGeluBf16 = 1,  // out_bf16 = gelu_erf(acc + bias)             (fc1)
+  kEpiResidualF32 = 2,   // out_f32 += gamma * (acc + bias)             (proj / fc2 + LayerScale + residual)
+  kEpiPatchEmbed = 3     // out_f32[b*T + 1 + t] = acc + bias + pos[1+t] (patch embedding)
+};
+
+struct GemmParams {
+  int M, N, K;            // D[M,N] = A[M,K] * W[N,K]^T, A and W bf16 with K contiguous
+  int epilogue;
+  const float* bias;      // [N]
+  const float* gamma;     // [N] LayerScale (kEpiResidualF32)
+  const float* pos;       // [T, N] position embedding incl. cls row (kEpiPatchEmbed)
+  int tokens_per_image;   // HW (kEpiPatchEmbed): row m -> image m / HW, token 1 + m % HW
+  void* out;              // bf16 [M, ldo] or f32 [rows, ldo]
+  int ldo;
+};
+int gemm_smem_bytes();
+cudaError_t launch_gemm(const CUtensorMap& map_a, const CUtensorMap& map_w, const GemmParams& p,
+                        int num_sms, cudaStream_t stream);
+
+struct AttnParams {
+  int B, T, heads;        // head_dim is 64
+  float scale;            // 1/sqrt(64)
+  __nv_bfloat16* out;     // [B*T, heads*64]
+};
+int attn_smem_bytes();
+// map_qkv: 3-D map over qkv bf16 [B, T, 3*heads*64] with box {64, 128, 1}
+cudaError_t launch_attention(const CUtensorMap& map_qkv, const AttnParams& p, cudaStream_t stream);
+
+// LayerNorm over the last dim (eps 1e-6): f32 [rows, C] -> bf16 [rows, C] (GEMM input) or, for the
+// final norm, f32 [B, T-1, C] with the cls row dropped.
+cudaError_t launch_layernorm_bf16(const float* x, const float* w, const float* b, __nv_bfloat16* out,
+                                  int rows, int C, cudaStream_t stream);
+cudaError_t launch_layernorm_final(const float* x, const float* w, const float* b, float* out, int B,
+                                   int T, int C, cudaStream_t stream);
+// u8 HWC RGB images -> ImageNet-normalised bf16 patch rows [B*gh*gw, kpad] (3*14*14 = 588 values in
+// conv-weight order c, dy, dx, zero padded to kpad) and the cls rows of x (cls + pos[0]).
+cudaError_t launch_patchify(const uint8_t* images, int B, int img_h, int img_w, int bgr,
+                            __nv_bfloat16* patches, int kpad, const float* cls_token, const float* pos,
+                            float* x, int C, cudaStream_t stream);
+
+}  // namespace vc
