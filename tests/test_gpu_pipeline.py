@@ -1,0 +1,98 @@
+"""End-to-end tests through the reference-facing Pipeline / extractor API on the GPU.  The first one
+is the reference's own tests/test_smoke_e2e.py restated against this package."""
+import sqlite3
+
+import numpy as np
+import pytest
+
+from test_boundary import _checkerboard, _write_shifted
+
+pytestmark = pytest.mark.gpu
+
+
+def test_smoke_e2e_dummy_extractor(tmp_path):
+    """tests/test_smoke_e2e.py:20-76: dummy extractor, PINHOLE, matching on, reconstruction off."""
+    from vit_colmap_b200.database import ColmapDatabase
+    from vit_colmap_b200.pipeline.run_pipeline import Pipeline
+    from vit_colmap_b200.utils.config import Config
+    images = _write_shifted(tmp_path)
+    db_path = tmp_path / "database.db"
+    config = Config()
+    config.extractor.extractor_type = "dummy"
+    config.camera.model = "PINHOLE"
+    config.do_matching = True
+    config.do_reconstruction = False
+    result = Pipeline(config).run(images, tmp_path / "out", db_path)
+    assert db_path.exists() and result is None
+    with ColmapDatabase.open_database(str(db_path)) as db:
+        assert ColmapDatabase.get_db_count(db, "num_cameras") >= 1
+        assert ColmapDatabase.get_db_count(db, "num_images") == 3
+        assert ColmapDatabase.get_db_count(db, "num_matched_image_pairs") >= 1
+        for image_id in (1, 2, 3):
+            assert db.exists_keypoints(image_id) and db.exists_descriptors(image_id)
+
+
+@pytest.fixture(scope="module")
+def vit_s():
+    from vit_colmap_b200.features.vit_extractor import ViTExtractor
+    return ViTExtractor(model_name="dinov2_vits14", num_keypoints=1024, descriptor_dim=128, synthetic_seed=0)
+
+
+def test_run_inference_contract(vit_s):
+    """tests/test_vit_integration.py:18-60: dtypes, column counts, equal lengths on a 476x644 image."""
+    rng = np.random.default_rng(0)
+    img = rng.integers(0, 256, (480, 650, 3), dtype=np.uint8)   # resized to 476x644 on the host
+    kps, desc = vit_s._run_inference(img)
+    assert kps.dtype == np.float32 and desc.dtype == np.uint8
+    assert kps.ndim == 2 and kps.shape[1] == 2 and desc.shape[1] == 128 and len(kps) == len(desc) > 0
+    assert kps[:, 0].min() >= 0 and kps[:, 0].max() <= 650 and kps[:, 1].max() <= 480
+
+
+def test_run_inference_matches_reference_postprocessing(vit_s):
+    """The extractor's output equals the oracle post-processing applied to the extractor's own patch
+    tokens (keypoints bit-exact apart from near-ties; descriptors within one quantisation step)."""
+    import torch
+    from oracle import extract_oracle as eo
+    rng = np.random.default_rng(1)
+    img = rng.integers(0, 256, (518, 518, 3), dtype=np.uint8)
+    kps, desc = vit_s._run_inference(img)
+    tokens = vit_s.model.forward_patch_tokens(torch.from_numpy(img).cuda()[None], bgr=True)[0].cpu()
+    fm = tokens.reshape(37, 37, -1).permute(2, 0, 1).contiguous()
+    ref = eo.dense_to_sparse(fm, (518, 518), (518, 518), 1024, 128, "harris",
+                             projection=vit_s.descriptor_projection.cpu())
+    a = {tuple(k) for k in kps.tolist()}
+    b = {tuple(k) for k in ref["keypoints"].tolist()}
+    assert len(a ^ b) <= 0.02 * len(b)          # near-ties of the score map (gap < 1e-5) may flip
+    pos = {tuple(k): i for i, k in enumerate(ref["keypoints"].tolist())}
+    common = [(i, pos[tuple(k)]) for i, k in enumerate(kps.tolist()) if tuple(k) in pos]
+    gi, ri = zip(*common)
+    diff = np.abs(desc[list(gi)].astype(int) - ref["desc_u8"][list(ri)].astype(int))
+    assert diff.max() <= 1
+
+
+def test_vit_pipeline_c1_checkerboards(tmp_path):
+    """Config C1 shape: 8 translated 518x518 checkerboards, ViT-S/14, exhaustive matching into the DB."""
+    import cv2
+    from vit_colmap_b200.database import ColmapDatabase
+    from vit_colmap_b200.features.vit_extractor import ViTExtractor
+    from vit_colmap_b200.matching import match_exhaustive
+    d = tmp_path / "images"
+    d.mkdir()
+    base = _checkerboard(518, 518, 37)
+    for i in range(8):
+        m = np.float32([[1, 0, 25 * i], [0, 1, 15 * i]])
+        cv2.imwrite(str(d / f"img_{i:03d}.png"), cv2.warpAffine(base, m, (518, 518)))
+    db_path = tmp_path / "db.db"
+    ex = ViTExtractor(model_name="dinov2_vits14", num_keypoints=2048, descriptor_dim=128, synthetic_seed=0, batch_size=4)
+    ex.extract(d, db_path, "SIMPLE_PINHOLE")
+    res = match_exhaustive(str(db_path))
+    assert len(res) == 28
+    con = sqlite3.connect(str(db_path))
+    assert con.execute("SELECT COUNT(*) FROM images").fetchone()[0] == 8
+    assert con.execute("SELECT COUNT(*) FROM keypoints").fetchone()[0] == 8
+    assert con.execute("SELECT COUNT(*) FROM matches").fetchone()[0] == 28
+    rows = con.execute("SELECT rows, cols FROM descriptors").fetchall()
+    assert all(c == 128 and r > 0 for r, c in rows)
+    with ColmapDatabase.open_database(str(db_path)) as db:
+        k = db.read_keypoints(1)
+        assert k.dtype == np.float32 and k.shape[1] == 2

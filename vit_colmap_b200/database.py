@@ -365,6 +365,12 @@ class ColmapDatabase:
     def commit(self) -> None:
         pass
 
+    def close(self) -> None:
+        """Extension: release the SQLite handle (the reference leaves this to garbage collection)."""
+        if getattr(self, "db", None) is not None:
+            self.db.close()
+            self.db = None
+
     @staticmethod
     @contextmanager
     def open_database(db_path: str):

@@ -135,3 +135,26 @@ class VitBackbone:
         """L*(24 T C^2 + 4 T^2 C) + 2 HW 588 C."""
         C, L, T = self.embed_dim, self.depth, gh * gw + 1
         return L * (24.0 * T * C * C + 4.0 * T * T * C) + 2.0 * gh * gw * 588 * C
+
+
+def synthetic_state_dict(name: str, seed: int = 0, depth: Optional[int] = None):
+    """Seeded random-init weights in the hub model's key layout (no checkpoint can be downloaded in
+    the build / benchmark environment): N(0, 0.02^2) linears, position and cls embeddings, LayerNorm
+    and LayerScale scales near 1.  Throughput does not depend on the values."""
+    import torch
+    C, L, _ = CONFIGS[name]
+    L = depth or L
+    g = torch.Generator().manual_seed(seed)
+    n = lambda *s, std=0.02: torch.randn(*s, generator=g) * std  # noqa: E731
+    sd = {"cls_token": n(1, 1, C), "pos_embed": n(1, 1 + BASE_GRID * BASE_GRID, C),
+          "patch_embed.proj.weight": n(C, 3, PATCH, PATCH), "patch_embed.proj.bias": n(C),
+          "norm.weight": 1 + n(C, std=0.1), "norm.bias": n(C, std=0.1)}
+    for i in range(L):
+        p = f"blocks.{i}."
+        sd.update({p + "norm1.weight": 1 + n(C, std=0.1), p + "norm1.bias": n(C, std=0.1),
+                   p + "attn.qkv.weight": n(3 * C, C, std=0.05), p + "attn.qkv.bias": n(3 * C),
+                   p + "attn.proj.weight": n(C, C), p + "attn.proj.bias": n(C), p + "ls1.gamma": 1 + n(C, std=0.1),
+                   p + "norm2.weight": 1 + n(C, std=0.1), p + "norm2.bias": n(C, std=0.1),
+                   p + "mlp.fc1.weight": n(4 * C, C), p + "mlp.fc1.bias": n(4 * C),
+                   p + "mlp.fc2.weight": n(C, 4 * C), p + "mlp.fc2.bias": n(C), p + "ls2.gamma": 1 + n(C, std=0.1)})
+    return sd
