@@ -39,6 +39,35 @@ __device__ __forceinline__ float ex2(float x) {
   return y;
 }
 
+// Blackwell packed fp32 pairs (FFMA2 / FADD2 / FMUL2) and the 3-input maximum (FMNMX3)
+__device__ __forceinline__ float2 ffma2(float2 a, float2 b, float2 c) {
+  uint64_t d;
+  asm("fma.rn.f32x2 %0, %1, %2, %3;"
+      : "=l"(d)
+      : "l"(*reinterpret_cast<uint64_t*>(&a)), "l"(*reinterpret_cast<uint64_t*>(&b)),
+        "l"(*reinterpret_cast<uint64_t*>(&c)));
+  return *reinterpret_cast<float2*>(&d);
+}
+__device__ __forceinline__ float2 fadd2(float2 a, float2 b) {
+  uint64_t d;
+  asm("add.rn.f32x2 %0, %1, %2;"
+      : "=l"(d)
+      : "l"(*reinterpret_cast<uint64_t*>(&a)), "l"(*reinterpret_cast<uint64_t*>(&b)));
+  return *reinterpret_cast<float2*>(&d);
+}
+__device__ __forceinline__ float2 fmul2(float2 a, float2 b) {
+  uint64_t d;
+  asm("mul.rn.f32x2 %0, %1, %2;"
+      : "=l"(d)
+      : "l"(*reinterpret_cast<uint64_t*>(&a)), "l"(*reinterpret_cast<uint64_t*>(&b)));
+  return *reinterpret_cast<float2*>(&d);
+}
+__device__ __forceinline__ float fmax3(float a, float b, float c) {
+  float d;
+  asm("max.f32 %0, %1, %2, %3;" : "=f"(d) : "f"(a), "f"(b), "f"(c));
+  return d;
+}
+
 __device__ __forceinline__ uint32_t pack_bf16(float a, float b) {
   __nv_bfloat162 v = __floats2bfloat162_rn(a, b);
   return *reinterpret_cast<uint32_t*>(&v);
@@ -162,71 +191,94 @@ vit_attention_kernel(const __grid_constant__ CUtensorMap map_qkv, const AttnPara
     const uint32_t t_o = tmem_base + (static_cast<uint32_t>(quarter * 32) << 16) + 256 + w * 64;
     const float sc = p.scale * 1.4426950408889634f;  // scores are handled in the exp2 domain
     uint8_t* prow = sP_gen + w * kPBytes + r * 128;
-    float o[kHd];
+    float2 o[kHd / 2];
 #pragma unroll
-    for (int e = 0; e < kHd; ++e) o[e] = 0.f;
+    for (int e = 0; e < kHd / 2; ++e) o[e] = make_float2(0.f, 0.f);
     float m_run = -1e30f, l_run = 0.f;
+    const float2 sc2 = make_float2(sc, sc);
     for (int j = 0; j < nkv; ++j) {
       const int valid = min(kTile, p.T - j * kTile);  // keys of this tile inside the image
-      mbar_wait(s_full(w), j & 1);
-      tc_fence_after();
-      // pass 1: row maximum
-      float mx = -1e30f;
-#pragma unroll 1
-      for (int c = 0; c < 4; ++c) {
-        uint32_t vr[32];
-        tmem_ld_32x32(t_s + c * 32, vr);
-        tmem_wait_ld();
-#pragma unroll
-        for (int e = 0; e < 32; ++e) {
-          const float v = __uint_as_float(vr[e]);
-          if (c * 32 + e < valid) mx = fmaxf(mx, v);
-        }
-      }
-      const float m_new = fmaxf(m_run, mx * sc);
-      const float alpha = ex2(m_run - m_new);
-      m_run = m_new;
-      // fold the previous tile's P V into the running output, then rescale to the new maximum
+      // fold the previous tile's P V into the running output (both are relative to m_run)
       if (j > 0) {
         mbar_wait(o_full(w), (j - 1) & 1);
         tc_fence_after();
+        uint32_t va[32], vb[32];
+        tmem_ld_32x32(t_o, va);
+        tmem_ld_32x32(t_o + 32, vb);
+        tmem_wait_ld();
 #pragma unroll
-        for (int c = 0; c < 2; ++c) {
-          uint32_t vr[32];
-          tmem_ld_32x32(t_o + c * 32, vr);
-          tmem_wait_ld();
-#pragma unroll
-          for (int e = 0; e < 32; ++e) o[c * 32 + e] = (o[c * 32 + e] + __uint_as_float(vr[e])) * alpha;
+        for (int e = 0; e < 16; ++e) {
+          o[e] = fadd2(o[e], make_float2(__uint_as_float(va[2 * e]), __uint_as_float(va[2 * e + 1])));
+          o[16 + e] = fadd2(o[16 + e], make_float2(__uint_as_float(vb[2 * e]), __uint_as_float(vb[2 * e + 1])));
         }
       }
+      mbar_wait(s_full(w), j & 1);
+      // the two warpgroups take turns: while one runs its softmax, the tensor core works for the
+      // other (P V of its last tile, S of its next) instead of both stalling in lockstep
+      if (nw == 2) {
+        if (w == 1) mbar_wait(p_full(0), j & 1);
+        else if (j > 0) mbar_wait(p_full(1), (j - 1) & 1);
+      }
+      tc_fence_after();
+      // pass 1: row maximum
+      float mx0 = -1e30f, mx1 = -1e30f;
+#pragma unroll 1
+      for (int c = 0; c < 4; c += 2) {
+        uint32_t va[32], vb[32];
+        tmem_ld_32x32(t_s + c * 32, va);
+        tmem_ld_32x32(t_s + c * 32 + 32, vb);
+        tmem_wait_ld();
+        if (valid < kTile) {
+#pragma unroll
+          for (int e = 0; e < 32; ++e) {
+            if (c * 32 + e >= valid) va[e] = 0xFF800000u;       // -inf
+            if (c * 32 + 32 + e >= valid) vb[e] = 0xFF800000u;
+          }
+        }
+#pragma unroll
+        for (int e = 0; e < 32; e += 2) {
+          mx0 = fmax3(mx0, __uint_as_float(va[e]), __uint_as_float(va[e + 1]));
+          mx1 = fmax3(mx1, __uint_as_float(vb[e]), __uint_as_float(vb[e + 1]));
+        }
+      }
+      const float m_new = fmaxf(m_run, fmaxf(mx0, mx1) * sc);
+      const float alpha = ex2(m_run - m_new);
+      m_run = m_new;
+      if (!__all_sync(0xffffffffu, alpha == 1.0f)) {  // rare once the maxima have settled
+        const float2 a2 = make_float2(alpha, alpha);
+#pragma unroll
+        for (int e = 0; e < kHd / 2; ++e) o[e] = fmul2(o[e], a2);
+      }
       // pass 2: probabilities -> bf16 operand tile in shared memory
-      float sum = 0.f;
+      float2 sum2 = make_float2(0.f, 0.f);
+      const float2 nm2 = make_float2(-m_new, -m_new);
 #pragma unroll 1
       for (int c = 0; c < 4; ++c) {
         uint32_t vr[32];
         tmem_ld_32x32(t_s + c * 32, vr);
         tmem_wait_ld();
-        float pv[32];
+        uint32_t pk[16];
 #pragma unroll
-        for (int e = 0; e < 32; ++e) {
-          const float x = ex2(fmaf(__uint_as_float(vr[e]), sc, -m_new));
-          pv[e] = (c * 32 + e < valid) ? x : 0.f;
-          sum += pv[e];
+        for (int e = 0; e < 16; ++e) {
+          float2 x = ffma2(make_float2(__uint_as_float(vr[2 * e]), __uint_as_float(vr[2 * e + 1])), sc2, nm2);
+          x.x = ex2(x.x);
+          x.y = ex2(x.y);
+          if (valid < kTile) {
+            if (c * 32 + 2 * e >= valid) x.x = 0.f;
+            if (c * 32 + 2 * e + 1 >= valid) x.y = 0.f;
+          }
+          sum2 = fadd2(sum2, x);
+          pk[e] = pack_bf16(x.x, x.y);
         }
         // chunk c covers keys [32c, 32c+32): half c>>1, 16-byte chunks (c&1)*4 .. +3 of the row
         uint8_t* half = prow + (c >> 1) * (kPBytes / 2);
 #pragma unroll
         for (int g = 0; g < 4; ++g) {
-          uint4 pk;
-          pk.x = pack_bf16(pv[8 * g + 0], pv[8 * g + 1]);
-          pk.y = pack_bf16(pv[8 * g + 2], pv[8 * g + 3]);
-          pk.z = pack_bf16(pv[8 * g + 4], pv[8 * g + 5]);
-          pk.w = pack_bf16(pv[8 * g + 6], pv[8 * g + 7]);
           const int chunk = ((c & 1) * 4 + g) ^ (r & 7);
-          *reinterpret_cast<uint4*>(half + chunk * 16) = pk;
+          *reinterpret_cast<uint4*>(half + chunk * 16) = make_uint4(pk[4 * g], pk[4 * g + 1], pk[4 * g + 2], pk[4 * g + 3]);
         }
       }
-      l_run = l_run * alpha + sum;
+      l_run = l_run * alpha + (sum2.x + sum2.y);
       fence_proxy_async_smem();
       tc_fence_before();
       mbar_arrive(p_full(w));
@@ -234,13 +286,16 @@ vit_attention_kernel(const __grid_constant__ CUtensorMap map_qkv, const AttnPara
     // last tile's P V
     mbar_wait(o_full(w), (nkv - 1) & 1);
     tc_fence_after();
-#pragma unroll
-    for (int c = 0; c < 2; ++c) {
-      uint32_t vr[32];
-      tmem_ld_32x32(t_o + c * 32, vr);
+    {
+      uint32_t va[32], vb[32];
+      tmem_ld_32x32(t_o, va);
+      tmem_ld_32x32(t_o + 32, vb);
       tmem_wait_ld();
 #pragma unroll
-      for (int e = 0; e < 32; ++e) o[c * 32 + e] += __uint_as_float(vr[e]);
+      for (int e = 0; e < 16; ++e) {
+        o[e] = fadd2(o[e], make_float2(__uint_as_float(va[2 * e]), __uint_as_float(va[2 * e + 1])));
+        o[16 + e] = fadd2(o[16 + e], make_float2(__uint_as_float(vb[2 * e]), __uint_as_float(vb[2 * e + 1])));
+      }
     }
     const int t = q0 + w * kTile + r;
     if (t < p.T) {
@@ -249,10 +304,10 @@ vit_attention_kernel(const __grid_constant__ CUtensorMap map_qkv, const AttnPara
 #pragma unroll
       for (int g = 0; g < 8; ++g) {
         uint4 pk;
-        pk.x = pack_bf16(o[8 * g + 0] * inv, o[8 * g + 1] * inv);
-        pk.y = pack_bf16(o[8 * g + 2] * inv, o[8 * g + 3] * inv);
-        pk.z = pack_bf16(o[8 * g + 4] * inv, o[8 * g + 5] * inv);
-        pk.w = pack_bf16(o[8 * g + 6] * inv, o[8 * g + 7] * inv);
+        pk.x = pack_bf16(o[4 * g + 0].x * inv, o[4 * g + 0].y * inv);
+        pk.y = pack_bf16(o[4 * g + 1].x * inv, o[4 * g + 1].y * inv);
+        pk.z = pack_bf16(o[4 * g + 2].x * inv, o[4 * g + 2].y * inv);
+        pk.w = pack_bf16(o[4 * g + 3].x * inv, o[4 * g + 3].y * inv);
         dst[g] = pk;
       }
     }
