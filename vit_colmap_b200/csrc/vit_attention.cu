@@ -7,14 +7,19 @@
 //           warps have published P_w (bf16, written to shared memory in the K-major swizzled
 //           operand layout), O_w^(j) = P_w V_j (M128 N64 K128; V is consumed as an MN-major operand
 //           exactly as TMA delivered it, so no transposed copy of V exists anywhere)
-//   warp 2  TMEM allocator (S_0, S_1: 2 x 128 columns, O tiles: 2 x 64 columns)
-//   warps 4-7 / 8-11  softmax warpgroup of query tile 0 / 1: thread = one query row.  Online
-//           softmax in the exp2 domain; the running output row lives in 64 registers and is rescaled
-//           when the row maximum moves, so TMEM is never read-modified-written.
+//           and allocates TMEM (S_0, S_1: 2 x 128 columns, O_0, O_1: 2 x 64 columns).  O accumulates
+//           in TMEM across the key tiles.
+//   warps 2-5 / 6-9  softmax warpgroup of query tile 0 / 1: thread = one query row.  The 128 scores
+//           of a tile are pulled into registers with one round of tcgen05.ld (TMEM latency is paid
+//           once per tile), online softmax in the exp2 domain with a lazily updated reference
+//           maximum: O and the row sum are only rescaled when the maximum grew by more than 2^8
+//           (probabilities stay <= 256, exact in the final normalisation), so the TMEM
+//           read-modify-write of O is rare.
 // The two warpgroups share every K/V tile and keep the tensor core busy for each other.
 #include "vit_kernels.cuh"
 
 #include <math.h>
+#include <stdlib.h>
 
 #include "vc_ptx.cuh"
 
@@ -26,7 +31,7 @@ constexpr int kTile = 128, kHd = 64, kKvStages = 3;
 constexpr int kQBytes = kTile * kHd * 2;          // 16 KB
 constexpr int kKvBytes = 2 * kTile * kHd * 2;     // K + V of one stage, 32 KB
 constexpr int kPBytes = kTile * kTile * 2;        // 32 KB per warpgroup
-constexpr int kThreads = 384;
+constexpr int kThreads = 320;  // warp 0 TMA, warp 1 MMA + TMEM alloc, warps 2-9 softmax
 constexpr int kTmemCols = 512;
 constexpr int kSmemBytes = 2 * kQBytes + kKvStages * kKvBytes + 2 * kPBytes + 1024 + 256;
 
@@ -73,6 +78,110 @@ __device__ __forceinline__ uint32_t pack_bf16(float a, float b) {
   return *reinterpret_cast<uint32_t*>(&v);
 }
 
+
+// One 128-key tile of the online softmax for one query row.  kMasked is only instantiated for the
+// last, partial key tile, so full tiles carry no per-element selects.
+template <bool kMasked>
+__device__ __forceinline__ void softmax_tile(uint32_t t_s, uint32_t t_o, uint8_t* prow, int r, int valid,
+                                             float sc, bool have_o, float& m_ref, float& l_run) {
+  // Software pipeline over TMEM: every tcgen05.ld is issued one step ahead of the arithmetic that
+  // consumes it (tcgen05.wait::ld waits for all outstanding loads, so the order is ld-next,
+  // compute-current, wait).  Pass 1 (maximum) reads the tile as two 64-column halves, pass 2
+  // (probabilities) as four 32-column chunks.
+  auto mask = [&](uint32_t (&x)[32], int col0) {
+    if (kMasked) {
+#pragma unroll
+      for (int e = 0; e < 32; ++e)
+        if (col0 + e >= valid) x[e] = 0xFF800000u;  // -inf
+    }
+  };
+  float mx[4] = {-1e30f, -1e30f, -1e30f, -1e30f};
+  auto fold_max = [&](const uint32_t (&x)[32]) {
+#pragma unroll
+    for (int e = 0; e < 32; e += 8) {
+#pragma unroll
+      for (int a = 0; a < 4; ++a)
+        mx[a] = fmax3(mx[a], __uint_as_float(x[e + 2 * a]), __uint_as_float(x[e + 2 * a + 1]));
+    }
+  };
+  uint32_t a0[32], a1[32], b0[32], b1[32];
+  tmem_ld_32x32(t_s, a0);
+  tmem_ld_32x32(t_s + 32, a1);
+  tmem_wait_ld();
+  tmem_ld_32x32(t_s + 64, b0);
+  tmem_ld_32x32(t_s + 96, b1);
+  mask(a0, 0);
+  mask(a1, 32);
+  fold_max(a0);
+  fold_max(a1);
+  tmem_wait_ld();
+  tmem_ld_32x32(t_s, a0);  // first chunk of pass 2, in flight during the rest of pass 1
+  mask(b0, 64);
+  mask(b1, 96);
+  fold_max(b0);
+  fold_max(b1);
+  const float m_tile = fmaxf(fmaxf(mx[0], mx[1]), fmaxf(mx[2], mx[3])) * sc;
+  // lazy reference maximum: move it (and rescale O, l) only when it is more than 2^8 behind
+  if (__any_sync(0xffffffffu, m_tile > m_ref + 8.0f)) {
+    const float m_new = fmaxf(m_ref, m_tile);
+    const float alpha = ex2(m_ref - m_new);
+    m_ref = m_new;
+    l_run *= alpha;
+    if (have_o) {
+      const float2 a2 = make_float2(alpha, alpha);
+      tmem_ld_32x32(t_o, b0);
+      tmem_ld_32x32(t_o + 32, b1);
+      tmem_wait_ld();
+#pragma unroll
+      for (int e = 0; e < 32; e += 2) {
+        float2 t = fmul2(make_float2(__uint_as_float(b0[e]), __uint_as_float(b0[e + 1])), a2);
+        b0[e] = __float_as_uint(t.x);
+        b0[e + 1] = __float_as_uint(t.y);
+        t = fmul2(make_float2(__uint_as_float(b1[e]), __uint_as_float(b1[e + 1])), a2);
+        b1[e] = __float_as_uint(t.x);
+        b1[e + 1] = __float_as_uint(t.y);
+      }
+      tmem_st_32x32(t_o, b0);
+      tmem_st_32x32(t_o + 32, b1);
+      tmem_wait_st();
+    }
+  }
+  const float2 sc2 = make_float2(sc, sc), nm2 = make_float2(-m_ref, -m_ref);
+  float2 sum[2] = {make_float2(0.f, 0.f), make_float2(0.f, 0.f)};
+  auto emit = [&](uint32_t (&x)[32], int c) {
+    mask(x, c * 32);
+    uint32_t pk[16];
+#pragma unroll
+    for (int e = 0; e < 16; ++e) {
+      float2 y = ffma2(make_float2(__uint_as_float(x[2 * e]), __uint_as_float(x[2 * e + 1])), sc2, nm2);
+      y.x = ex2(y.x);  // masked keys: exp2(-inf) = 0
+      y.y = ex2(y.y);
+      sum[e & 1] = fadd2(sum[e & 1], y);
+      pk[e] = pack_bf16(y.x, y.y);
+    }
+    // chunk c covers keys [32c, 32c+32): half c>>1, 16-byte chunks (c&1)*4 .. +3 of the swizzled row
+    uint8_t* half = prow + (c >> 1) * (kPBytes / 2);
+#pragma unroll
+    for (int g = 0; g < 4; ++g) {
+      const int chunk = ((c & 1) * 4 + g) ^ (r & 7);
+      *reinterpret_cast<uint4*>(half + chunk * 16) =
+          make_uint4(pk[4 * g], pk[4 * g + 1], pk[4 * g + 2], pk[4 * g + 3]);
+    }
+  };
+  tmem_wait_ld();
+  tmem_ld_32x32(t_s + 32, a1);
+  emit(a0, 0);
+  tmem_wait_ld();
+  tmem_ld_32x32(t_s + 64, a0);
+  emit(a1, 1);
+  tmem_wait_ld();
+  tmem_ld_32x32(t_s + 96, a1);
+  emit(a0, 2);
+  tmem_wait_ld();
+  emit(a1, 3);
+  l_run += (sum[0].x + sum[0].y) + (sum[1].x + sum[1].y);
+}
+
 }  // namespace
 
 __global__ void __launch_bounds__(kThreads, 1)
@@ -105,8 +214,8 @@ vit_attention_kernel(const __grid_constant__ CUtensorMap map_qkv, const AttnPara
   const int nw = (q0 + kTile < p.T) ? 2 : 1;
   const int nkv = (p.T + kTile - 1) / kTile;
 
-  if (warp == 0 && lane == 0) tma_prefetch_desc(&map_qkv);
-  if (warp == 1 && lane == 0) {
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&map_qkv);
     mbar_init(q_full, 1);
     for (int s = 0; s < kKvStages; ++s) {
       mbar_init(kv_full(s), 1);
@@ -119,7 +228,7 @@ vit_attention_kernel(const __grid_constant__ CUtensorMap map_qkv, const AttnPara
     }
     fence_mbar_init();
   }
-  if (warp == 2) {
+  if (warp == 1) {
     tmem_alloc(smem_u32(tmem_slot), kTmemCols);
     tmem_relinquish();
   }
@@ -136,7 +245,7 @@ vit_attention_kernel(const __grid_constant__ CUtensorMap map_qkv, const AttnPara
     for (int j = 0; j < nkv; ++j) {
       const int s = j % kKvStages;
       const uint32_t ph = (j / kKvStages) & 1;
-      mbar_wait(kv_empty(s), ph ^ 1);
+      mbar_wait_sleep(kv_empty(s), ph ^ 1, 256);
       mbar_arrive_expect_tx(kv_full(s), kKvBytes);
       tma_load_3d(sKV + s * kKvBytes, &map_qkv, kv_full(s), C + head * kHd, j * kTile, img);
       tma_load_3d(sKV + s * kKvBytes + kKvBytes / 2, &map_qkv, kv_full(s), 2 * C + head * kHd, j * kTile,
@@ -167,170 +276,95 @@ vit_attention_kernel(const __grid_constant__ CUtensorMap map_qkv, const AttnPara
         tc_fence_after();
       }
       for (int w = 0; w < nw; ++w) {
-        mbar_wait(p_full(w), j & 1);
+        mbar_wait_sleep(p_full(w), j & 1, 32);
         tc_fence_after();
-        // O_w^(j) = P_w (128 x 128, two 64-key halves, K-major) * V_j (128 keys x 64, MN-major)
+        // O_w += P_w (128 x 128, two 64-key halves, K-major) * V_j (128 keys x 64, MN-major)
         const uint32_t pw = sP + w * kPBytes;
         const uint64_t dv = umma_desc_k_sw128(sKV + s * kKvBytes + kKvBytes / 2);
 #pragma unroll
         for (int k = 0; k < kTile / 16; ++k) {
           const uint64_t dp = umma_desc_k_sw128(pw + (k >> 2) * (kPBytes / 2)) + 2 * (k & 3);
-          tc_mma_bf16(tmem_base + 256 + w * 64, dp, dv + 128 * k, idesc_o, k != 0);
+          tc_mma_bf16(tmem_base + 256 + w * 64, dp, dv + 128 * k, idesc_o, (j | k) != 0);
         }
-        tc_commit(o_full(w));
-        if (more) issue_s(w, s1);
+        if (!more) tc_commit(o_full(w));
+        if (more) issue_s(w, s1);   // its commit also covers the P V above: S_w ready => O_w up to date
       }
       tc_commit(kv_empty(s));
     }
-  } else if (warp >= 4 && (warp - 4) / 4 < nw) {
+  } else if (warp >= 2 && (warp - 2) / 4 < nw) {
     // ------------------------------------------------------------ softmax warpgroups
-    const int w = (warp - 4) >> 2;
-    const int quarter = warp & 3;
+    const int w = (warp - 2) >> 2;
+    const int quarter = warp & 3;       // TMEM lane quarter a warp may touch = warp id % 4
     const int r = quarter * 32 + lane;  // row inside the query tile == TMEM lane
     const uint32_t t_s = tmem_base + (static_cast<uint32_t>(quarter * 32) << 16) + w * 128;
     const uint32_t t_o = tmem_base + (static_cast<uint32_t>(quarter * 32) << 16) + 256 + w * 64;
     const float sc = p.scale * 1.4426950408889634f;  // scores are handled in the exp2 domain
     uint8_t* prow = sP_gen + w * kPBytes + r * 128;
-    float2 o[kHd / 2];
-#pragma unroll
-    for (int e = 0; e < kHd / 2; ++e) o[e] = make_float2(0.f, 0.f);
-    float m_run = -1e30f, l_run = 0.f;
-    const float2 sc2 = make_float2(sc, sc);
+    float m_ref = -1e30f, l_run = 0.f;
     for (int j = 0; j < nkv; ++j) {
       const int valid = min(kTile, p.T - j * kTile);  // keys of this tile inside the image
-      // fold the previous tile's P V into the running output (both are relative to m_run)
-      if (j > 0) {
-        mbar_wait(o_full(w), (j - 1) & 1);
-        tc_fence_after();
-        uint32_t va[32], vb[32];
-        tmem_ld_32x32(t_o, va);
-        tmem_ld_32x32(t_o + 32, vb);
-        tmem_wait_ld();
-#pragma unroll
-        for (int e = 0; e < 16; ++e) {
-          o[e] = fadd2(o[e], make_float2(__uint_as_float(va[2 * e]), __uint_as_float(va[2 * e + 1])));
-          o[16 + e] = fadd2(o[16 + e], make_float2(__uint_as_float(vb[2 * e]), __uint_as_float(vb[2 * e + 1])));
-        }
-      }
-      mbar_wait(s_full(w), j & 1);
-      // the two warpgroups take turns: while one runs its softmax, the tensor core works for the
-      // other (P V of its last tile, S of its next) instead of both stalling in lockstep
-      if (nw == 2) {
-        if (w == 1) mbar_wait(p_full(0), j & 1);
-        else if (j > 0) mbar_wait(p_full(1), (j - 1) & 1);
+      mbar_wait_sleep(s_full(w), j & 1, 32);
+      if (p.alternate && nw == 2) {
+        // optional turn-taking: one warpgroup runs its softmax while the tensor core serves the other
+        if (w == 1) mbar_wait_sleep(p_full(0), j & 1, 64);
+        else if (j > 0) mbar_wait_sleep(p_full(1), (j - 1) & 1, 64);
       }
       tc_fence_after();
-      // pass 1: row maximum
-      float mx0 = -1e30f, mx1 = -1e30f;
-#pragma unroll 1
-      for (int c = 0; c < 4; c += 2) {
-        uint32_t va[32], vb[32];
-        tmem_ld_32x32(t_s + c * 32, va);
-        tmem_ld_32x32(t_s + c * 32 + 32, vb);
-        tmem_wait_ld();
-        if (valid < kTile) {
-#pragma unroll
-          for (int e = 0; e < 32; ++e) {
-            if (c * 32 + e >= valid) va[e] = 0xFF800000u;       // -inf
-            if (c * 32 + 32 + e >= valid) vb[e] = 0xFF800000u;
-          }
-        }
-#pragma unroll
-        for (int e = 0; e < 32; e += 2) {
-          mx0 = fmax3(mx0, __uint_as_float(va[e]), __uint_as_float(va[e + 1]));
-          mx1 = fmax3(mx1, __uint_as_float(vb[e]), __uint_as_float(vb[e + 1]));
-        }
-      }
-      const float m_new = fmaxf(m_run, fmaxf(mx0, mx1) * sc);
-      const float alpha = ex2(m_run - m_new);
-      m_run = m_new;
-      if (!__all_sync(0xffffffffu, alpha == 1.0f)) {  // rare once the maxima have settled
-        const float2 a2 = make_float2(alpha, alpha);
-#pragma unroll
-        for (int e = 0; e < kHd / 2; ++e) o[e] = fmul2(o[e], a2);
-      }
-      // pass 2: probabilities -> bf16 operand tile in shared memory
-      float2 sum2 = make_float2(0.f, 0.f);
-      const float2 nm2 = make_float2(-m_new, -m_new);
-#pragma unroll 1
-      for (int c = 0; c < 4; ++c) {
-        uint32_t vr[32];
-        tmem_ld_32x32(t_s + c * 32, vr);
-        tmem_wait_ld();
-        uint32_t pk[16];
-#pragma unroll
-        for (int e = 0; e < 16; ++e) {
-          float2 x = ffma2(make_float2(__uint_as_float(vr[2 * e]), __uint_as_float(vr[2 * e + 1])), sc2, nm2);
-          x.x = ex2(x.x);
-          x.y = ex2(x.y);
-          if (valid < kTile) {
-            if (c * 32 + 2 * e >= valid) x.x = 0.f;
-            if (c * 32 + 2 * e + 1 >= valid) x.y = 0.f;
-          }
-          sum2 = fadd2(sum2, x);
-          pk[e] = pack_bf16(x.x, x.y);
-        }
-        // chunk c covers keys [32c, 32c+32): half c>>1, 16-byte chunks (c&1)*4 .. +3 of the row
-        uint8_t* half = prow + (c >> 1) * (kPBytes / 2);
-#pragma unroll
-        for (int g = 0; g < 4; ++g) {
-          const int chunk = ((c & 1) * 4 + g) ^ (r & 7);
-          *reinterpret_cast<uint4*>(half + chunk * 16) = make_uint4(pk[4 * g], pk[4 * g + 1], pk[4 * g + 2], pk[4 * g + 3]);
-        }
-      }
-      l_run = l_run * alpha + (sum2.x + sum2.y);
+      if (valid == kTile)
+        softmax_tile<false>(t_s, t_o, prow, r, valid, sc, j > 0, m_ref, l_run);
+      else
+        softmax_tile<true>(t_s, t_o, prow, r, valid, sc, j > 0, m_ref, l_run);
       fence_proxy_async_smem();
       tc_fence_before();
       mbar_arrive(p_full(w));
     }
-    // last tile's P V
-    mbar_wait(o_full(w), (nkv - 1) & 1);
+    mbar_wait_sleep(o_full(w), 0, 32);
     tc_fence_after();
-    {
-      uint32_t va[32], vb[32];
-      tmem_ld_32x32(t_o, va);
-      tmem_ld_32x32(t_o + 32, vb);
-      tmem_wait_ld();
-#pragma unroll
-      for (int e = 0; e < 16; ++e) {
-        o[e] = fadd2(o[e], make_float2(__uint_as_float(va[2 * e]), __uint_as_float(va[2 * e + 1])));
-        o[16 + e] = fadd2(o[16 + e], make_float2(__uint_as_float(vb[2 * e]), __uint_as_float(vb[2 * e + 1])));
-      }
-    }
     const int t = q0 + w * kTile + r;
-    if (t < p.T) {
-      const float inv = 1.0f / l_run;
-      uint4* dst = reinterpret_cast<uint4*>(p.out + ((size_t)img * p.T + t) * C + head * kHd);
+    const float inv = 1.0f / l_run;
+    uint4* dst = reinterpret_cast<uint4*>(p.out + ((size_t)img * p.T + t) * C + head * kHd);
 #pragma unroll
-      for (int g = 0; g < 8; ++g) {
-        uint4 pk;
-        pk.x = pack_bf16(o[4 * g + 0].x * inv, o[4 * g + 0].y * inv);
-        pk.y = pack_bf16(o[4 * g + 1].x * inv, o[4 * g + 1].y * inv);
-        pk.z = pack_bf16(o[4 * g + 2].x * inv, o[4 * g + 2].y * inv);
-        pk.w = pack_bf16(o[4 * g + 3].x * inv, o[4 * g + 3].y * inv);
-        dst[g] = pk;
+    for (int c = 0; c < 2; ++c) {
+      uint32_t ov[32];
+      tmem_ld_32x32(t_o + c * 32, ov);
+      tmem_wait_ld();
+      if (t < p.T) {
+#pragma unroll
+        for (int g = 0; g < 4; ++g) {
+          uint4 pk;
+          pk.x = pack_bf16(__uint_as_float(ov[8 * g + 0]) * inv, __uint_as_float(ov[8 * g + 1]) * inv);
+          pk.y = pack_bf16(__uint_as_float(ov[8 * g + 2]) * inv, __uint_as_float(ov[8 * g + 3]) * inv);
+          pk.z = pack_bf16(__uint_as_float(ov[8 * g + 4]) * inv, __uint_as_float(ov[8 * g + 5]) * inv);
+          pk.w = pack_bf16(__uint_as_float(ov[8 * g + 6]) * inv, __uint_as_float(ov[8 * g + 7]) * inv);
+          dst[c * 4 + g] = pk;
+        }
       }
     }
   }
 
   tc_fence_before();
   __syncthreads();
-  if (warp == 2) tmem_dealloc(tmem_base, kTmemCols);
+  if (warp == 1) tmem_dealloc(tmem_base, kTmemCols);
 }
 
 int attn_smem_bytes() { return kSmemBytes; }
 
 cudaError_t launch_attention(const CUtensorMap& map_qkv, const AttnParams& p, cudaStream_t stream) {
   static bool configured = false;
+  static int alternate = 0;
   if (!configured) {
     cudaError_t e = cudaFuncSetAttribute(vit_attention_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                          kSmemBytes);
     if (e != cudaSuccess) return e;
+    const char* env = getenv("VC_ATTN_ALTERNATE");  // tuning knob, see DESIGN.md
+    if (env) alternate = atoi(env);
     configured = true;
   }
   if (p.B <= 0 || p.T <= 0) return cudaSuccess;
+  AttnParams q = p;
+  q.alternate = alternate;
   const int q_pairs = (p.T + 2 * kTile - 1) / (2 * kTile);
-  vit_attention_kernel<<<p.B * p.heads * q_pairs, kThreads, kSmemBytes, stream>>>(map_qkv, p);
+  vit_attention_kernel<<<p.B * p.heads * q_pairs, kThreads, kSmemBytes, stream>>>(map_qkv, q);
   return cudaGetLastError();
 }
 

@@ -166,7 +166,7 @@ vit_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant
       const int m = tm * BM + q * 32 + lane;
       const bool row_ok = m < p.M;
       const uint32_t as = it & 1, aph = (it >> 1) & 1;
-      mbar_wait(tfull_bar(as), aph);
+      mbar_wait_sleep(tfull_bar(as), aph, 32);
       tc_fence_after();
       const uint32_t t_addr = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + as * BN;
       size_t out_row = (size_t)m;
