@@ -1,0 +1,235 @@
+"""Multi-GPU orchestration of the hot path: one process per GPU (torchrun), `torch.distributed` for
+the plumbing (NCCL on the GPUs, gloo in the CPU tests).
+
+The reference's only parallelism on this path is independent image pairs handed to per-GPU worker
+threads, with descriptors re-uploaded from the host per pair
+(COLMAP/controllers/feature_matching_utils.cc:249-283, SIFTGPU/SiftMatchCU.cpp:99-112).  Here:
+  * extraction shards by image (contiguous ranges of the sorted file list, vit_extractor.py:684-687);
+    the PCA projection fitted on the first image (vit_extractor.py:601-639) is broadcast from its
+    owner so the result does not depend on the sharding;
+  * ONE all-gather makes every rank's descriptors resident everywhere;
+  * matching shards by pair block (pairing.shard_blocks, collective-free, same table on every rank);
+  * match lists are gathered to rank 0, the single database writer (as in the reference,
+    feature_matching_utils.cc:480-500).
+The compute calls are injected (`match_fn`), so the host logic is testable without a GPU.
+"""
+from __future__ import annotations
+
+from typing import Callable, Dict, List, Optional, Sequence, Tuple
+
+import numpy as np
+
+from .pairing import ExhaustivePairGenerator, shard_blocks
+
+
+def _dist():
+    import torch.distributed as dist
+    return dist
+
+
+def world_info() -> Tuple[int, int]:
+    dist = _dist()
+    if dist.is_available() and dist.is_initialized():
+        return dist.get_rank(), dist.get_world_size()
+    return 0, 1
+
+
+def shard_range(n: int, rank: int, world: int) -> Tuple[int, int]:
+    """Contiguous split of n sorted images; the first ranks take the remainder."""
+    base, rem = divmod(n, world)
+    lo = rank * base + min(rank, rem)
+    return lo, lo + base + (1 if rank < rem else 0)
+
+
+def broadcast_projection(projection, channels: int, dim: int, device, src: int = 0):
+    """PCA projection [C, d] f32 from the rank that owns image 0 to everyone."""
+    import torch
+    dist = _dist()
+    rank, world = world_info()
+    if world == 1:
+        return projection
+    if rank != src or projection is None:
+        projection = torch.empty((channels, dim), dtype=torch.float32, device=device)
+    projection = projection.to(device=device, dtype=torch.float32).contiguous()
+    dist.broadcast(projection, src=src)
+    return projection
+
+
+def all_gather_descriptors(desc_local, counts_local, n_total: int):
+    """desc_local [n_local, K, d], counts_local int32 [n_local] (shard_range order) ->
+    (desc [n_total, K, d], counts [n_total]) on every rank.  One all-gather for the payload, one
+    for the counts; shards are padded to the largest shard so the collective is regular."""
+    import torch
+    dist = _dist()
+    rank, world = world_info()
+    if world == 1:
+        return desc_local, counts_local
+    n_max = -(-n_total // world)
+    K, d = desc_local.shape[1], desc_local.shape[2]
+    pad_d = torch.zeros((n_max, K, d), dtype=desc_local.dtype, device=desc_local.device)
+    pad_c = torch.zeros((n_max,), dtype=torch.int32, device=desc_local.device)
+    pad_d[: desc_local.shape[0]] = desc_local
+    pad_c[: counts_local.shape[0]] = counts_local
+    out_d = torch.empty((world * n_max, K, d), dtype=desc_local.dtype, device=desc_local.device)
+    out_c = torch.empty((world * n_max,), dtype=torch.int32, device=desc_local.device)
+    dist.all_gather_into_tensor(out_d, pad_d)
+    dist.all_gather_into_tensor(out_c, pad_c)
+    keep = []
+    for r in range(world):
+        lo, hi = shard_range(n_total, r, world)
+        keep.extend(range(r * n_max, r * n_max + (hi - lo)))
+    idx = torch.tensor(keep, dtype=torch.long, device=desc_local.device)
+    return out_d.index_select(0, idx).contiguous(), out_c.index_select(0, idx).contiguous()
+
+
+def gather_to_writer(local: dict, dst: int = 0) -> Optional[dict]:
+    """Merge per-rank {key: ndarray} dictionaries on the writer rank (None elsewhere)."""
+    dist = _dist()
+    rank, world = world_info()
+    if world == 1:
+        return local
+    bucket = [None] * world if rank == dst else None
+    dist.gather_object(local, bucket, dst=dst)
+    if rank != dst:
+        return None
+    merged: dict = {}
+    for part in bucket:
+        merged.update(part)
+    return merged
+
+
+MatchFn = Callable[[np.ndarray], List[np.ndarray]]
+
+
+def match_exhaustive_sharded(image_ids: Sequence[int], match_fn: Callable[[np.ndarray], List[np.ndarray]],
+                             block_size: int = 50, min_num_matches: int = 15,
+                             skip: Optional[Callable[[int, int], bool]] = None) -> Optional[Dict[Tuple[int, int], np.ndarray]]:
+    """Exhaustive matching of the images `image_ids` (database order) sharded by pair block.
+
+    `match_fn(index_pairs int32 [n,2]) -> list of [m,2] uint32` matches pairs given as indices into
+    `image_ids` against the descriptors resident on this rank (GPU: Matcher.match_pairs on the
+    all-gathered tensor).  Blocks follow ExhaustivePairGenerator (pairing.cc:202-236); pairs with
+    fewer than `min_num_matches` matches are blanked (feature_matching_utils.cc:485-488).
+    Returns {(id1, id2): matches} on rank 0, None elsewhere."""
+    rank, world = world_info()
+    ids = [int(i) for i in image_ids]
+    index_of = {i: k for k, i in enumerate(ids)}
+    blocks = list(ExhaustivePairGenerator(ids, block_size).blocks())
+    mine = shard_blocks([len(b) for b in blocks], world)[rank]
+    local: Dict[Tuple[int, int], np.ndarray] = {}
+    for b in mine:
+        pairs = [p for p in blocks[b] if not (skip and skip(*p))]
+        if not pairs:
+            continue
+        idx = np.array([(index_of[a], index_of[c]) for a, c in pairs], dtype=np.int32)
+        for pair, m in zip(pairs, match_fn(idx)):
+            m = np.asarray(m, dtype=np.uint32).reshape(-1, 2)
+            local[pair] = m if m.shape[0] >= min_num_matches else np.zeros((0, 2), np.uint32)
+    return gather_to_writer(local, 0)
+
+
+def gpu_match_fn(matcher, desc, counts, options, pairs_per_launch: int = 512) -> MatchFn:
+    """match_fn over device-resident descriptors (bf16 [n, K, d]) with the fused sm_100a matcher."""
+    import torch
+
+    def fn(idx: np.ndarray) -> List[np.ndarray]:
+        out: List[np.ndarray] = []
+        inv = 1.0 if desc.dtype == torch.bfloat16 else None
+        for s in range(0, len(idx), pairs_per_launch):
+            chunk = torch.from_numpy(idx[s:s + pairs_per_launch]).to(desc.device)
+            m, n = matcher.match_pairs(desc, counts, chunk, options.max_ratio, options.max_distance,
+                                       options.cross_check, inv if inv is not None else 1.0)
+            n_h = n.cpu().numpy()
+            m_h = m.cpu().numpy().view(np.uint32)
+            out.extend(m_h[i, : n_h[i]].copy() for i in range(len(n_h)))
+        return out
+    return fn
+
+
+def extract_and_match(image_dir, db_path, extractor, camera_model: str = "SIMPLE_PINHOLE", camera_params=None,
+                      matching_options=None, block_size: int = 50, matcher=None):
+    """Whole hot path on `world` GPUs: every rank extracts its contiguous shard of the sorted image
+    list with `extractor` (a ViTExtractor bound to this rank's GPU), descriptors are all-gathered
+    once, pair blocks are matched where they were dealt, rank 0 writes every database row.
+
+    Matching runs on the uint8 descriptors -- the bytes COLMAP would read back from the database --
+    converted exactly to bf16 on the device (inv_norm = 1/512^2), so the result equals the
+    single-process `extract()` + `match_exhaustive()` pipeline.  Returns the matches dict on rank 0."""
+    import cv2
+    import torch
+    from .database import ColmapDatabase, make_camera
+    from .features.base_extractor import default_camera_params, list_images
+    from .matching import FeatureMatchingOptions, Matcher, SQ_SIFT_NORM
+    rank, world = world_info()
+    options = matching_options or FeatureMatchingOptions()
+    files = list_images(image_dir)
+    if not files:
+        raise ValueError(f"No images found in {image_dir}")
+    n = len(files)
+    lo, hi = shard_range(n, rank, world)
+    dev = extractor.device
+    K, d = extractor.num_keypoints, min(extractor.descriptor_dim, extractor.model.embed_dim)
+    needs_pca = extractor.model.embed_dim > extractor.descriptor_dim
+
+    def run_batch(paths):
+        imgs, orig, res = [], None, None
+        for p in paths:
+            im, orig, res = extractor._resize(cv2.imread(str(p)))
+            imgs.append(im)
+        return extractor._extract_batch(imgs, orig, res)[0]
+
+    feats: Dict[int, Tuple[np.ndarray, np.ndarray]] = {}
+    if needs_pca:  # fitted on image 0 by its owner, then shared (vit_extractor.py:601-639)
+        if rank == 0:
+            feats[0] = run_batch([files[0]])[0]
+        extractor.descriptor_projection = broadcast_projection(extractor.descriptor_projection,
+                                                               extractor.model.embed_dim, d, dev)
+    todo = [i for i in range(lo, hi) if i not in feats]
+    for s in range(0, len(todo), extractor.batch_size):
+        chunk = todo[s:s + extractor.batch_size]
+        sizes = {cv2.imread(str(files[i])).shape[:2] for i in chunk} if len(chunk) > 1 else {None}
+        groups = [chunk] if len(sizes) == 1 else [[i] for i in chunk]
+        for g in groups:
+            for i, f in zip(g, run_batch([files[i] for i in g])):
+                feats[i] = f
+    # uint8 descriptors of this shard, padded to K rows -> one all-gather
+    desc_local = torch.zeros((hi - lo, K, d), dtype=torch.uint8)
+    counts_local = torch.zeros((hi - lo,), dtype=torch.int32)
+    for i in range(lo, hi):
+        m = min(len(feats[i][1]), K)
+        desc_local[i - lo, :m] = torch.from_numpy(feats[i][1][:m])
+        counts_local[i - lo] = m
+    desc_u8, counts = all_gather_descriptors(desc_local.to(dev), counts_local.to(dev), n)
+    matcher = matcher or Matcher(extractor.device_index)
+    desc = matcher.to_bf16(desc_u8)
+
+    def fn(idx):
+        out = []
+        for s in range(0, len(idx), 512):
+            chunk = torch.from_numpy(idx[s:s + 512]).to(dev)
+            m, nm = matcher.match_pairs(desc, counts, chunk, options.max_ratio, options.max_distance,
+                                        options.cross_check, 1.0 / SQ_SIFT_NORM)
+            nm_h, m_h = nm.cpu().numpy(), m.cpu().numpy().view(np.uint32)
+            out.extend(m_h[k, : nm_h[k]].copy() for k in range(len(nm_h)))
+        return out
+
+    ids = list(range(1, n + 1))  # image ids are assigned in sorted file order by the single writer
+    matches = match_exhaustive_sharded(ids, fn, block_size, options.min_num_matches)
+    all_feats = gather_to_writer(feats, 0)
+    if rank != 0:
+        return None
+    db = ColmapDatabase(str(db_path))
+    first = cv2.imread(str(files[0]))
+    h, w = first.shape[:2]
+    params = camera_params if camera_params is not None else default_camera_params(camera_model, w, h)
+    cam = db.db.write_camera(make_camera(camera_model, w, h, params))
+    for i, f in enumerate(files):
+        image_id = db.add_image(f.name, camera_id=cam)
+        kps, du8 = all_feats[i]
+        if len(kps):
+            db.add_keypoints(image_id, kps)
+            db.add_descriptors(image_id, du8)
+    for (a, b), m in matches.items():
+        db.add_matches(a, b, m)
+    db.close()
+    return matches
