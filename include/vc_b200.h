@@ -169,6 +169,22 @@ int vc_sample_pack(vc_handle* h, const void* tokens, int dtype, int n_images, in
                    const float* kp_scale, float* keypoints, void* desc_bf16, uint8_t* desc_u8,
                    float* desc_f32, void* stream);
 
+/* Keypoint selection of the `trainable_vit` extractor.
+ *   kp_map    : device f32 [n_images, map_h*map_w, 4], channel-last head output at 1/4 resolution:
+ *               score logit, dx, dy, orientation (raw when apply_tanh != 0: tanh(.)*pi is applied
+ *               here as vit_colmap/model/vit_feature_model.py:222-223 does)
+ *   kp_scale  : host float[4] = {w_orig/w_new, h_orig/h_new, w_orig-1, h_orig-1}
+ *   coords    : int32 [n_images, capacity, 2] (y, x) cells, for vc_sample_pack(quant TRAINABLE)
+ *   keypoints : f32 [n_images, capacity, 6] = x, y, 1, orientation, score, 0
+ * Rows are in descending score order (ties: lower row-major cell first).
+ * Replaces: sigmoid, _simple_nms (max_pool2d, ties kept), threshold, nonzero, topk and the
+ * sub-pixel coordinate arithmetic of trainable_vit_extractor.py:114-138,183-254. */
+size_t vc_trainable_workspace_bytes(int n_images, int map_h, int map_w);
+int vc_trainable_select(vc_handle* h, const float* kp_map, int n_images, int map_h, int map_w,
+                        int num_keypoints, float score_threshold, int nms_radius, int apply_tanh,
+                        const float* kp_scale, int32_t* coords, float* keypoints, int32_t* counts,
+                        int capacity, void* workspace, size_t workspace_bytes, void* stream);
+
 /* ------------------------------------------------------------------------------------------
  * DINOv2 ViT-S/B/L/14 forward (the backbone the reference pulls through torch.hub,
  * vit_colmap/features/vit_extractor.py:95-98, and calls as

@@ -215,3 +215,42 @@ def simple_nms(scores: torch.Tensor, radius: int) -> torch.Tensor:
     s = scores[None, None]
     mx = F.max_pool2d(s, kernel_size=2 * radius + 1, stride=1, padding=radius)
     return (s == mx).squeeze(0).squeeze(0)
+
+
+def synthetic_head_maps(seed: int, d: int, h4: int, w4: int):
+    """Seeded stand-ins for ViTFeatureModel's outputs: keypoint map [4,h4,w4] (score logit, dx, dy,
+    orientation already in [-pi, pi]) and an L2-normalised descriptor map [d,h4,w4]."""
+    rng = np.random.default_rng(seed)
+    low = rng.standard_normal((1, (h4 + 2) // 3, (w4 + 2) // 3)).astype(np.float32)
+    logit = np.repeat(np.repeat(low, 3, axis=1), 3, axis=2)[:, :h4, :w4] + 0.7 * rng.standard_normal((1, h4, w4)).astype(np.float32)
+    off = 0.5 * np.tanh(rng.standard_normal((2, h4, w4))).astype(np.float32)
+    ori = (np.pi * np.tanh(rng.standard_normal((1, h4, w4)))).astype(np.float32)
+    kp = torch.from_numpy(np.concatenate([logit, off, ori], axis=0))
+    desc = F.normalize(torch.from_numpy(rng.standard_normal((d, h4, w4)).astype(np.float32)), p=2, dim=0, eps=1e-8)
+    return kp, desc
+
+
+def trainable_select(kp_map: torch.Tensor, desc_map: torch.Tensor, orig_wh, resized_wh, num_keypoints: int,
+                     score_threshold: float, nms_radius: int):
+    """trainable_vit_extractor.py:173-269 on prepared head outputs.  Ties of torch.topk are resolved
+    towards the lower row-major cell index.  Returns (keypoints [K,6] f32, descriptors [K,d] u8,
+    coords [K,2] (y,x))."""
+    w_orig, h_orig = orig_wh
+    w_new, h_new = resized_wh
+    scores = torch.sigmoid(kp_map[0])
+    valid = (scores > score_threshold) & simple_nms(scores, nms_radius)
+    coords = torch.nonzero(valid, as_tuple=False)
+    d = desc_map.shape[0]
+    if len(coords) == 0:
+        return np.zeros((0, 6), np.float32), np.zeros((0, d), np.uint8), np.zeros((0, 2), np.int64)
+    vs = scores[coords[:, 0], coords[:, 1]]
+    k = min(num_keypoints, len(vs))
+    _, order = _topk_stable(vs.numpy(), k)
+    order = torch.from_numpy(order.copy())
+    sel, sel_scores = coords[order], vs[order]
+    sy, sx = sel[:, 0], sel[:, 1]
+    kx = ((sx.float() + kp_map[1][sy, sx] + 0.5) * 4.0 * (w_orig / w_new)).clamp(0, w_orig - 1)
+    ky = ((sy.float() + kp_map[2][sy, sx] + 0.5) * 4.0 * (h_orig / h_new)).clamp(0, h_orig - 1)
+    kps = torch.stack([kx, ky, torch.ones_like(kx), kp_map[3][sy, sx], sel_scores, torch.zeros_like(kx)], dim=1)
+    desc = desc_map[:, sy, sx].t().numpy()
+    return kps.numpy().astype(np.float32), ((desc + 1.0) * 127.5).clip(0, 255).astype(np.uint8), sel.numpy()

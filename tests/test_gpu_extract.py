@@ -166,3 +166,66 @@ def test_batched_bf16_tokens_whole_stage(pp):
             idx = [pos[tuple(c)] for c in out.coords[i, :n].cpu().numpy().tolist()]
             assert np.abs(out.desc_f32[i, :n].cpu().numpy() - ref["desc_float"][idx]).max() < 1e-5
             assert np.array_equal(out.keypoints[i, :n].cpu().numpy(), ref["keypoints"][idx])
+
+
+TRAINABLE = sorted((Path(__file__).parent / "golden").glob("trainable_*.npz"))
+
+
+@pytest.mark.parametrize("path", TRAINABLE, ids=[p.stem for p in TRAINABLE])
+def test_trainable_select_pack_matches_reference(pp, path):
+    """vc_trainable_select + vc_sample_pack(quant TRAINABLE) vs the reference's own
+    TrainableViTExtractor._run_inference outputs (stubbed network, tests/golden/trainable_*.npz).
+    Keypoint sets are identical; rows may only swap among exactly equal scores; the sigmoid is
+    allowed 1 ulp (CUDA expf vs ATen's vectorised exp)."""
+    import torch
+    from oracle import extract_oracle as eo
+    from vit_colmap_b200.extraction import trainable_select_pack
+    g = np.load(path)
+    seed, d, h4, w4, K, r, ow, oh, rw, rh = (int(x) for x in g["meta"])
+    kp, desc = eo.synthetic_head_maps(seed, d, h4, w4)
+    kp_cl = kp.permute(1, 2, 0)[None].contiguous().cuda()
+    desc_cl = desc.permute(1, 2, 0)[None].contiguous().cuda()
+    kps, du8, dbf, df32, counts = trainable_select_pack(pp, kp_cl, desc_cl, (ow, oh), (rw, rh), K, float(g["thr"]), r,
+                                                        apply_tanh=False, want_f32=True)
+    n = int(counts[0])
+    ref_k, ref_d = g["keypoints"], g["desc_u8"]
+    assert n == len(ref_k)
+    if n == 0:
+        return
+    got_k, got_d = kps[0, :n].cpu().numpy(), du8[0, :n].cpu().numpy()
+    assert np.all(np.diff(got_k[:, 4]) <= 0)                                   # descending scores
+    key = lambda a: np.lexsort((a[:, 1], a[:, 0]))  # noqa: E731  by position: sets must coincide
+    po, pg = key(got_k), key(ref_k)
+    assert np.array_equal(got_k[po][:, [0, 1, 2, 3, 5]], ref_k[pg][:, [0, 1, 2, 3, 5]])
+    assert np.abs(got_k[po][:, 4] - ref_k[pg][:, 4]).max() <= 1.2e-7
+    diff = np.abs(got_d[po].astype(int) - ref_d[pg].astype(int))
+    assert diff.max() <= 1 and (diff > 0).mean() < 1e-3      # re-normalising unit rows moves <= 1 ulp
+    assert np.abs(dbf[0, :n].float().cpu().numpy() - df32[0, :n].cpu().numpy()).max() <= 2 ** -8
+
+
+def test_trainable_select_large_map_and_tanh(pp):
+    """A 1600x1200-sized score map (399x297 cells, beyond any shared-memory path), batch of 2,
+    orientation produced from raw head output (apply_tanh)."""
+    import torch
+    from oracle import extract_oracle as eo
+    from vit_colmap_b200.extraction import trainable_select_pack
+    h4, w4, d = 297, 399, 32
+    outs = []
+    maps = [eo.synthetic_head_maps(30 + i, d, h4, w4) for i in range(2)]
+    kp_cl = torch.stack([m[0].permute(1, 2, 0) for m in maps]).contiguous()
+    raw = kp_cl.clone()
+    raw[..., 3] = torch.atanh((kp_cl[..., 3] / np.pi).clamp(-0.999, 0.999))
+    desc_cl = torch.stack([m[1].permute(1, 2, 0) for m in maps]).contiguous()
+    kps, du8, _, _, counts = trainable_select_pack(pp, raw.cuda(), desc_cl.cuda(), (1600, 1200), (1596, 1190), 8192,
+                                                   0.6, 2, apply_tanh=True)
+    for i, (kp, desc) in enumerate(maps):
+        kp = kp.clone()
+        kp[3] = torch.tanh(raw[i, ..., 3]) * torch.pi
+        rk, rd, _ = eo.trainable_select(kp, desc, (1600, 1200), (1596, 1190), 8192, 0.6, 2)
+        n = int(counts[i])
+        assert n == len(rk) and n > 1000
+        gk = kps[i, :n].cpu().numpy()
+        po, pg = np.lexsort((gk[:, 1], gk[:, 0])), np.lexsort((rk[:, 1], rk[:, 0]))
+        assert np.array_equal(gk[po][:, :3], rk[pg][:, :3])
+        assert np.abs(gk[po][:, 3] - rk[pg][:, 3]).max() < 1e-6 and np.abs(gk[po][:, 4] - rk[pg][:, 4]).max() <= 1.2e-7
+        assert np.abs(du8[i, :n].cpu().numpy()[po].astype(int) - rd[pg].astype(int)).max() <= 1

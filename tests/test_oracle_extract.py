@@ -56,3 +56,30 @@ def test_binning_ignores_cells_beyond_last_full_bin():
     score = eo.distinctiveness(fm).numpy()
     coords, _ = eo.spatial_binning_selection(score, 8192, 16)
     assert coords.max() < 32 and len(coords) == 1024
+
+
+TRAINABLE = sorted((Path(__file__).parent / "golden").glob("trainable_*.npz"))
+
+
+def load_trainable(path):
+    g = np.load(path)
+    seed, d, h4, w4, K, r, ow, oh, rw, rh = (int(x) for x in g["meta"])
+    return g, dict(seed=seed, d=d, h4=h4, w4=w4, K=K, r=r, thr=float(g["thr"]), orig=(ow, oh), resized=(rw, rh))
+
+
+@pytest.mark.parametrize("path", TRAINABLE, ids=[p.stem for p in TRAINABLE])
+def test_trainable_restatement_matches_reference_outputs(path):
+    """oracle.trainable_select vs the reference's own TrainableViTExtractor._run_inference
+    (stubbed network, oracle/gen_golden_trainable.py)."""
+    g, m = load_trainable(path)
+    kp, desc = eo.synthetic_head_maps(m["seed"], m["d"], m["h4"], m["w4"])
+    kps, du8, _ = eo.trainable_select(kp, desc, m["orig"], m["resized"], m["K"], m["thr"], m["r"])
+    assert kps.shape == g["keypoints"].shape and du8.shape == g["desc_u8"].shape
+    if len(kps) == 0:
+        return
+    assert np.array_equal(kps[:, 4], g["keypoints"][:, 4])        # scores, descending
+    # order among exactly equal scores is unspecified in torch.topk: compare as sorted row sets
+    key = lambda a: np.lexsort((a[:, 1], a[:, 0], -a[:, 4].astype(np.float64)))  # noqa: E731
+    po, pg = key(kps), key(g["keypoints"])
+    assert np.array_equal(kps[po], g["keypoints"][pg])
+    assert np.array_equal(du8[po], g["desc_u8"][pg])

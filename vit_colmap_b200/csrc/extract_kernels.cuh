@@ -51,6 +51,7 @@ struct SampleParams {
   const float* projection;  // [C, d] or nullptr (then d == C)
   int d;
   int quant_mode;      // 0: trunc(clip(512 v, 0, 255)) (vit); 1: round, COLMAP; 2: (v+1)*127.5
+  float norm_eps;      // F.normalize eps: 1e-12 (vit_extractor.py:243), 1e-8 (vit_feature_model.py:226)
   float sx1, sx2, sy1, sy2;  // keypoint scale factors: x = (col + .5) * sx1 * sx2
   float* keypoints;    // out [B, cap, 2] (x, y) or nullptr
   __nv_bfloat16* desc_bf16;  // out [B, cap, d] or nullptr
@@ -58,5 +59,22 @@ struct SampleParams {
   float* desc_f32;           // out [B, cap, d] or nullptr
 };
 cudaError_t launch_sample_pack(const SampleParams& p, cudaStream_t stream);
+
+struct TrainableSelectParams {
+  const float* kp_map;   // [B, H*W, 4] channel-last: score logit, dx, dy, orientation
+  int B, H, W;
+  int num_keypoints, nms_radius, apply_tanh;
+  float score_threshold;
+  float scale_x, scale_y;  // w_orig / w_new, h_orig / h_new
+  float max_x, max_y;      // w_orig - 1, h_orig - 1
+  int cap;
+  float* score_scratch;               // [B, H*W]
+  unsigned long long* key_scratch;    // [B, key_capacity]
+  size_t key_capacity;                // power of two >= H*W
+  int32_t* coords;       // out [B, cap, 2] (y, x)
+  float* keypoints;      // out [B, cap, 6] x, y, 1, orientation, score, 0
+  int32_t* counts;       // out [B]
+};
+cudaError_t launch_trainable_select(const TrainableSelectParams& p, cudaStream_t stream);
 
 }  // namespace vc

@@ -164,7 +164,7 @@ __global__ void __launch_bounds__(256) sample_pack_direct(const SampleParams p) 
   for (int j = 0; j < kVec; ++j)
     ss += acc[j].x * acc[j].x + acc[j].y * acc[j].y + acc[j].z * acc[j].z + acc[j].w * acc[j].w;
   ss = warp_sum(ss);
-  const float den = fmaxf(sqrtf(ss), 1e-12f);  // F.normalize eps
+  const float den = fmaxf(sqrtf(ss), p.norm_eps);  // F.normalize eps
 #pragma unroll
   for (int j = 0; j < kVec; ++j) {
     const int v = lane + 32 * j;
@@ -267,7 +267,7 @@ __global__ void __launch_bounds__(256) sample_pack_project(const SampleParams p,
       ss += x.x * x.x + x.y * x.y + x.z * x.z + x.w * x.w;
     }
     ss = warp_sum(ss);
-    const float den = fmaxf(sqrtf(ss), 1e-12f);
+    const float den = fmaxf(sqrtf(ss), p.norm_eps);
     for (int v = lane; v < dvec; v += 32) {
       const float4 x = *reinterpret_cast<const float4*>(row + 4 * v);
       float4 o;

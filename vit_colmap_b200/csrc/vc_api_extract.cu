@@ -120,9 +120,9 @@ int vc_sample_pack(vc_handle* h, const void* tokens, int dtype, int n_images, in
                    const int32_t* counts, int capacity, const float* projection, int d, int quant_mode,
                    const float* kp_scale, float* keypoints, void* desc_bf16, uint8_t* desc_u8,
                    float* desc_f32, void* stream) {
-  int rc = check_grid(h, n_images, grid_h, grid_w);
-  if (rc != VC_OK) return rc;
-  rc = check_tokens(tokens, dtype, channels);
+  if (!h) return fail(VC_ERR_INVALID, "null handle");
+  if (n_images <= 0 || grid_h <= 0 || grid_w <= 0) return fail(VC_ERR_INVALID, "bad sizes");
+  int rc = check_tokens(tokens, dtype, channels);
   if (rc != VC_OK) return rc;
   if (!coords || !counts) return fail(VC_ERR_INVALID, "null coords / counts");
   if (capacity <= 0) return fail(VC_ERR_INVALID, "bad capacity");
@@ -152,6 +152,7 @@ int vc_sample_pack(vc_handle* h, const void* tokens, int dtype, int n_images, in
   p.projection = projection;
   p.d = d;
   p.quant_mode = quant_mode;
+  p.norm_eps = quant_mode == VC_QUANT_TRAINABLE ? 1e-8f : 1e-12f;
   if (kp_scale) {
     p.sx1 = kp_scale[0];
     p.sx2 = kp_scale[1];
@@ -163,6 +164,58 @@ int vc_sample_pack(vc_handle* h, const void* tokens, int dtype, int n_images, in
   p.desc_u8 = desc_u8;
   p.desc_f32 = desc_f32;
   VC_CUDA(vc::launch_sample_pack(p, reinterpret_cast<cudaStream_t>(stream)));
+  vc::add_launches(1);
+  return VC_OK;
+}
+
+size_t vc_trainable_workspace_bytes(int n_images, int map_h, int map_w) {
+  if (n_images <= 0 || map_h <= 0 || map_w <= 0) return 256;
+  size_t cap = 2;
+  while (cap < (size_t)map_h * map_w) cap <<= 1;
+  return vc::align_up((size_t)n_images * map_h * map_w * sizeof(float), 256) + (size_t)n_images * cap * 8;
+}
+
+int vc_trainable_select(vc_handle* h, const float* kp_map, int n_images, int map_h, int map_w,
+                        int num_keypoints, float score_threshold, int nms_radius, int apply_tanh,
+                        const float* kp_scale, int32_t* coords, float* keypoints, int32_t* counts,
+                        int capacity, void* workspace, size_t workspace_bytes, void* stream) {
+  if (!h) return fail(VC_ERR_INVALID, "null handle");
+  if (!kp_map || !kp_scale || !coords || !keypoints || !counts || !workspace)
+    return fail(VC_ERR_INVALID, "null pointer argument");
+  if (n_images <= 0 || map_h <= 0 || map_w <= 0 || num_keypoints <= 0 || nms_radius < 0 || nms_radius > 16)
+    return fail(VC_ERR_INVALID, "bad selection parameters");
+  if ((long long)map_h * map_w > (1ll << 30)) return fail(VC_ERR_INVALID, "score map too large");
+  if (capacity < std::min(num_keypoints, map_h * map_w))
+    return fail(VC_ERR_INVALID, "capacity %d < min(num_keypoints, cells)", capacity);
+  if (workspace_bytes < vc_trainable_workspace_bytes(n_images, map_h, map_w))
+    return fail(VC_ERR_WORKSPACE, "workspace %zu B < required %zu B", workspace_bytes,
+                vc_trainable_workspace_bytes(n_images, map_h, map_w));
+  if ((reinterpret_cast<uintptr_t>(kp_map) & 15) != 0) return fail(VC_ERR_INVALID, "kp_map must be 16-byte aligned");
+  VC_CUDA(cudaSetDevice(h->device));
+  vc::TrainableSelectParams p{};
+  p.kp_map = kp_map;
+  p.B = n_images;
+  p.H = map_h;
+  p.W = map_w;
+  p.num_keypoints = num_keypoints;
+  p.nms_radius = nms_radius;
+  p.apply_tanh = apply_tanh;
+  p.score_threshold = score_threshold;
+  p.scale_x = kp_scale[0];
+  p.scale_y = kp_scale[1];
+  p.max_x = kp_scale[2];
+  p.max_y = kp_scale[3];
+  p.cap = capacity;
+  size_t cap = 2;
+  while (cap < (size_t)map_h * map_w) cap <<= 1;
+  p.key_capacity = cap;
+  p.score_scratch = static_cast<float*>(workspace);
+  p.key_scratch = reinterpret_cast<unsigned long long*>(
+      static_cast<uint8_t*>(workspace) + vc::align_up((size_t)n_images * map_h * map_w * sizeof(float), 256));
+  p.coords = coords;
+  p.keypoints = keypoints;
+  p.counts = counts;
+  VC_CUDA(vc::launch_trainable_select(p, reinterpret_cast<cudaStream_t>(stream)));
   vc::add_launches(1);
   return VC_OK;
 }

@@ -137,3 +137,38 @@ class PostProcessor:
         kps, dbf, du8, df32 = self.sample_pack(tokens, grid_hw, coords, counts, orig_wh, resized_wh,
                                                projection, quant_mode, want_f32)
         return SparseFeatures(counts, coords, scores, kps, dbf, du8, df32)
+
+
+def trainable_select_pack(pp: PostProcessor, kp_map, desc_map, orig_wh, resized_wh, num_keypoints: int = 2048,
+                          score_threshold: float = 0.0, nms_radius: int = 4, apply_tanh: bool = False,
+                          want_f32: bool = False):
+    """Selection + packing stage of the `trainable_vit` extractor
+    (vit_colmap/features/trainable_vit_extractor.py:173-269) on channel-last head outputs:
+    kp_map f32 [B, h4, w4, 4], desc_map f32/bf16 [B, h4, w4, d] (un-normalised is fine: rows are
+    L2-normalised with the model's eps 1e-8 as they are packed).
+    Returns (keypoints f32 [B,cap,6], desc_u8 [B,cap,d], desc_bf16, desc_f32|None, counts int32 [B])."""
+    torch = pp.torch
+    B, h4, w4, _ = kp_map.shape
+    d = int(desc_map.shape[3])
+    kp_map = kp_map.contiguous()
+    desc_map = desc_map.contiguous()
+    cap = min(int(num_keypoints), h4 * w4)
+    need = int(pp.lib.vc_trainable_workspace_bytes(B, h4, w4))
+    ws = torch.empty(need, dtype=torch.uint8, device=kp_map.device)
+    coords = torch.zeros((B, cap, 2), dtype=torch.int32, device=kp_map.device)
+    kps = torch.zeros((B, cap, 6), dtype=torch.float32, device=kp_map.device)
+    counts = torch.zeros((B,), dtype=torch.int32, device=kp_map.device)
+    w_orig, h_orig = orig_wh
+    w_new, h_new = resized_wh
+    scale = (ctypes.c_float * 4)(w_orig / w_new, h_orig / h_new, w_orig - 1, h_orig - 1)
+    _lib.check(pp.lib.vc_trainable_select(pp.handle, _ptr(kp_map), B, h4, w4, int(num_keypoints),
+                                          float(score_threshold), int(nms_radius), int(bool(apply_tanh)), scale,
+                                          _ptr(coords), _ptr(kps), _ptr(counts), cap, _ptr(ws), need, pp._stream()))
+    dbf = torch.zeros((B, cap, d), dtype=torch.bfloat16, device=kp_map.device)
+    du8 = torch.zeros((B, cap, d), dtype=torch.uint8, device=kp_map.device)
+    df32 = torch.zeros((B, cap, d), dtype=torch.float32, device=kp_map.device) if want_f32 else None
+    tok = desc_map.reshape(B, h4 * w4, d)
+    _lib.check(pp.lib.vc_sample_pack(pp.handle, _ptr(tok), pp._dtype_code(torch, tok), B, h4, w4, d, int(tok.stride(0)),
+                                     _ptr(coords), 0, _ptr(counts), cap, 0, d, QUANT_TRAINABLE, None, 0, _ptr(dbf),
+                                     _ptr(du8), _ptr(df32), pp._stream()))
+    return kps, du8, dbf, df32, counts
