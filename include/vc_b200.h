@@ -240,6 +240,66 @@ int vc_vit_attention(vc_handle* h, const void* qkv, int n_images, int tokens, in
 int vc_vit_layernorm(vc_handle* h, const float* x, const float* w, const float* b, int rows, int channels,
                      void* out_bf16, void* stream);
 
+/* ------------------------------------------------------------------------------------------
+ * Convolutional head of ViTFeatureModel (vit_colmap/model/vit_feature_model.py:12-29 UpsampleBlock,
+ * :90-121 upsampler / trunk / heads, :173-295 forward / forward_from_backbone_features), eval mode.
+ * Activations are channels-last bf16 on the device; convolution weights are bf16 repacked by the
+ * caller (vit_colmap_b200/head.py) into GEMM rows, BatchNorm is folded into per-channel fp32
+ * scale/shift applied in the epilogue:  y = gelu(conv_nobias * scale + shift),
+ * scale = gamma / sqrt(var + 1e-5), shift = (conv_bias - mean) * scale + beta.
+ * ------------------------------------------------------------------------------------------ */
+typedef struct {
+  int32_t backbone_dim;    /* C: 384 / 768 / 1024 (multiple of 64) */
+  int32_t descriptor_dim;  /* d (multiple of 32) */
+  /* upsampler.{0,1}: ConvTranspose2d(k4,s2,p1) as 4 sub-pixel phases, bf16 [4*512, 4*Cin]: row
+   * (2*py+px)*512 + co, column (2*ty+tx)*Cin + ci = weight[ci, co, ky, kx] with (phase 0: tap 0 ->
+   * k=3, offset -1; tap 1 -> k=1, offset 0; phase 1: tap 0 -> k=2, offset 0; tap 1 -> k=0, offset +1) */
+  const void* deconv_w[2];
+  const float* deconv_b[2];    /* [512] */
+  /* Conv3x3 weights bf16 [Cout, 9*Cin], column (ky*3+kx)*Cin + ci */
+  const void* conv_w[2];       /* [512, 9*512] */
+  const float* conv_scale[2];  /* [512] */
+  const float* conv_shift[2];
+  const void* trunk_w;         /* [256, 9*512] */
+  const float *trunk_scale, *trunk_shift;
+  const void* heads_w;         /* [192, 9*256]: rows 0..63 keypoint_head.0, rows 64..191 descriptor_head.0 */
+  const float *heads_scale, *heads_shift; /* [192] */
+  const float* kp_w;           /* f32 [4, 64]  keypoint_head.3 */
+  const float* kp_b;           /* f32 [4] */
+  const void* desc_w;          /* bf16 [d, 128] descriptor_head.3 */
+  const float* desc_b;         /* f32 [d] */
+} vc_head_weights;
+
+size_t vc_head_workspace_bytes(int n_images, int grid_h, int grid_w, int backbone_dim, int out_h,
+                               int out_w);
+
+/* tokens: device [n_images, grid_h*grid_w, C] patch tokens (f32 or bf16; = the NCHW feature map of
+ *         vit_feature_model.py:165-169 in channels-last form).
+ * out_h, out_w: target size, (14*grid_h)//4 x (14*grid_w)//4 in the reference (:195-197).
+ * kp_map       : f32 [n_images, out_h, out_w, 4]  score logit, dx, dy, tanh(.)*pi        (required)
+ * desc_map     : f32 [n_images, out_h, out_w, d]  L2-normalised (eps 1e-8)               (may be NULL)
+ * features     : bf16 [n_images, out_h, out_w, 256] trunk output                         (may be NULL)
+ * desc_hidden  : bf16 [n_images, out_h, out_w, 128] descriptor head before its 1x1 conv  (may be NULL;
+ *                with desc_map == NULL the caller projects only the selected keypoints:
+ *                vc_sample_pack(projection = desc_w^T, bias))
+ * Replaces: ViTFeatureModel.forward_from_backbone_features, vit_feature_model.py:234-295. */
+int vc_conv_head_forward(vc_handle* h, const vc_head_weights* w, const void* tokens, int dtype,
+                         int n_images, int grid_h, int grid_w, int out_h, int out_w, float* kp_map,
+                         float* desc_map, void* features, void* desc_hidden, void* workspace,
+                         size_t workspace_bytes, void* stream);
+
+/* Building block exposed for the per-op parity tests: one convolution through the implicit-GEMM
+ * kernel.  kind 0: Conv3x3 pad 1 (w bf16 [Cout, 9*Cin]); 1: ConvTranspose2d k4 s2 p1 (w bf16
+ * [4*Cout, 4*Cin] phase-packed as above); 2: Conv1x1 (w bf16 [Cout, Cin]).
+ * epilogue 0: out bf16 = acc + shift; 1: out bf16 = gelu(acc*scale + shift); 2: out f32 = acc + shift.
+ * in: bf16 [n, h, w, Cin]; out: [n, h*s, w*s, Cout] with s = 2 for kind 1. */
+int vc_conv2d(vc_handle* h, const void* in, int n, int height, int width, int c_in, const void* w,
+              int c_out, int kind, int epilogue, const float* scale, const float* shift, void* out,
+              void* stream);
+/* F.interpolate(bilinear, align_corners=False) on bf16 channels-last maps (vit_feature_model.py:205-212). */
+int vc_resize_bilinear(vc_handle* h, const void* in, int n, int in_h, int in_w, int out_h, int out_w,
+                       int channels, void* out, void* stream);
+
 /* Number of kernels launched by this library on the calling thread since the last reset
  * (bench.py reports it as gpu_launches). */
 int64_t vc_launch_count(int reset);

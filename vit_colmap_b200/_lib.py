@@ -64,6 +64,13 @@ SIGNATURES = {
     "vc_vit_attention": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_void_p, c_void_p]),
     "vc_vit_layernorm": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_void_p,
                                  c_void_p]),
+    "vc_head_workspace_bytes": (c_size_t, [c_int, c_int, c_int, c_int, c_int, c_int]),
+    "vc_conv_head_forward": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_int, c_int,
+                                     c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_size_t, c_void_p]),
+    "vc_conv2d": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_void_p, c_int, c_int, c_int,
+                          c_void_p, c_void_p, c_void_p, c_void_p]),
+    "vc_resize_bilinear": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_int, c_int, c_void_p,
+                                   c_void_p]),
 }
 
 
@@ -79,6 +86,16 @@ class VitWeights(ctypes.Structure):
                 ("patch_w", c_void_p), ("patch_b", c_void_p), ("cls_token", c_void_p),
                 ("pos_embed", c_void_p), ("norm_w", c_void_p), ("norm_b", c_void_p),
                 ("blocks", POINTER(VitBlock))]
+
+class HeadWeights(ctypes.Structure):
+    """vc_head_weights (include/vc_b200.h)."""
+    _fields_ = [("backbone_dim", c_int32), ("descriptor_dim", c_int32),
+                ("deconv_w", c_void_p * 2), ("deconv_b", c_void_p * 2),
+                ("conv_w", c_void_p * 2), ("conv_scale", c_void_p * 2), ("conv_shift", c_void_p * 2),
+                ("trunk_w", c_void_p), ("trunk_scale", c_void_p), ("trunk_shift", c_void_p),
+                ("heads_w", c_void_p), ("heads_scale", c_void_p), ("heads_shift", c_void_p),
+                ("kp_w", c_void_p), ("kp_b", c_void_p), ("desc_w", c_void_p), ("desc_b", c_void_p)]
+
 
 DTYPE_U8, DTYPE_F32, DTYPE_BF16 = 0, 1, 2
 

@@ -18,7 +18,7 @@ CSRC = PKG / "csrc"
 OUT = PKG / "_vc_b200.so"
 SOURCES = ["match_kernel.cu", "match_fused.cu", "vc_api.cu", "score_kernels.cu", "select_kernels.cu",
            "sample_kernels.cu", "vc_api_extract.cu", "vit_gemm.cu", "vit_attention.cu",
-           "vit_pointwise.cu", "vc_api_vit.cu"]
+           "vit_pointwise.cu", "vc_api_vit.cu", "conv_gemm.cu", "head_pointwise.cu", "vc_api_head.cu"]
 EXTRA_SOURCES_GLOB = "*_kernels.cu"
 
 NVCC_FLAGS = [
