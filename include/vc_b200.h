@@ -153,6 +153,8 @@ typedef enum {
  *                 coords_are_float != 0 (bilinear between cells, border clamp)
  *   projection  : f32 [channels, d] applied before normalisation (PCA of
  *                 vit_extractor.py:588-653, fitted by the caller), or NULL with d == channels
+ *   projection_bias : f32 [d] added after the projection, or NULL (the 1x1 descriptor convolution
+ *                 of vit_feature_model.py:120 applied only at the selected keypoints)
  *   kp_scale    : host float[4] = {w_res/W, w_orig/w_res, h_res/H, h_orig/h_res} so that
  *                 x = (col + 0.5) * kp_scale[0] * kp_scale[1] (vit_extractor.py:229-236)
  *   keypoints   : f32 [n_images, capacity, 2] (x, y) pixel coordinates           (may be NULL)
@@ -165,8 +167,8 @@ typedef enum {
  * conversion :246-250. */
 int vc_sample_pack(vc_handle* h, const void* tokens, int dtype, int n_images, int grid_h, int grid_w,
                    int channels, int64_t image_stride, const void* coords, int coords_are_float,
-                   const int32_t* counts, int capacity, const float* projection, int d, int quant_mode,
-                   const float* kp_scale, float* keypoints, void* desc_bf16, uint8_t* desc_u8,
+                   const int32_t* counts, int capacity, const float* projection,
+                   const float* projection_bias, int d, int quant_mode, const float* kp_scale, float* keypoints, void* desc_bf16, uint8_t* desc_u8,
                    float* desc_f32, void* stream);
 
 /* Keypoint selection of the `trainable_vit` extractor.

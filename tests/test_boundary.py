@@ -106,13 +106,11 @@ def test_extractor_switch_and_error_contracts(tmp_path):
     assert isinstance(ex, ColmapSiftExtractor) and isinstance(ex, BaseExtractor)
     with pytest.raises(ImportError):
         ex.extract(tmp_path, tmp_path / "db.db", "PINHOLE")
-    c.extractor.extractor_type = "trainable_vit"
-    with pytest.raises(NotImplementedError):
-        Pipeline(c)._make_extractor()
-    if not torch.cuda.is_available():  # the GPU extractor refuses to run without a device
+    if not torch.cuda.is_available():  # the GPU extractors refuse to run without a device
         from vit_colmap_b200 import _lib
-        c.extractor.extractor_type = "anything-else-falls-through-to-vit"
-        with pytest.raises(_lib.VcError):
-            Pipeline(c)._make_extractor()
+        for t in ("trainable_vit", "anything-else-falls-through-to-vit"):
+            c.extractor.extractor_type = t
+            with pytest.raises(_lib.VcError):
+                Pipeline(c)._make_extractor()
     with pytest.raises(TypeError):
         BaseExtractor()

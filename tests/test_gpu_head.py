@@ -204,3 +204,88 @@ def test_head_target_size_equal_skips_resize():
     kp = out["keypoints"].permute(0, 3, 1, 2).cpu()
     assert (kp - ref["keypoints"]).abs().max().item() <= 2e-2 * ref["keypoints"].abs().max().item()
     head.close()
+
+
+def _oracle_trainable(sd_b, sd_h, name, img_rgb_u8, K, thr, r, d, orig_wh, resized_wh):
+    """Oracle pipeline for one image: ViT oracle (bf16 emulation) -> head oracle (bf16 emulation) ->
+    the reference's selection / packing restatement."""
+    import torch
+    from oracle import extract_oracle as eo
+    from oracle import head_oracle as ho
+    from oracle import vit_oracle as vo
+    heads = vo.CONFIGS[name][2]
+    x = vo.preprocess(torch.from_numpy(img_rgb_u8[None]))
+    tok = vo.forward_features(sd_b, x, heads, emulate_bf16=True)["x_norm_patchtokens"]
+    gh, gw = img_rgb_u8.shape[0] // 14, img_rgb_u8.shape[1] // 14
+    feat = tok.reshape(1, gh, gw, -1).permute(0, 3, 1, 2)
+    out = ho.head_forward(sd_h, feat, emulate_bf16=True)
+    return eo.trainable_select(out["keypoints"][0], out["descriptors"][0], orig_wh, resized_wh, K, thr, r), out
+
+
+def test_trainable_extractor_matches_oracle_pipeline():
+    """TrainableViTExtractor._run_inference (backbone + head + selection + sparse descriptor
+    projection) vs the chained oracles on one 112x140 image.  Both pipelines are bf16, so score maps
+    differ by rounding noise: keypoints are compared as sets of cells where the oracle's score clears
+    the NMS/threshold decisions by a margin, and descriptors of common cells within 2 u8 steps."""
+    import torch
+    from oracle import head_oracle as ho
+    from oracle import vit_oracle as vo
+    from vit_colmap_b200.features.trainable_vit_extractor import TrainableViTExtractor
+    name, d, K, thr, r = "dinov2_vits14", 64, 200, 0.3, 2
+    sd_b = vo.synthetic_state_dict(name, seed=3, depth=2)
+    sd_h = ho.synthetic_head_state_dict(384, d, 7)
+    rng = np.random.default_rng(5)
+    img_bgr = rng.integers(0, 256, (112, 140, 3), dtype=np.uint8)
+    ex = TrainableViTExtractor(model_name=name, num_keypoints=K, descriptor_dim=d, score_threshold=thr,
+                               nms_radius=r, state_dict=sd_b, head_state_dict=sd_h)
+    kps, du8 = ex._run_inference(img_bgr)
+    assert kps.dtype == np.float32 and kps.shape[1] == 6 and du8.dtype == np.uint8 and du8.shape == (len(kps), d)
+    assert 0 < len(kps) <= K
+    assert np.all(kps[:, 2] == 1.0) and np.all(kps[:, 5] == 0.0)
+    assert np.all(np.diff(kps[:, 4]) <= 0)  # descending score
+    (rk, rd, rc), out = _oracle_trainable(sd_b, sd_h, name, img_bgr[:, :, ::-1].copy(), K, thr, r, d, (140, 112), (140, 112))
+    # the two bf16 pipelines agree on the dense maps ...
+    gh, gw = 8, 10
+    tokens = ex.backbone.forward_patch_tokens(torch.from_numpy(img_bgr[None]).cuda(), bgr=True)
+    maps = ex.head.forward(tokens, (gh, gw))
+    torch.cuda.synchronize()
+    kp_map = maps["keypoints"][0].permute(2, 0, 1).cpu()
+    assert (kp_map - out["keypoints"][0]).abs().max().item() < 0.05 * out["keypoints"][0].abs().max().item()
+    cos = (maps["descriptors"][0].permute(2, 0, 1).cpu() * out["descriptors"][0]).sum(dim=0)
+    assert cos.min().item() > 0.999
+    # ... and therefore on most keypoints; descriptors of the common ones match to quantisation noise
+    # (cells are paired through their sub-pixel coordinates: same cell <=> (x, y) within 0.25 px)
+    dist = np.abs(kps[:, None, :2] - rk[None, :, :2]).max(axis=2)
+    pairs = [(i, int(dist[i].argmin())) for i in range(len(kps)) if dist[i].min() < 0.25]
+    assert len(pairs) >= 0.8 * min(len(kps), len(rk)), (len(pairs), len(kps), len(rk))
+    diffs = [np.abs(du8[i].astype(int) - rd[j].astype(int)).max() for i, j in pairs]
+    assert np.percentile(diffs, 90) <= 2
+    assert np.abs(kps[[i for i, _ in pairs], 3:5] - rk[[j for _, j in pairs], 3:5]).max() < 0.05
+    ex.backbone.close()
+
+
+def test_trainable_sparse_projection_equals_dense_path():
+    """Projecting only the selected keypoints (vc_sample_pack with the 1x1 weights) gives the same
+    descriptors as gathering from the dense normalised map: same keypoints, u8 within one step."""
+    import torch
+    from oracle import head_oracle as ho
+    from vit_colmap_b200.extraction import PostProcessor, trainable_select_pack
+    from vit_colmap_b200.head import ConvHead
+    sd, feat = _head_case(384, 128, 6, 7, 31, B=2)
+    head = ConvHead(sd, 384, 128, 0)
+    pp = PostProcessor(0, handle=head.handle)
+    tokens = feat.permute(0, 2, 3, 1).reshape(2, 42, 384).cuda()
+    dense = head.forward(tokens, (6, 7))
+    sparse = head.forward(tokens, (6, 7), dense_descriptors=False)
+    P, b = head.desc_projection
+    a = trainable_select_pack(pp, dense["keypoints"], dense["descriptors"], (98, 84), (98, 84), 150, 0.2, 1, want_f32=True)
+    s = trainable_select_pack(pp, sparse["keypoints"], sparse["desc_hidden"], (98, 84), (98, 84), 150, 0.2, 1,
+                              want_f32=True, projection=P, projection_bias=b)
+    torch.cuda.synchronize()
+    assert torch.equal(a[4], s[4]) and torch.equal(a[0], s[0])
+    n = a[4].cpu().numpy()
+    assert n.min() > 10
+    for i in range(2):
+        assert (a[3][i, :n[i]] - s[3][i, :n[i]]).abs().max().item() < 2e-5
+        assert (a[1][i, :n[i]].int() - s[1][i, :n[i]].int()).abs().max().item() <= 1
+    head.close()

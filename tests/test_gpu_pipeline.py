@@ -96,3 +96,41 @@ def test_vit_pipeline_c1_checkerboards(tmp_path):
     with ColmapDatabase.open_database(str(db_path)) as db:
         k = db.read_keypoints(1)
         assert k.dtype == np.float32 and k.shape[1] == 2
+
+
+def test_trainable_vit_pipeline_into_database(tmp_path):
+    """`trainable_vit` switch value end to end: 5 images (one unreadable, .ppm accepted), SIMPLE_RADIAL
+    default camera (trainable_vit_extractor.py:302,323-341), 6-column keypoints and d-column uint8
+    descriptors in the COLMAP tables, then exhaustive matching over them."""
+    import cv2
+    from vit_colmap_b200.database import ColmapDatabase
+    from vit_colmap_b200.features.trainable_vit_extractor import TrainableViTExtractor
+    from vit_colmap_b200.matching import match_exhaustive
+    d = tmp_path / "images"
+    d.mkdir()
+    rng = np.random.default_rng(0)
+    base = cv2.GaussianBlur(rng.integers(0, 256, (240, 300, 3), dtype=np.uint8), (0, 0), 2.0)
+    for i in range(4):
+        m = np.float32([[1, 0, 6 * i], [0, 1, 4 * i]])
+        cv2.imwrite(str(d / f"img_{i:03d}.{'ppm' if i == 3 else 'png'}"), cv2.warpAffine(base, m, (300, 240)))
+    (d / "img_broken.png").write_bytes(b"not an image")
+    db_path = tmp_path / "db.db"
+    ex = TrainableViTExtractor(model_name="dinov2_vits14", num_keypoints=512, descriptor_dim=64, score_threshold=0.1,
+                               nms_radius=2, synthetic_seed=0, batch_size=3)
+    ex.extract(d, db_path, "SIMPLE_RADIAL")
+    con = sqlite3.connect(str(db_path))
+    assert con.execute("SELECT COUNT(*) FROM images").fetchone()[0] == 4
+    assert con.execute("SELECT model, params FROM cameras").fetchone()[0] == 2
+    rows = con.execute("SELECT rows, cols FROM keypoints ORDER BY image_id").fetchall()
+    assert len(rows) == 4 and all(c == 6 and 0 < r <= 512 for r, c in rows)
+    drows = con.execute("SELECT rows, cols FROM descriptors ORDER BY image_id").fetchall()
+    assert [r for r, _ in drows] == [r for r, _ in rows] and all(c == 64 for _, c in drows)
+    with ColmapDatabase.open_database(str(db_path)) as db:
+        k = db.read_keypoints(1)
+        assert k.dtype == np.float32 and k.shape[1] == 6
+        assert k[:, 0].min() >= 0 and k[:, 0].max() <= 299 and k[:, 1].max() <= 239
+        assert np.all(np.diff(k[:, 4]) <= 0) and k[:, 4].min() > 0.1
+    res = match_exhaustive(str(db_path))
+    assert len(res) == 6
+    assert con.execute("SELECT COUNT(*) FROM matches").fetchone()[0] == 6
+    ex.backbone.close()

@@ -50,7 +50,7 @@ SIGNATURES = {
     "vc_select_keypoints": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_int, c_float,
                                     c_void_p, c_void_p, c_void_p, c_int, c_void_p]),
     "vc_sample_pack": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_int, c_int64,
-                               c_void_p, c_int, c_void_p, c_int, c_void_p, c_int, c_int,
+                               c_void_p, c_int, c_void_p, c_int, c_void_p, c_void_p, c_int, c_int,
                                POINTER(c_float), c_void_p, c_void_p, c_void_p, c_void_p, c_void_p]),
     "vc_trainable_workspace_bytes": (c_size_t, [c_int, c_int, c_int]),
     "vc_trainable_select": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_float, c_int, c_int,

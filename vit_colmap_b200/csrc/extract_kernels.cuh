@@ -49,6 +49,7 @@ struct SampleParams {
   const int32_t* counts;  // [B]
   int cap;
   const float* projection;  // [C, d] or nullptr (then d == C)
+  const float* proj_bias;   // [d] added after the projection, or nullptr
   int d;
   int quant_mode;      // 0: trunc(clip(512 v, 0, 255)) (vit); 1: round, COLMAP; 2: (v+1)*127.5
   float norm_eps;      // F.normalize eps: 1e-12 (vit_extractor.py:243), 1e-8 (vit_feature_model.py:226)

@@ -251,8 +251,9 @@ __global__ void __launch_bounds__(256) sample_pack_project(const SampleParams p,
         acc[6] = fmaf(e.z, w, acc[6]);
         acc[7] = fmaf(e.w, w, acc[7]);
       }
+      const float bj = p.proj_bias ? __ldg(p.proj_bias + j) : 0.f;
 #pragma unroll
-      for (int i = 0; i < 8; ++i) outp[(size_t)(grp * 8 + i) * p.d + j] = acc[i];
+      for (int i = 0; i < 8; ++i) outp[(size_t)(grp * 8 + i) * p.d + j] = acc[i] + bj;
     }
   }
   __syncthreads();

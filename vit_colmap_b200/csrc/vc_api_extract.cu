@@ -117,8 +117,8 @@ int vc_select_keypoints(vc_handle* h, const float* score, int n_images, int grid
 
 int vc_sample_pack(vc_handle* h, const void* tokens, int dtype, int n_images, int grid_h, int grid_w,
                    int channels, int64_t image_stride, const void* coords, int coords_are_float,
-                   const int32_t* counts, int capacity, const float* projection, int d, int quant_mode,
-                   const float* kp_scale, float* keypoints, void* desc_bf16, uint8_t* desc_u8,
+                   const int32_t* counts, int capacity, const float* projection,
+                   const float* projection_bias, int d, int quant_mode, const float* kp_scale, float* keypoints, void* desc_bf16, uint8_t* desc_u8,
                    float* desc_f32, void* stream) {
   if (!h) return fail(VC_ERR_INVALID, "null handle");
   if (n_images <= 0 || grid_h <= 0 || grid_w <= 0) return fail(VC_ERR_INVALID, "bad sizes");
@@ -150,6 +150,7 @@ int vc_sample_pack(vc_handle* h, const void* tokens, int dtype, int n_images, in
   p.counts = counts;
   p.cap = capacity;
   p.projection = projection;
+  p.proj_bias = projection ? projection_bias : nullptr;
   p.d = d;
   p.quant_mode = quant_mode;
   p.norm_eps = quant_mode == VC_QUANT_TRAINABLE ? 1e-8f : 1e-12f;

@@ -107,7 +107,7 @@ class PostProcessor:
         return coords, scores, counts
 
     def sample_pack(self, tokens, grid_hw, coords, counts, orig_wh, resized_wh, projection=None,
-                    quant_mode: int = QUANT_VIT, want_f32: bool = False):
+                    quant_mode: int = QUANT_VIT, want_f32: bool = False, projection_bias=None):
         torch = self.torch
         H, W = grid_hw
         B, T, C = tokens.shape
@@ -125,7 +125,8 @@ class PostProcessor:
         is_float = coords.dtype == torch.float32
         _lib.check(self.lib.vc_sample_pack(self.handle, _ptr(tokens), self._dtype_code(torch, tokens), B, H, W, C,
                                            int(tokens.stride(0)), _ptr(coords.contiguous()), int(is_float),
-                                           _ptr(counts), cap, _ptr(projection), d, int(quant_mode), scale,
+                                           _ptr(counts), cap, _ptr(projection), _ptr(projection_bias), d, int(quant_mode),
+                                           scale,
                                            _ptr(kps), _ptr(dbf), _ptr(du8), _ptr(df32), self._stream()))
         return kps, dbf, du8, df32
 
@@ -141,15 +142,18 @@ class PostProcessor:
 
 def trainable_select_pack(pp: PostProcessor, kp_map, desc_map, orig_wh, resized_wh, num_keypoints: int = 2048,
                           score_threshold: float = 0.0, nms_radius: int = 4, apply_tanh: bool = False,
-                          want_f32: bool = False):
+                          want_f32: bool = False, projection=None, projection_bias=None):
     """Selection + packing stage of the `trainable_vit` extractor
     (vit_colmap/features/trainable_vit_extractor.py:173-269) on channel-last head outputs:
-    kp_map f32 [B, h4, w4, 4], desc_map f32/bf16 [B, h4, w4, d] (un-normalised is fine: rows are
-    L2-normalised with the model's eps 1e-8 as they are packed).
+    kp_map f32 [B, h4, w4, 4], desc_map f32/bf16 [B, h4, w4, c] (un-normalised is fine: rows are
+    L2-normalised with the model's eps 1e-8 as they are packed).  With ``projection`` f32 [c, d]
+    (+ ``projection_bias`` [d]) desc_map is the descriptor head's hidden map and its 1x1 convolution
+    (vit_feature_model.py:120) is applied only at the selected keypoints.
     Returns (keypoints f32 [B,cap,6], desc_u8 [B,cap,d], desc_bf16, desc_f32|None, counts int32 [B])."""
     torch = pp.torch
     B, h4, w4, _ = kp_map.shape
-    d = int(desc_map.shape[3])
+    c = int(desc_map.shape[3])
+    d = c if projection is None else int(projection.shape[1])
     kp_map = kp_map.contiguous()
     desc_map = desc_map.contiguous()
     cap = min(int(num_keypoints), h4 * w4)
@@ -167,8 +171,12 @@ def trainable_select_pack(pp: PostProcessor, kp_map, desc_map, orig_wh, resized_
     dbf = torch.zeros((B, cap, d), dtype=torch.bfloat16, device=kp_map.device)
     du8 = torch.zeros((B, cap, d), dtype=torch.uint8, device=kp_map.device)
     df32 = torch.zeros((B, cap, d), dtype=torch.float32, device=kp_map.device) if want_f32 else None
-    tok = desc_map.reshape(B, h4 * w4, d)
-    _lib.check(pp.lib.vc_sample_pack(pp.handle, _ptr(tok), pp._dtype_code(torch, tok), B, h4, w4, d, int(tok.stride(0)),
-                                     _ptr(coords), 0, _ptr(counts), cap, 0, d, QUANT_TRAINABLE, None, 0, _ptr(dbf),
-                                     _ptr(du8), _ptr(df32), pp._stream()))
+    tok = desc_map.reshape(B, h4 * w4, c)
+    if projection is not None:
+        projection = projection.to(device=kp_map.device, dtype=torch.float32).contiguous()
+        if projection_bias is not None:
+            projection_bias = projection_bias.to(device=kp_map.device, dtype=torch.float32).contiguous()
+    _lib.check(pp.lib.vc_sample_pack(pp.handle, _ptr(tok), pp._dtype_code(torch, tok), B, h4, w4, c, int(tok.stride(0)),
+                                     _ptr(coords), 0, _ptr(counts), cap, _ptr(projection), _ptr(projection_bias), d,
+                                     QUANT_TRAINABLE, None, 0, _ptr(dbf), _ptr(du8), _ptr(df32), pp._stream()))
     return kps, du8, dbf, df32, counts
