@@ -298,6 +298,7 @@ def run_ours(args):
     _lib.launch_count(reset=True)
     extract = run_extract(args, torch, dist, dev, local, world) if not args.skip_extract else None
     extract_launches = _lib.launch_count()
+    extract_tr = run_extract_trainable(args, torch, dist, dev, local, world) if not args.skip_extract else None
     if rank == 0:
         cpu_v, cpu_rows, cpu_dt, cpu_threads = (cpu_sample(12.0) if world == 1 else (None, 0, 0, 0))
         line = {
@@ -326,6 +327,7 @@ def run_ours(args):
                                            "sample": f"{en} images ({edt:.1f} s), fp32 PyTorch DINOv2 restatement + "
                                                      "reference post-processing restatement"}
             line["extract"] = extract
+            line["extract_trainable"] = extract_tr
         if allgather_ms is not None:
             line["allgather_ms"] = allgather_ms
         if cpu_v is not None:
@@ -422,6 +424,57 @@ def run_extract(args, torch, dist, dev, local, world):
                      "note": "algorithmic 303.1 GFLOP per image (SURVEY 8d) x 32 images over the whole forward; "
                              "per-kernel shares in profiles/"},
     }
+
+
+def run_extract_trainable(args, torch, dist, dev, local, world):
+    """Config C4's extraction side: the `trainable_vit` extractor (DINOv2 ViT-B/14 backbone +
+    ViTFeatureModel conv head + max-pool NMS selection + sparse descriptor projection) at 518x518,
+    d = 128, num_keypoints 8192.  Synthetic images, seeded random-init weights."""
+    from vit_colmap_b200.features.trainable_vit_extractor import TrainableViTExtractor
+    B = 16
+    ex = TrainableViTExtractor(model_name=EXTRACT_MODEL, num_keypoints=8192, descriptor_dim=128,
+                               device=f"cuda:{local}", score_threshold=0.0, nms_radius=1, synthetic_seed=0,
+                               batch_size=B)
+    g = torch.Generator(device=dev)
+    g.manual_seed(2)
+    imgs = torch.randint(0, 256, (B, EXTRACT_SIZE, EXTRACT_SIZE, 3), generator=g, device=dev, dtype=torch.uint8)
+    gh = EXTRACT_SIZE // 14
+    wh = (EXTRACT_SIZE, EXTRACT_SIZE)
+    tokens = ex.backbone.forward_patch_tokens(imgs, bgr=True)
+
+    def timed(fn, n):
+        for _ in range(3):
+            fn()
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        e0, e1 = torch.cuda.Event(True), torch.cuda.Event(True)
+        e0.record()
+        for _ in range(n):
+            fn()
+        e1.record()
+        torch.cuda.synchronize()
+        t = torch.tensor([e0.elapsed_time(e1) / n], dtype=torch.float64, device=dev)
+        if world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    n = max(2, min(args.steps, 5))
+    ms = timed(lambda: ex._forward_device(imgs, wh, wh), n)
+    ms_head = timed(lambda: ex.head.forward(tokens, (gh, gh), dense_descriptors=False), n)
+    counts = ex._forward_device(imgs, wh, wh)[4]
+    peak_tf, _, peak_src = _peaks()
+    tf = ex.head.flops_per_image(gh, gh) * B / (ms_head / 1e3) / 1e12
+    return {"metric": "extracted_images_per_sec@trainable_vitb14_518px_d128", "value": world * B / (ms / 1e3),
+            "unit": "images/s", "ms_per_step": ms, "dtype": "bf16",
+            "config": {"workload": f"{EXTRACT_MODEL} forward + conv head + NMS/top-8192 selection + sparse 128-d "
+                                   f"descriptors, batch {B} x {EXTRACT_SIZE}x{EXTRACT_SIZE} per GPU per step",
+                       "mean_keypoints_per_image": float(counts.float().mean().item())},
+            "roofline": {"bound": "tensor", "achieved": tf, "peak": peak_tf, "unit": "TFLOP/s", "frac": tf / peak_tf,
+                         "traffic": None, "peak_source": f"{peak_src} sustained bf16",
+                         "kernel": "vc_conv_head_forward (conv_gemm_kernel launches)", "kernel_ms": ms_head,
+                         "note": f"algorithmic {ex.head.flops_per_image(gh, gh) / 1e9:.1f} GFLOP per image for the "
+                                 "head (2*MACs of the seven convolutions, SURVEY 8a T1)"}}
 
 
 def cpu_extract_sample(n_images=2):
