@@ -140,3 +140,37 @@ def test_u8_compat_mode_bit_exact(matcher):
     both = np.stack([d1, d1[::-1].copy()])
     (m,) = matcher.match_pairs_host(both, np.array([50, 50], np.int32), np.array([[0, 1]], np.int32))
     assert len(m) == 50 and all(j == 49 - i for i, j in m.tolist())
+
+
+def test_full_size_8192_d768_against_oracle_and_properties(matcher):
+    """BASELINE.json's headline size (N = M = 8192, d = 768).  (a) one pair against the C oracle
+    directly (51 GFLOP on the host cores); (b) size-independent properties: a permuted copy matches
+    through the permutation, swapping the pair transposes the match list, an image against itself
+    yields the identity, and the ragged count 8191 works."""
+    import torch
+    rng = np.random.default_rng(8192)
+    kmax, d = 8192, 768
+    counts = [8192, 8192, 8192, 8191]
+    desc = _make_set(rng, 2, kmax, d, counts[:2])
+    perm = rng.permutation(kmax)
+    desc = np.concatenate([desc, desc[0][perm][None], desc[1][None]], axis=0)
+    desc[3, 8191] = 0
+    n_exact = _compare_with_oracle(matcher, desc, counts, [(0, 1)], 0.8, 0.7, True)
+    assert n_exact == 1
+    t = torch.from_numpy(desc).cuda().to(torch.bfloat16)
+    c = torch.tensor(counts, dtype=torch.int32, device="cuda")
+    pairs = [(0, 1), (1, 0), (0, 2), (0, 0), (0, 3)]
+    p = torch.tensor(pairs, dtype=torch.int32, device="cuda")
+    m, n = matcher.match_pairs(t, c, p, 0.8, 0.7, True, 1.0)
+    torch.cuda.synchronize()
+    m, n = m.cpu().numpy(), n.cpu().numpy()
+    fwd, bwd = m[0, : n[0]], m[1, : n[1]]
+    assert n[0] > 3000 and np.all(np.diff(fwd[:, 0].astype(np.int64)) > 0)      # ascending idx1
+    assert sorted(map(tuple, fwd.tolist())) == sorted((j, i) for i, j in bwd.tolist())
+    pm = m[2, : n[2]]
+    assert n[2] == kmax and np.array_equal(perm[pm[:, 1]], pm[:, 0])            # row perm[k] of image 0 is row k of image 2
+    ident = m[3, : n[3]]
+    assert n[3] == kmax and np.array_equal(ident[:, 0], ident[:, 1])           # an image against itself: identity
+    keep = fwd[fwd[:, 1] != 8191]
+    got3 = m[4, : n[4]]
+    assert abs(int(n[4]) - len(keep)) <= 2 and len(set(map(tuple, got3.tolist())) ^ set(map(tuple, keep.tolist()))) <= 4
