@@ -3,18 +3,22 @@
 //
 // CTA = (image, head, pair of 128-row query tiles).  Roles:
 //   warp 0  TMA: both Q tiles once, then a 3-stage ring of (K_j, V_j) 128-key tiles (128B swizzle)
-//   warp 1  tcgen05.mma issuer: S_w = Q_w K_j^T (M128 N128 K64) into TMEM, and, once the softmax
-//           warps have published P_w (bf16, written to shared memory in the K-major swizzled
-//           operand layout), O_w^(j) = P_w V_j (M128 N64 K128; V is consumed as an MN-major operand
-//           exactly as TMA delivered it, so no transposed copy of V exists anywhere)
-//           and allocates TMEM (S_0, S_1: 2 x 128 columns, O_0, O_1: 2 x 64 columns).  O accumulates
-//           in TMEM across the key tiles.
-//   warps 2-5 / 6-9  softmax warpgroup of query tile 0 / 1: thread = one query row.  The 128 scores
-//           of a tile are pulled into registers with one round of tcgen05.ld (TMEM latency is paid
-//           once per tile), online softmax in the exp2 domain with a lazily updated reference
-//           maximum: O and the row sum are only rescaled when the maximum grew by more than 2^8
-//           (probabilities stay <= 256, exact in the final normalisation), so the TMEM
-//           read-modify-write of O is rare.
+//   warp 1 / 2  tcgen05.mma issuer of query tile 0 / 1 (warp 1 also allocates TMEM; one issuer per
+//           tile so every wait is a blocking mbarrier wait in its natural order, no polling):
+//           S_w = Q_w K_j^T (M128 N128 K64) into TMEM as soon as the softmax threads have pulled the
+//           previous S_w into registers (so Q K^T of tile j+1 overlaps the softmax of tile j), and,
+//           once a softmax half has published its P (bf16, written to shared memory in the K-major
+//           swizzled operand layout), O_{w,h} += P_{w,h} V_{j,h} (M128 N64 K64; V is consumed as an
+//           MN-major operand exactly as TMA delivered it, so no transposed copy of V exists).
+//           TMEM: S_0, S_1 (2 x 128 columns), O_{w,h} (4 x 64 columns).
+//   warps 4-11 / 12-19  softmax warpgroup of query tile 0 / 1, 256 threads: thread = one query row x
+//           one 64-key half of the tile (warp%4 = TMEM lane quarter, (warp-4)/4%2 = key half), so
+//           every SM sub-partition holds four softmax warps to hide the MUFU / TMEM latencies.
+//           The two key halves of a row are independent split-K streams: each keeps its own lazily
+//           updated reference maximum, row sum and O accumulator (rescaled only when the maximum
+//           grew by more than 2^8, so the TMEM read-modify-write of O is rare) and never
+//           synchronises with its sibling until the end, where the two partial results are merged
+//           as in split-K flash attention: O = (a0 O_0 + a1 O_1) / (a0 l_0 + a1 l_1), a_h = 2^(m_h - m).
 // The two warpgroups share every K/V tile and keep the tensor core busy for each other.
 #include "vit_kernels.cuh"
 
@@ -31,9 +35,10 @@ constexpr int kTile = 128, kHd = 64, kKvStages = 3;
 constexpr int kQBytes = kTile * kHd * 2;          // 16 KB
 constexpr int kKvBytes = 2 * kTile * kHd * 2;     // K + V of one stage, 32 KB
 constexpr int kPBytes = kTile * kTile * 2;        // 32 KB per warpgroup
-constexpr int kThreads = 320;  // warp 0 TMA, warp 1 MMA + TMEM alloc, warps 2-9 softmax
+constexpr int kThreads = 640;  // warps 0-3 control (TMA, two MMA issuers, spare), warps 4-19 softmax
 constexpr int kTmemCols = 512;
-constexpr int kSmemBytes = 2 * kQBytes + kKvStages * kKvBytes + 2 * kPBytes + 1024 + 256;
+constexpr int kXchBytes = 2 * 2 * kTile * 8;      // (m, l) of every (warpgroup, half, row)
+constexpr int kSmemBytes = 2 * kQBytes + kKvStages * kKvBytes + 2 * kPBytes + kXchBytes + 1024 + 256;
 
 // K-major A (bits 15 = 0), MN-major B (bit 16 = 1): B = V tile [keys, 64] with the head dim contiguous
 __host__ __device__ constexpr uint32_t idesc_pv() { return umma_idesc_bf16(128, 64) | (1u << 16); }
@@ -79,48 +84,42 @@ __device__ __forceinline__ uint32_t pack_bf16(float a, float b) {
 }
 
 
-// One 128-key tile of the online softmax for one query row.  kMasked is only instantiated for the
-// last, partial key tile, so full tiles carry no per-element selects.
+// One 64-key half tile of the online softmax for one query row (thread = row x key half).  The 64
+// scores are pulled into registers with one round of tcgen05.ld and never re-read.  kMasked is only
+// instantiated for the last, partial key tile, so full tiles carry no per-element selects.
 template <bool kMasked>
-__device__ __forceinline__ void softmax_tile(uint32_t t_s, uint32_t t_o, uint8_t* prow, int r, int valid,
-                                             float sc, bool have_o, float& m_ref, float& l_run) {
-  // Software pipeline over TMEM: every tcgen05.ld is issued one step ahead of the arithmetic that
-  // consumes it (tcgen05.wait::ld waits for all outstanding loads, so the order is ld-next,
-  // compute-current, wait).  Pass 1 (maximum) reads the tile as two 64-column halves, pass 2
-  // (probabilities) as four 32-column chunks.
-  auto mask = [&](uint32_t (&x)[32], int col0) {
-    if (kMasked) {
+__device__ __forceinline__ void softmax_half(uint32_t t_s, uint32_t t_o, uint8_t* prow, int r, int valid,
+                                             float sc, bool have_o, uint32_t bar_s_free, uint32_t bar_o_ready,
+                                             uint32_t o_parity, float& m_ref, float& l_run) {
+  uint32_t a[32], b[32];
+  tmem_ld_32x32(t_s, a);
+  tmem_ld_32x32(t_s + 32, b);
+  tmem_wait_ld();
+  // the scores now live in registers: hand S back so Q K^T of the next key tile overlaps this softmax
+  tc_fence_before();
+  mbar_arrive(bar_s_free);
+  if (kMasked) {
 #pragma unroll
-      for (int e = 0; e < 32; ++e)
-        if (col0 + e >= valid) x[e] = 0xFF800000u;  // -inf
+    for (int e = 0; e < 32; ++e) {
+      if (e >= valid) a[e] = 0xFF800000u;  // -inf
+      if (32 + e >= valid) b[e] = 0xFF800000u;
     }
-  };
+  }
   float mx[4] = {-1e30f, -1e30f, -1e30f, -1e30f};
-  auto fold_max = [&](const uint32_t (&x)[32]) {
 #pragma unroll
-    for (int e = 0; e < 32; e += 8) {
+  for (int e = 0; e < 32; e += 8) {
 #pragma unroll
-      for (int a = 0; a < 4; ++a)
-        mx[a] = fmax3(mx[a], __uint_as_float(x[e + 2 * a]), __uint_as_float(x[e + 2 * a + 1]));
+    for (int q = 0; q < 4; ++q) {
+      mx[q] = fmax3(mx[q], __uint_as_float(a[e + 2 * q]), __uint_as_float(a[e + 2 * q + 1]));
+      mx[q] = fmax3(mx[q], __uint_as_float(b[e + 2 * q]), __uint_as_float(b[e + 2 * q + 1]));
     }
-  };
-  uint32_t a0[32], a1[32], b0[32], b1[32];
-  tmem_ld_32x32(t_s, a0);
-  tmem_ld_32x32(t_s + 32, a1);
-  tmem_wait_ld();
-  tmem_ld_32x32(t_s + 64, b0);
-  tmem_ld_32x32(t_s + 96, b1);
-  mask(a0, 0);
-  mask(a1, 32);
-  fold_max(a0);
-  fold_max(a1);
-  tmem_wait_ld();
-  tmem_ld_32x32(t_s, a0);  // first chunk of pass 2, in flight during the rest of pass 1
-  mask(b0, 64);
-  mask(b1, 96);
-  fold_max(b0);
-  fold_max(b1);
+  }
   const float m_tile = fmaxf(fmaxf(mx[0], mx[1]), fmaxf(mx[2], mx[3])) * sc;
+  if (have_o) {
+    // P V of the previous key tile must have completed before P is overwritten / O is rescaled
+    mbar_wait_sleep(bar_o_ready, o_parity, 20);
+    tc_fence_after();
+  }
   // lazy reference maximum: move it (and rescale O, l) only when it is more than 2^8 behind
   if (__any_sync(0xffffffffu, m_tile > m_ref + 8.0f)) {
     const float m_new = fmaxf(m_ref, m_tile);
@@ -129,27 +128,25 @@ __device__ __forceinline__ void softmax_tile(uint32_t t_s, uint32_t t_o, uint8_t
     l_run *= alpha;
     if (have_o) {
       const float2 a2 = make_float2(alpha, alpha);
-      tmem_ld_32x32(t_o, b0);
-      tmem_ld_32x32(t_o + 32, b1);
-      tmem_wait_ld();
+#pragma unroll 1
+      for (int c = 0; c < 2; ++c) {
+        uint32_t o[32];
+        tmem_ld_32x32(t_o + c * 32, o);
+        tmem_wait_ld();
 #pragma unroll
-      for (int e = 0; e < 32; e += 2) {
-        float2 t = fmul2(make_float2(__uint_as_float(b0[e]), __uint_as_float(b0[e + 1])), a2);
-        b0[e] = __float_as_uint(t.x);
-        b0[e + 1] = __float_as_uint(t.y);
-        t = fmul2(make_float2(__uint_as_float(b1[e]), __uint_as_float(b1[e + 1])), a2);
-        b1[e] = __float_as_uint(t.x);
-        b1[e + 1] = __float_as_uint(t.y);
+        for (int e = 0; e < 32; e += 2) {
+          const float2 t = fmul2(make_float2(__uint_as_float(o[e]), __uint_as_float(o[e + 1])), a2);
+          o[e] = __float_as_uint(t.x);
+          o[e + 1] = __float_as_uint(t.y);
+        }
+        tmem_st_32x32(t_o + c * 32, o);
       }
-      tmem_st_32x32(t_o, b0);
-      tmem_st_32x32(t_o + 32, b1);
       tmem_wait_st();
     }
   }
   const float2 sc2 = make_float2(sc, sc), nm2 = make_float2(-m_ref, -m_ref);
   float2 sum[2] = {make_float2(0.f, 0.f), make_float2(0.f, 0.f)};
   auto emit = [&](uint32_t (&x)[32], int c) {
-    mask(x, c * 32);
     uint32_t pk[16];
 #pragma unroll
     for (int e = 0; e < 16; ++e) {
@@ -159,26 +156,16 @@ __device__ __forceinline__ void softmax_tile(uint32_t t_s, uint32_t t_o, uint8_t
       sum[e & 1] = fadd2(sum[e & 1], y);
       pk[e] = pack_bf16(y.x, y.y);
     }
-    // chunk c covers keys [32c, 32c+32): half c>>1, 16-byte chunks (c&1)*4 .. +3 of the swizzled row
-    uint8_t* half = prow + (c >> 1) * (kPBytes / 2);
+    // chunk c covers keys [32c, 32c+32) of this half: 16-byte chunks 4c .. 4c+3 of the swizzled row
 #pragma unroll
     for (int g = 0; g < 4; ++g) {
-      const int chunk = ((c & 1) * 4 + g) ^ (r & 7);
-      *reinterpret_cast<uint4*>(half + chunk * 16) =
+      const int chunk = (c * 4 + g) ^ (r & 7);
+      *reinterpret_cast<uint4*>(prow + chunk * 16) =
           make_uint4(pk[4 * g], pk[4 * g + 1], pk[4 * g + 2], pk[4 * g + 3]);
     }
   };
-  tmem_wait_ld();
-  tmem_ld_32x32(t_s + 32, a1);
-  emit(a0, 0);
-  tmem_wait_ld();
-  tmem_ld_32x32(t_s + 64, a0);
-  emit(a1, 1);
-  tmem_wait_ld();
-  tmem_ld_32x32(t_s + 96, a1);
-  emit(a0, 2);
-  tmem_wait_ld();
-  emit(a1, 3);
+  emit(a, 0);
+  emit(b, 1);
   l_run += (sum[0].x + sum[0].y) + (sum[1].x + sum[1].y);
 }
 
@@ -194,15 +181,18 @@ vit_attention_kernel(const __grid_constant__ CUtensorMap map_qkv, const AttnPara
   const uint32_t sKV = sQ + 2 * kQBytes;                       // stages x (K 16 KB, V 16 KB)
   const uint32_t sP = sKV + kKvStages * kKvBytes;              // 2 x 32 KB
   uint8_t* sP_gen = smem + 2 * kQBytes + kKvStages * kKvBytes;
-  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + 2 * kQBytes + kKvStages * kKvBytes + 2 * kPBytes);
+  float2* xch = reinterpret_cast<float2*>(sP_gen + 2 * kPBytes);  // [2 wg][2 halves][128 rows] (m, l)
+  uint64_t* bars = reinterpret_cast<uint64_t*>(sP_gen + 2 * kPBytes + kXchBytes);
   const uint32_t bar0 = smem_u32(bars);
   const uint32_t q_full = bar0;
   auto kv_full = [&](int s) { return bar0 + 8u * (1 + s); };
   auto kv_empty = [&](int s) { return bar0 + 8u * (1 + kKvStages + s); };
   auto s_full = [&](int w) { return bar0 + 8u * (1 + 2 * kKvStages + w); };
-  auto p_full = [&](int w) { return bar0 + 8u * (3 + 2 * kKvStages + w); };
-  auto o_full = [&](int w) { return bar0 + 8u * (5 + 2 * kKvStages + w); };
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 7 + 2 * kKvStages);
+  auto s_free = [&](int w) { return bar0 + 8u * (3 + 2 * kKvStages + w); };
+  auto p_full = [&](int w, int h) { return bar0 + 8u * (5 + 2 * kKvStages + 2 * w + h); };
+  auto o_ready = [&](int w, int h) { return bar0 + 8u * (9 + 2 * kKvStages + 2 * w + h); };
+  auto o_full = [&](int w) { return bar0 + 8u * (13 + 2 * kKvStages + w); };
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 15 + 2 * kKvStages);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int C = p.heads * kHd;
@@ -219,12 +209,16 @@ vit_attention_kernel(const __grid_constant__ CUtensorMap map_qkv, const AttnPara
     mbar_init(q_full, 1);
     for (int s = 0; s < kKvStages; ++s) {
       mbar_init(kv_full(s), 1);
-      mbar_init(kv_empty(s), 1);
+      mbar_init(kv_empty(s), nw);
     }
     for (int w = 0; w < 2; ++w) {
       mbar_init(s_full(w), 1);
-      mbar_init(p_full(w), 128);
+      mbar_init(s_free(w), 256);
       mbar_init(o_full(w), 1);
+      for (int h = 0; h < 2; ++h) {
+        mbar_init(p_full(w, h), 128);
+        mbar_init(o_ready(w, h), 1);
+      }
     }
     fence_mbar_init();
   }
@@ -251,93 +245,101 @@ vit_attention_kernel(const __grid_constant__ CUtensorMap map_qkv, const AttnPara
       tma_load_3d(sKV + s * kKvBytes + kKvBytes / 2, &map_qkv, kv_full(s), 2 * C + head * kHd, j * kTile,
                   img);
     }
-  } else if (warp == 1 && lane == 0) {
-    // ------------------------------------------------------------ MMA issuer
+  } else if ((warp == 1 || warp == 2) && lane == 0 && warp - 1 < nw) {
+    // ------------------------------------------------------------ MMA issuer of query tile w
+    const int w = warp - 1;
     constexpr uint32_t idesc_s = umma_idesc_bf16(128, 128);
     constexpr uint32_t idesc_o = idesc_pv();
-    auto issue_s = [&](int w, int s) {
-      const uint64_t da = umma_desc_k_sw128(sQ + w * kQBytes);
+    const uint64_t dq = umma_desc_k_sw128(sQ + w * kQBytes);
+    auto issue_s = [&](int s) {
       const uint64_t db = umma_desc_k_sw128(sKV + s * kKvBytes);
 #pragma unroll
       for (int k = 0; k < kHd / 16; ++k)
-        tc_mma_bf16(tmem_base + w * 128, da + 2 * k, db + 2 * k, idesc_s, k != 0);
+        tc_mma_bf16(tmem_base + w * 128, dq + 2 * k, db + 2 * k, idesc_s, k != 0);
       tc_commit(s_full(w));
     };
     mbar_wait(q_full, 0);
     mbar_wait(kv_full(0), 0);
     tc_fence_after();
-    for (int w = 0; w < nw; ++w) issue_s(w, 0);
+    issue_s(0);
     for (int j = 0; j < nkv; ++j) {
       const int s = j % kKvStages;
-      const bool more = j + 1 < nkv;
-      const int s1 = (j + 1) % kKvStages;
-      if (more) {
-        mbar_wait(kv_full(s1), ((j + 1) / kKvStages) & 1);
+      if (j + 1 < nkv) {
+        const int s1 = (j + 1) % kKvStages;
+        mbar_wait_sleep(kv_full(s1), ((j + 1) / kKvStages) & 1, 32);
+        mbar_wait_sleep(s_free(w), j & 1, 32);   // S_w(j) is in the softmax threads' registers
         tc_fence_after();
+        issue_s(s1);
       }
-      for (int w = 0; w < nw; ++w) {
-        mbar_wait_sleep(p_full(w), j & 1, 32);
-        tc_fence_after();
-        // O_w += P_w (128 x 128, two 64-key halves, K-major) * V_j (128 keys x 64, MN-major)
-        const uint32_t pw = sP + w * kPBytes;
-        const uint64_t dv = umma_desc_k_sw128(sKV + s * kKvBytes + kKvBytes / 2);
+      const uint64_t dv = umma_desc_k_sw128(sKV + s * kKvBytes + kKvBytes / 2);
 #pragma unroll
-        for (int k = 0; k < kTile / 16; ++k) {
-          const uint64_t dp = umma_desc_k_sw128(pw + (k >> 2) * (kPBytes / 2)) + 2 * (k & 3);
-          tc_mma_bf16(tmem_base + 256 + w * 64, dp, dv + 128 * k, idesc_o, (j | k) != 0);
-        }
-        if (!more) tc_commit(o_full(w));
-        if (more) issue_s(w, s1);   // its commit also covers the P V above: S_w ready => O_w up to date
+      for (int h = 0; h < 2; ++h) {
+        mbar_wait_sleep(p_full(w, h), j & 1, 32);
+        tc_fence_after();
+        // O_{w,h} += P_{w,h} (128 x 64 keys, K-major) * V_j rows [64h, 64h+64) (MN-major)
+        const uint64_t dp = umma_desc_k_sw128(sP + w * kPBytes + h * (kPBytes / 2));
+#pragma unroll
+        for (int k = 0; k < 4; ++k)
+          tc_mma_bf16(tmem_base + 256 + (2 * w + h) * 64, dp + 2 * k, dv + 128 * (4 * h + k), idesc_o,
+                      (j | k) != 0);
+        tc_commit(o_ready(w, h));
       }
+      if (j + 1 == nkv) tc_commit(o_full(w));
       tc_commit(kv_empty(s));
     }
-  } else if (warp >= 2 && (warp - 2) / 4 < nw) {
+  } else if (warp >= 4 && (warp - 4) / 8 < nw) {
     // ------------------------------------------------------------ softmax warpgroups
-    const int w = (warp - 2) >> 2;
-    const int quarter = warp & 3;       // TMEM lane quarter a warp may touch = warp id % 4
-    const int r = quarter * 32 + lane;  // row inside the query tile == TMEM lane
-    const uint32_t t_s = tmem_base + (static_cast<uint32_t>(quarter * 32) << 16) + w * 128;
-    const uint32_t t_o = tmem_base + (static_cast<uint32_t>(quarter * 32) << 16) + 256 + w * 64;
+    const int w = (warp - 4) >> 3;
+    const int h = ((warp - 4) >> 2) & 1;  // key half
+    const int quarter = warp & 3;         // TMEM lane quarter a warp may touch = warp id % 4
+    const int r = quarter * 32 + lane;    // row inside the query tile == TMEM lane
+    const uint32_t lane_base = tmem_base + (static_cast<uint32_t>(quarter * 32) << 16);
+    const uint32_t t_s = lane_base + w * 128 + h * 64;
+    const uint32_t t_o = lane_base + 256 + (2 * w + h) * 64;
     const float sc = p.scale * 1.4426950408889634f;  // scores are handled in the exp2 domain
-    uint8_t* prow = sP_gen + w * kPBytes + r * 128;
+    uint8_t* prow = sP_gen + w * kPBytes + h * (kPBytes / 2) + r * 128;
     float m_ref = -1e30f, l_run = 0.f;
     for (int j = 0; j < nkv; ++j) {
-      const int valid = min(kTile, p.T - j * kTile);  // keys of this tile inside the image
+      // keys of this half tile inside the image
+      const int valid = min(kTile / 2, p.T - j * kTile - h * (kTile / 2));
       mbar_wait_sleep(s_full(w), j & 1, 32);
-      if (p.alternate && nw == 2) {
-        // optional turn-taking: one warpgroup runs its softmax while the tensor core serves the other
-        if (w == 1) mbar_wait_sleep(p_full(0), j & 1, 64);
-        else if (j > 0) mbar_wait_sleep(p_full(1), (j - 1) & 1, 64);
-      }
       tc_fence_after();
-      if (valid == kTile)
-        softmax_tile<false>(t_s, t_o, prow, r, valid, sc, j > 0, m_ref, l_run);
+      if (valid == kTile / 2)
+        softmax_half<false>(t_s, t_o, prow, r, valid, sc, j > 0, s_free(w), o_ready(w, h), (j - 1) & 1, m_ref, l_run);
       else
-        softmax_tile<true>(t_s, t_o, prow, r, valid, sc, j > 0, m_ref, l_run);
+        softmax_half<true>(t_s, t_o, prow, r, valid, sc, j > 0, s_free(w), o_ready(w, h), (j - 1) & 1, m_ref, l_run);
       fence_proxy_async_smem();
       tc_fence_before();
-      mbar_arrive(p_full(w));
+      mbar_arrive(p_full(w, h));
     }
+    // merge the two key halves of the row (split-K): exchange (m, l) through shared memory
+    xch[(w * 2 + h) * kTile + r] = make_float2(m_ref, l_run);
+    asm volatile("bar.sync %0, 256;" ::"r"(1 + w) : "memory");
+    const float2 other = xch[(w * 2 + (h ^ 1)) * kTile + r];
+    const float m_all = fmaxf(m_ref, other.x);
+    const float a_me = ex2(m_ref - m_all), a_ot = ex2(other.x - m_all);
+    const float inv = 1.0f / (l_run * a_me + other.y * a_ot);
+    const float c0 = (h == 0 ? a_me : a_ot) * inv, c1 = (h == 0 ? a_ot : a_me) * inv;
     mbar_wait_sleep(o_full(w), 0, 32);
     tc_fence_after();
+    // this thread finishes output columns [32h, 32h+32) of its row from both partial accumulators
     const int t = q0 + w * kTile + r;
-    const float inv = 1.0f / l_run;
-    uint4* dst = reinterpret_cast<uint4*>(p.out + ((size_t)img * p.T + t) * C + head * kHd);
+    uint32_t o0[32], o1[32];
+    tmem_ld_32x32(lane_base + 256 + (2 * w) * 64 + h * 32, o0);
+    tmem_ld_32x32(lane_base + 256 + (2 * w + 1) * 64 + h * 32, o1);
+    tmem_wait_ld();
+    if (t < p.T) {
+      uint4* dst = reinterpret_cast<uint4*>(p.out + ((size_t)img * p.T + t) * C + head * kHd + h * 32);
 #pragma unroll
-    for (int c = 0; c < 2; ++c) {
-      uint32_t ov[32];
-      tmem_ld_32x32(t_o + c * 32, ov);
-      tmem_wait_ld();
-      if (t < p.T) {
+      for (int g = 0; g < 4; ++g) {
+        uint32_t pk[4];
 #pragma unroll
-        for (int g = 0; g < 4; ++g) {
-          uint4 pk;
-          pk.x = pack_bf16(__uint_as_float(ov[8 * g + 0]) * inv, __uint_as_float(ov[8 * g + 1]) * inv);
-          pk.y = pack_bf16(__uint_as_float(ov[8 * g + 2]) * inv, __uint_as_float(ov[8 * g + 3]) * inv);
-          pk.z = pack_bf16(__uint_as_float(ov[8 * g + 4]) * inv, __uint_as_float(ov[8 * g + 5]) * inv);
-          pk.w = pack_bf16(__uint_as_float(ov[8 * g + 6]) * inv, __uint_as_float(ov[8 * g + 7]) * inv);
-          dst[c * 4 + g] = pk;
+        for (int e = 0; e < 4; ++e) {
+          const int i0 = 8 * g + 2 * e;
+          pk[e] = pack_bf16(fmaf(__uint_as_float(o0[i0]), c0, __uint_as_float(o1[i0]) * c1),
+                            fmaf(__uint_as_float(o0[i0 + 1]), c0, __uint_as_float(o1[i0 + 1]) * c1));
         }
+        dst[g] = make_uint4(pk[0], pk[1], pk[2], pk[3]);
       }
     }
   }
