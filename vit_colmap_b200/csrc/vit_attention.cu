@@ -84,10 +84,30 @@ __device__ __forceinline__ uint32_t pack_bf16(float a, float b) {
 }
 
 
+// 2^y for a pair on the FMA pipe instead of the MUFU (the kernel is bound by the 16 exp2 per clock of
+// an SM, so a share of the exponentials is moved over, as in FlashAttention-4): Cody-Waite split with
+// the 1.5*2^23 magic constant (n = round(y) lands in the low mantissa bits of t, f = y - n in
+// [-0.5, 0.5]), degree-3 minimax polynomial for 2^f (max relative error 7.5e-5, 50x below the bf16
+// rounding of P), n added into the exponent field.  y is clamped at -125 so the result never
+// leaves the normal range; y <= +8 by construction of the lazy reference maximum.
+__device__ __forceinline__ float2 exp2_poly2(float2 y) {
+  y.x = fmaxf(y.x, -125.0f);
+  y.y = fmaxf(y.y, -125.0f);
+  const float2 magic = make_float2(12582912.0f, 12582912.0f);
+  const float2 t = fadd2(y, magic);
+  const float2 n = fadd2(t, make_float2(-12582912.0f, -12582912.0f));
+  const float2 f = fadd2(y, make_float2(-n.x, -n.y));
+  float2 q = ffma2(make_float2(5.517145991e-02f, 5.517145991e-02f), f, make_float2(2.426108569e-01f, 2.426108569e-01f));
+  q = ffma2(q, f, make_float2(6.932609677e-01f, 6.932609677e-01f));
+  q = ffma2(q, f, make_float2(9.999281168e-01f, 9.999281168e-01f));
+  return make_float2(__uint_as_float(__float_as_uint(q.x) + (__float_as_uint(t.x) << 23)),
+                     __uint_as_float(__float_as_uint(q.y) + (__float_as_uint(t.y) << 23)));
+}
+
 // One 64-key half tile of the online softmax for one query row (thread = row x key half).  The 64
 // scores are pulled into registers with one round of tcgen05.ld and never re-read.  kMasked is only
 // instantiated for the last, partial key tile, so full tiles carry no per-element selects.
-template <bool kMasked>
+template <bool kMasked, int kPolyPairs>
 __device__ __forceinline__ void softmax_half(uint32_t t_s, uint32_t t_o, uint8_t* prow, int r, int valid,
                                              float sc, bool have_o, uint32_t bar_s_free, uint32_t bar_o_ready,
                                              uint32_t o_parity, float& m_ref, float& l_run) {
@@ -129,17 +149,17 @@ __device__ __forceinline__ void softmax_half(uint32_t t_s, uint32_t t_o, uint8_t
     if (have_o) {
       const float2 a2 = make_float2(alpha, alpha);
 #pragma unroll 1
-      for (int c = 0; c < 2; ++c) {
-        uint32_t o[32];
-        tmem_ld_32x32(t_o + c * 32, o);
+      for (int c = 0; c < 4; ++c) {
+        uint32_t o[16];
+        tmem_ld_32x16(t_o + c * 16, o);
         tmem_wait_ld();
 #pragma unroll
-        for (int e = 0; e < 32; e += 2) {
+        for (int e = 0; e < 16; e += 2) {
           const float2 t = fmul2(make_float2(__uint_as_float(o[e]), __uint_as_float(o[e + 1])), a2);
           o[e] = __float_as_uint(t.x);
           o[e + 1] = __float_as_uint(t.y);
         }
-        tmem_st_32x32(t_o + c * 32, o);
+        tmem_st_32x16(t_o + c * 16, o);
       }
       tmem_wait_st();
     }
@@ -147,21 +167,30 @@ __device__ __forceinline__ void softmax_half(uint32_t t_s, uint32_t t_o, uint8_t
   const float2 sc2 = make_float2(sc, sc), nm2 = make_float2(-m_ref, -m_ref);
   float2 sum[2] = {make_float2(0.f, 0.f), make_float2(0.f, 0.f)};
   auto emit = [&](uint32_t (&x)[32], int c) {
-    uint32_t pk[16];
+    // 16 keys at a time keeps the live set small: 8 packed registers, two 16-byte stores
 #pragma unroll
-    for (int e = 0; e < 16; ++e) {
-      float2 y = ffma2(make_float2(__uint_as_float(x[2 * e]), __uint_as_float(x[2 * e + 1])), sc2, nm2);
-      y.x = ex2(y.x);  // masked keys: exp2(-inf) = 0
-      y.y = ex2(y.y);
-      sum[e & 1] = fadd2(sum[e & 1], y);
-      pk[e] = pack_bf16(y.x, y.y);
-    }
-    // chunk c covers keys [32c, 32c+32) of this half: 16-byte chunks 4c .. 4c+3 of the swizzled row
+    for (int q = 0; q < 2; ++q) {
+      uint32_t pk[8];
 #pragma unroll
-    for (int g = 0; g < 4; ++g) {
-      const int chunk = (c * 4 + g) ^ (r & 7);
-      *reinterpret_cast<uint4*>(prow + chunk * 16) =
-          make_uint4(pk[4 * g], pk[4 * g + 1], pk[4 * g + 2], pk[4 * g + 3]);
+      for (int e = 0; e < 8; ++e) {
+        const int i0 = 16 * q + 2 * e;
+        float2 y = ffma2(make_float2(__uint_as_float(x[i0]), __uint_as_float(x[i0 + 1])), sc2, nm2);
+        if (!kMasked && e < kPolyPairs) {
+          y = exp2_poly2(y);
+        } else {
+          y.x = ex2(y.x);  // masked keys: exp2(-inf) = 0
+          y.y = ex2(y.y);
+        }
+        sum[e & 1] = fadd2(sum[e & 1], y);
+        pk[e] = pack_bf16(y.x, y.y);
+      }
+      // chunk c covers keys [32c, 32c+32) of this half: 16-byte chunks 4c .. 4c+3 of the swizzled row
+#pragma unroll
+      for (int g = 0; g < 2; ++g) {
+        const int chunk = (c * 4 + 2 * q + g) ^ (r & 7);
+        *reinterpret_cast<uint4*>(prow + chunk * 16) =
+            make_uint4(pk[4 * g], pk[4 * g + 1], pk[4 * g + 2], pk[4 * g + 3]);
+      }
     }
   };
   emit(a, 0);
@@ -171,6 +200,7 @@ __device__ __forceinline__ void softmax_half(uint32_t t_s, uint32_t t_o, uint8_t
 
 }  // namespace
 
+template <int kPolyPairs>
 __global__ void __launch_bounds__(kThreads, 1)
 vit_attention_kernel(const __grid_constant__ CUtensorMap map_qkv, const AttnParams p) {
   extern __shared__ uint8_t smem_raw[];
@@ -305,9 +335,9 @@ vit_attention_kernel(const __grid_constant__ CUtensorMap map_qkv, const AttnPara
       mbar_wait_sleep(s_full(w), j & 1, 32);
       tc_fence_after();
       if (valid == kTile / 2)
-        softmax_half<false>(t_s, t_o, prow, r, valid, sc, j > 0, s_free(w), o_ready(w, h), (j - 1) & 1, m_ref, l_run);
+        softmax_half<false, kPolyPairs>(t_s, t_o, prow, r, valid, sc, j > 0, s_free(w), o_ready(w, h), (j - 1) & 1, m_ref, l_run);
       else
-        softmax_half<true>(t_s, t_o, prow, r, valid, sc, j > 0, s_free(w), o_ready(w, h), (j - 1) & 1, m_ref, l_run);
+        softmax_half<true, kPolyPairs>(t_s, t_o, prow, r, valid, sc, j > 0, s_free(w), o_ready(w, h), (j - 1) & 1, m_ref, l_run);
       fence_proxy_async_smem();
       tc_fence_before();
       mbar_arrive(p_full(w, h));
@@ -351,23 +381,36 @@ vit_attention_kernel(const __grid_constant__ CUtensorMap map_qkv, const AttnPara
 
 int attn_smem_bytes() { return kSmemBytes; }
 
-cudaError_t launch_attention(const CUtensorMap& map_qkv, const AttnParams& p, cudaStream_t stream) {
+template <int kPolyPairs>
+static cudaError_t launch_variant(const CUtensorMap& map_qkv, const AttnParams& p, int grid, cudaStream_t stream) {
   static bool configured = false;
-  static int alternate = 0;
   if (!configured) {
-    cudaError_t e = cudaFuncSetAttribute(vit_attention_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                         kSmemBytes);
+    cudaError_t e = cudaFuncSetAttribute(vit_attention_kernel<kPolyPairs>,
+                                         cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes);
     if (e != cudaSuccess) return e;
-    const char* env = getenv("VC_ATTN_ALTERNATE");  // tuning knob, see DESIGN.md
-    if (env) alternate = atoi(env);
     configured = true;
   }
-  if (p.B <= 0 || p.T <= 0) return cudaSuccess;
-  AttnParams q = p;
-  q.alternate = alternate;
-  const int q_pairs = (p.T + 2 * kTile - 1) / (2 * kTile);
-  vit_attention_kernel<<<p.B * p.heads * q_pairs, kThreads, kSmemBytes, stream>>>(map_qkv, q);
+  vit_attention_kernel<kPolyPairs><<<grid, kThreads, kSmemBytes, stream>>>(map_qkv, p);
   return cudaGetLastError();
+}
+
+cudaError_t launch_attention(const CUtensorMap& map_qkv, const AttnParams& p, cudaStream_t stream) {
+  // pairs of every 8 (16 keys) whose exp2 runs on the FMA pipe; VC_ATTN_POLY overrides (tuning knob)
+  static int poly = -1;
+  if (poly < 0) {
+    const char* env = getenv("VC_ATTN_POLY");
+    poly = env ? atoi(env) : 3;
+  }
+  if (p.B <= 0 || p.T <= 0) return cudaSuccess;
+  const int q_pairs = (p.T + 2 * kTile - 1) / (2 * kTile);
+  const int grid = p.B * p.heads * q_pairs;
+  switch (poly) {
+    case 0: return launch_variant<0>(map_qkv, p, grid, stream);
+    case 1: return launch_variant<1>(map_qkv, p, grid, stream);
+    case 2: return launch_variant<2>(map_qkv, p, grid, stream);
+    case 4: return launch_variant<4>(map_qkv, p, grid, stream);
+    default: return launch_variant<3>(map_qkv, p, grid, stream);
+  }
 }
 
 }  // namespace vc
