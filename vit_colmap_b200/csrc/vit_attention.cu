@@ -399,17 +399,17 @@ cudaError_t launch_attention(const CUtensorMap& map_qkv, const AttnParams& p, cu
   static int poly = -1;
   if (poly < 0) {
     const char* env = getenv("VC_ATTN_POLY");
-    poly = env ? atoi(env) : 3;
+    poly = env ? atoi(env) : 0;
   }
   if (p.B <= 0 || p.T <= 0) return cudaSuccess;
   const int q_pairs = (p.T + 2 * kTile - 1) / (2 * kTile);
   const int grid = p.B * p.heads * q_pairs;
   switch (poly) {
-    case 0: return launch_variant<0>(map_qkv, p, grid, stream);
     case 1: return launch_variant<1>(map_qkv, p, grid, stream);
     case 2: return launch_variant<2>(map_qkv, p, grid, stream);
     case 4: return launch_variant<4>(map_qkv, p, grid, stream);
-    default: return launch_variant<3>(map_qkv, p, grid, stream);
+    case 3: return launch_variant<3>(map_qkv, p, grid, stream);
+    default: return launch_variant<0>(map_qkv, p, grid, stream);
   }
 }
 
