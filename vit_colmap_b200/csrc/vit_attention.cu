@@ -353,23 +353,38 @@ vit_attention_kernel(const __grid_constant__ CUtensorMap map_qkv, const AttnPara
     mbar_wait_sleep(o_full(w), 0, 32);
     tc_fence_after();
     // this thread finishes output columns [32h, 32h+32) of its row from both partial accumulators
-    const int t = q0 + w * kTile + r;
     uint32_t o0[32], o1[32];
     tmem_ld_32x32(lane_base + 256 + (2 * w) * 64 + h * 32, o0);
     tmem_ld_32x32(lane_base + 256 + (2 * w + 1) * 64 + h * 32, o1);
     tmem_wait_ld();
-    if (t < p.T) {
-      uint4* dst = reinterpret_cast<uint4*>(p.out + ((size_t)img * p.T + t) * C + head * kHd + h * 32);
+    // The 32 rows x 64 columns of a lane quarter (both halves) meet in a swizzled shared-memory tile
+    // -- a slice of this warpgroup's P buffer, free now that every P V has completed -- and leave as
+    // whole 128-byte lines (8 lanes per row): a row-per-thread store touches 32 lines per instruction
+    uint8_t* stg = sP_gen + w * kPBytes + quarter * 4096;
 #pragma unroll
-      for (int g = 0; g < 4; ++g) {
-        uint32_t pk[4];
+    for (int g = 0; g < 4; ++g) {
+      uint32_t pk[4];
 #pragma unroll
-        for (int e = 0; e < 4; ++e) {
-          const int i0 = 8 * g + 2 * e;
-          pk[e] = pack_bf16(fmaf(__uint_as_float(o0[i0]), c0, __uint_as_float(o1[i0]) * c1),
-                            fmaf(__uint_as_float(o0[i0 + 1]), c0, __uint_as_float(o1[i0 + 1]) * c1));
+      for (int e = 0; e < 4; ++e) {
+        const int i0 = 8 * g + 2 * e;
+        pk[e] = pack_bf16(fmaf(__uint_as_float(o0[i0]), c0, __uint_as_float(o1[i0]) * c1),
+                          fmaf(__uint_as_float(o0[i0 + 1]), c0, __uint_as_float(o1[i0 + 1]) * c1));
+      }
+      *reinterpret_cast<uint4*>(stg + lane * 128 + (((h * 4 + g) ^ (lane & 7)) << 4)) =
+          make_uint4(pk[0], pk[1], pk[2], pk[3]);
+    }
+    asm volatile("bar.sync %0, 256;" ::"r"(1 + w) : "memory");
+    {
+      const int tc = lane & 7;
+      __nv_bfloat16* dst = p.out + (size_t)img * p.T * C + head * kHd + tc * 8;
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        const int rr = 16 * h + (lane >> 3) + 4 * i;   // this warp stores rows [16h, 16h+16) of the quarter
+        const int tt = q0 + w * kTile + quarter * 32 + rr;
+        if (tt < p.T) {
+          const uint4 v = *reinterpret_cast<const uint4*>(stg + rr * 128 + ((tc ^ (rr & 7)) << 4));
+          *reinterpret_cast<uint4*>(dst + (size_t)tt * C) = v;
         }
-        dst[g] = make_uint4(pk[0], pk[1], pk[2], pk[3]);
       }
     }
   }
