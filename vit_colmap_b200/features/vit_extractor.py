@@ -106,11 +106,45 @@ class ViTExtractor(BaseExtractor):
         self.descriptor_projection = proj.to(self.device)
 
     # ------------------------------------------------------------------ batched core
+    def _upload(self, images_bgr: List[np.ndarray]):
+        """Host images -> one device batch [B, H, W, 3] uint8.  Each image is copied once into a
+        persistent pinned staging buffer and its host->device copy is enqueued immediately, so the
+        staging memcpy of image k+1 overlaps the DMA of image k."""
+        import torch
+        B = len(images_bgr)
+        shape = (B,) + tuple(images_bgr[0].shape)
+        n = int(np.prod(shape))
+        if getattr(self, "_pinned", None) is None or self._pinned.numel() < n:
+            self._pinned = torch.empty(n, dtype=torch.uint8).pin_memory()
+        stage = self._pinned[:n].view(shape)
+        dev = torch.empty(shape, dtype=torch.uint8, device=self.device)
+        stage_np = stage.numpy()
+        for i, img in enumerate(images_bgr):
+            np.copyto(stage_np[i], img)
+            dev[i].copy_(stage[i], non_blocking=True)
+        return dev
+
+    def _download(self, kps, du8, nmax: int):
+        """Only the populated rows ([:, :nmax]) come back, through persistent pinned buffers."""
+        import torch
+        outs = []
+        for name, t in (("_pin_kps", kps), ("_pin_desc", du8)):
+            t = t[:, :nmax].contiguous()
+            buf = getattr(self, name, None)
+            if buf is None or buf.numel() < t.numel() or buf.dtype != t.dtype:
+                buf = torch.empty(max(t.numel(), 1), dtype=t.dtype).pin_memory()
+                setattr(self, name, buf)
+            host = buf[: t.numel()].view(t.shape)
+            host.copy_(t, non_blocking=True)
+            outs.append(host)
+        torch.cuda.current_stream(self.device).synchronize()
+        return outs[0].numpy(), outs[1].numpy()
+
     def _extract_batch(self, images_bgr: List[np.ndarray], orig_wh, resized_wh):
         """images: equally sized BGR uint8 arrays (already multiples of 14).  Returns per-image
         (keypoints f32 [n,2], descriptors u8 [n,d]) plus the device-resident SparseFeatures."""
         import torch
-        batch = torch.from_numpy(np.stack(images_bgr)).pin_memory().to(self.device, non_blocking=True)
+        batch = self._upload(images_bgr)
         gh, gw = batch.shape[1] // PATCH, batch.shape[2] // PATCH
         self._grid = (gh, gw)
         tokens = self.model.forward_patch_tokens(batch, bgr=True)
@@ -122,7 +156,7 @@ class ViTExtractor(BaseExtractor):
         proj = self.descriptor_projection if C > self.descriptor_dim else None
         kps, dbf, du8, _ = self.post.sample_pack(tokens, (gh, gw), coords, counts, orig_wh, resized_wh, projection=proj)
         n = counts.cpu().numpy()
-        kps_h, du8_h = kps.cpu().numpy(), du8.cpu().numpy()
+        kps_h, du8_h = self._download(kps, du8, int(n.max()) if len(n) else 0)
         out = [(kps_h[i, : n[i]].copy(), du8_h[i, : n[i]].copy()) for i in range(len(images_bgr))]
         return out, (counts, dbf)
 
