@@ -41,7 +41,18 @@ typedef struct {
   /* score scale applied before acos: 1/512^2 for uint8 COLMAP descriptors
    * (COLMAP/feature/sift.cc:63,739), 1.0 for unit-norm float descriptors. */
   float inv_norm;
+  /* Acceptance rule applied to each row's / column's (best, second) scores:
+   *   VC_RULE_ANGULAR (0): theta = acos(min(score * inv_norm, 1)); reject theta1 > max_distance or
+   *     theta1 >= max_ratio * theta2 -- FindBestMatchesOneWayBruteForce, COLMAP/feature/sift.cc:733-787
+   *     (the GPU / brute-force path).
+   *   VC_RULE_L2 (1): scores are l2_offset - squared L2 distance (the caller augments the descriptors
+   *     so that the dot product is exactly that, see vit_colmap_b200/matching.py); reject
+   *     d1^2 > max_distance^2 / inv_norm or sqrt(d1^2) >= max_ratio * sqrt(d2^2) --
+   *     FindBestMatchesOneWayIndex, COLMAP/feature/sift.cc:827-874 (the CPU index path, done exactly). */
+  int32_t rule;
+  float l2_offset;
 } vc_match_options;
+enum { VC_RULE_ANGULAR = 0, VC_RULE_L2 = 1 };
 
 const char* vc_last_error(void);
 const char* vc_version(void);

@@ -180,6 +180,41 @@ def match_python(desc1, desc2, max_ratio=0.8, max_distance=0.7, cross_check=True
     return np.asarray(out, dtype=np.uint32).reshape(-1, 2)
 
 
+def match_l2_numpy(desc1, desc2, max_ratio=0.8, max_distance=0.7, cross_check=True):
+    """FindBestMatchesIndex / FindBestMatchesOneWayIndex (COLMAP/feature/sift.cc:827-915) with the
+    index replaced by an exact search: uint8 descriptors, squared L2 distances (exact in int64),
+    first minimum wins (strict '<'), best > 512^2 * max_distance^2 rejected, sqrt(best) >=
+    max_ratio * sqrt(second) rejected, second = FLT_MAX when there is only one candidate."""
+    a = np.asarray(desc1).astype(np.int64)
+    b = np.asarray(desc2).astype(np.int64)
+    if a.shape[0] == 0 or b.shape[0] == 0:
+        return np.zeros((0, 2), np.uint32)
+    d2 = (a * a).sum(1)[:, None] + (b * b).sum(1)[None, :] - 2 * (a @ b.T)
+    max_l2 = np.float32(SQ_SIFT_NORM) * np.float32(max_distance) * np.float32(max_distance)
+
+    def one_way(mat):
+        out = np.full(mat.shape[0], -1, np.int64)
+        for i in range(mat.shape[0]):
+            row = mat[i]
+            j = int(np.argmin(row))  # first minimum
+            best = np.float32(row[j])
+            second = np.float32(np.partition(row, 1)[1]) if row.shape[0] > 1 else np.float32(np.finfo(np.float32).max)
+            if best > max_l2:
+                continue
+            if np.sqrt(best) >= np.float32(max_ratio) * np.sqrt(second):
+                continue
+            out[i] = j
+        return out
+
+    m12 = one_way(d2)
+    if cross_check:
+        m21 = one_way(d2.T)
+        keep = [(i, j) for i, j in enumerate(m12) if j >= 0 and m21[j] == i]
+    else:
+        keep = [(i, j) for i, j in enumerate(m12) if j >= 0]
+    return np.array(keep, dtype=np.uint32).reshape(-1, 2)
+
+
 def exhaustive_pairs(image_ids, block_size: int = 50):
     """ExhaustivePairGenerator (pairing.cc:171-236).  Returns (pairs [n,2] uint32,
     per-Next() block sizes)."""

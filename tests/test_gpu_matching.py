@@ -174,3 +174,29 @@ def test_full_size_8192_d768_against_oracle_and_properties(matcher):
     keep = fwd[fwd[:, 1] != 8191]
     got3 = m[4, : n[4]]
     assert abs(int(n[4]) - len(keep)) <= 2 and len(set(map(tuple, got3.tolist())) ^ set(map(tuple, keep.tolist()))) <= 4
+
+
+def test_l2_rule_matches_oracle(matcher):
+    """rule 'l2' (COLMAP's CPU index semantics, sift.cc:827-915, exact search) through the fused GEMM
+    with role-augmented descriptors: bit-exact match lists against the int64 oracle on SIFT-like and
+    on uniform-random (dummy extractor) uint8 descriptors, ragged counts, both cross-check settings."""
+    from oracle import matching as om
+    rng = np.random.default_rng(21)
+    kmax, d = 400, 128
+    counts = [400, 333, 1, 0]
+    f = np.abs(_make_set(rng, 4, kmax, d, counts))
+    sift = np.zeros((4, kmax, d), np.uint8)
+    for i, n in enumerate(counts):
+        sift[i, :n] = om.to_uint8_colmap(om.l2_normalize(f[i, :n])) if n else 0
+    dummy = rng.integers(0, 256, (4, kmax, d), dtype=np.uint8)
+    dummy[1, :150] = dummy[0, 100:250]           # shared cells
+    dummy[1, 200] = dummy[1, 201]                # exact duplicate: best == second -> rejected
+    pairs = [(0, 1), (1, 0), (0, 2), (2, 1), (0, 3)]
+    for desc, (ratio, dist) in ((sift, (0.8, 0.7)), (dummy, (0.8, 0.7)), (dummy, (0.95, 3.5))):
+        for cross in (True, False):
+            got = matcher.match_pairs_host(desc, np.array(counts, np.int32), np.array(pairs, np.int32), ratio, dist,
+                                           cross, rule="l2")
+            for k, (i1, i2) in enumerate(pairs):
+                ref = om.match_l2_numpy(desc[i1, : counts[i1]], desc[i2, : counts[i2]], ratio, dist, cross)
+                assert got[k].tolist() == ref.tolist(), (k, cross, len(got[k]), len(ref))
+    assert len(matcher.match_pairs_host(dummy, np.array(counts, np.int32), np.array([[0, 1]], np.int32), rule="l2")[0]) >= 140

@@ -30,6 +30,11 @@ def test_smoke_e2e_dummy_extractor(tmp_path):
         assert ColmapDatabase.get_db_count(db, "num_matched_image_pairs") >= 1
         for image_id in (1, 2, 3):
             assert db.exists_keypoints(image_id) and db.exists_descriptors(image_id)
+    # the fake backend is matched under COLMAP's L2 (index) rule: identical grid cells pair up one-to-one
+    con = sqlite3.connect(str(db_path))
+    rows = [r for (r,) in con.execute("SELECT rows FROM matches")]
+    n_kp = con.execute("SELECT rows FROM keypoints WHERE image_id=1").fetchone()[0]
+    assert len(rows) == 3 and all(r == n_kp for r in rows)
 
 
 @pytest.fixture(scope="module")

@@ -121,3 +121,27 @@ def test_dummy_descriptors_saturate_angular_rule():
     rng = np.random.RandomState(42)
     d = rng.randint(0, 256, (40, 128)).astype(np.uint8)
     assert len(_all_impls(d, d.copy())) == 0
+
+
+def test_l2_rule_known_answers():
+    """CPU index rule (sift.cc:827-915) done exactly.  KA2-style: 50 ten-hot rows vs reversed -> 50
+    matches under both rules; KA8: DummyExtractor descriptors (uniform uint8, norm ~1670 > 512)
+    match identical grid cells one-to-one under l2 and not at all under the angular rule."""
+    d1 = om.ten_hot_descriptors(50, np.random.default_rng(1))
+    m = om.match_l2_numpy(d1, d1[::-1].copy(), 0.8, 0.7, True)
+    assert len(m) == 50 and all(j == 49 - i for i, j in m.tolist())
+    cells = [np.random.RandomState(42 + 1000 * gx + gy).randint(0, 256, 128, dtype=np.uint8)
+             for gy in range(15) for gx in range(20)]  # dummy_extractor.py:100-109
+    a = np.stack(cells)
+    perm = np.random.default_rng(2).permutation(300)
+    b = a[perm]
+    m = om.match_l2_numpy(a, b, 0.8, 0.7, True)
+    assert len(m) == 300 and np.array_equal(perm[m[:, 1]], m[:, 0])
+    assert len(om.match_numpy(a, b, 0.8, 0.7, True)) == 0
+    # distance threshold: a near-duplicate farther than 512*max_distance is rejected
+    c = a[:1].copy().astype(np.int64)
+    c[0, :64] = np.clip(c[0, :64] + 60, 0, 255)
+    assert len(om.match_l2_numpy(a[:1], c.astype(np.uint8), 0.8, 0.7, False)) == 0  # |diff| ~ 480 > 358
+    assert len(om.match_l2_numpy(a[:1], c.astype(np.uint8), 0.8, 1.0, False)) == 1
+    # empty sides
+    assert om.match_l2_numpy(a[:0], b).shape == (0, 2)

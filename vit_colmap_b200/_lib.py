@@ -21,7 +21,7 @@ class VcError(RuntimeError):
 class MatchOptions(ctypes.Structure):
     """vc_match_options (include/vc_b200.h)."""
     _fields_ = [("max_ratio", c_float), ("max_distance", c_float), ("cross_check", c_int32),
-                ("inv_norm", c_float)]
+                ("inv_norm", c_float), ("rule", c_int32), ("l2_offset", c_float)]
 
 
 # name -> (restype, argtypes); kept in one table so tests can check every exported symbol

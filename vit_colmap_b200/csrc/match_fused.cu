@@ -53,16 +53,6 @@ __device__ __forceinline__ FItem decode_fitem(const MatchParams& p, int item) {
   return it;
 }
 
-__device__ __forceinline__ int accept_top2f(float best, float second, int idx, float inv_norm,
-                                            float max_ratio, float max_distance) {
-  if (idx < 0) return -1;
-  const float t1 = (float)acos((double)fminf(inv_norm * best, 1.0f));
-  if (t1 > max_distance) return -1;
-  const float t2 = (float)acos((double)fminf(inv_norm * second, 1.0f));
-  if (t1 >= max_ratio * t2) return -1;
-  return idx;
-}
-
 __device__ __forceinline__ void epi_bar_sync() { asm volatile("bar.sync 1, 256;" ::: "memory"); }
 
 }  // namespace
@@ -293,7 +283,7 @@ match_fused_kernel(const __grid_constant__ CUtensorMap tmap, const MatchParams p
         const float csec = __uint_as_float(colsec[et]);
         const int cidx = key ? (int)(0xFFFFFFFFu - (unsigned)(key & 0xFFFFFFFFull)) : -1;
         const size_t o = ((size_t)it.pair * 2 + 1) * p.kmax + it.cb * BN + et;
-        p.m_out[o] = accept_top2f(cbest, csec, cidx, p.inv_norm, p.max_ratio, p.max_distance);
+        p.m_out[o] = accept_scores(cbest, csec, cidx, p);
         if (p.top_best != nullptr) {
           p.top_best[o] = cbest;
           p.top_second[o] = csec;
@@ -334,7 +324,7 @@ __global__ void merge_rows_kernel(const MatchParams p) {
     }
   }
   const size_t o = ((size_t)pair * 2) * p.kmax + row;
-  p.m_out[o] = accept_top2f(best, second, idx, p.inv_norm, p.max_ratio, p.max_distance);
+  p.m_out[o] = accept_scores(best, second, idx, p);
   if (p.top_best != nullptr) {
     p.top_best[o] = best;
     p.top_second[o] = second;

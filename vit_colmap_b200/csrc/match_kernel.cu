@@ -55,18 +55,6 @@ __device__ __forceinline__ Item decode_item(const MatchParams& p, int item) {
   return it;
 }
 
-// COLMAP/feature/sift.cc:759-783.  acos is evaluated in double and rounded once so the float
-// result agrees with a correctly rounded host acosf.
-__device__ __forceinline__ int accept_top2(float best, float second, int idx, float inv_norm,
-                                           float max_ratio, float max_distance) {
-  if (idx < 0) return -1;
-  const float t1 = (float)acos((double)fminf(inv_norm * best, 1.0f));
-  if (t1 > max_distance) return -1;
-  const float t2 = (float)acos((double)fminf(inv_norm * second, 1.0f));
-  if (t1 >= max_ratio * t2) return -1;
-  return idx;
-}
-
 }  // namespace
 
 template <bool kDebug>
@@ -230,7 +218,7 @@ match_top2_kernel(const __grid_constant__ CUtensorMap tmap, const MatchParams p)
       }
       if (row < it.n_m) {
         const size_t o = ((size_t)it.pair * 2 + it.dir) * p.kmax + row;
-        p.m_out[o] = accept_top2(best, second, bidx, p.inv_norm, p.max_ratio, p.max_distance);
+        p.m_out[o] = accept_scores(best, second, bidx, p);
         if (p.top_best != nullptr) {
           p.top_best[o] = best;
           p.top_second[o] = second;

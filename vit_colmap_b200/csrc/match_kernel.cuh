@@ -17,6 +17,8 @@ struct MatchParams {
   int rb_per_img;         // ceil(kmax / 128)
   int n_items;            // n_pairs * 2 * rb_per_img
   float inv_norm, max_ratio, max_distance;
+  int rule;               // 0 angular (sift.cc:733-787), 1 squared-L2 (sift.cc:827-874)
+  float l2_offset;        // rule 1: score = l2_offset - squared distance
   int cross_check;
   int32_t* m_out;         // [n_pairs, 2, kmax] accepted best index or -1
   float* top_best;        // optional diagnostics [n_pairs, 2, kmax]
@@ -31,6 +33,25 @@ struct MatchParams {
   float* part_second;
   int32_t* part_idx;
 };
+
+// Acceptance tests on a row's (best, second) scores.  acos is evaluated in double and rounded once so
+// the float result agrees with a correctly rounded host acosf.
+__device__ __forceinline__ int accept_scores(float best, float second, int idx, const MatchParams& p) {
+  if (idx < 0) return -1;
+  if (p.rule == 1) {
+    // COLMAP/feature/sift.cc:832,859-871: squared-L2 threshold, ratio test on the distances
+    const float d1 = p.l2_offset - best, d2 = p.l2_offset - second;
+    if (d1 > p.max_distance * p.max_distance / p.inv_norm) return -1;
+    if (sqrtf(fmaxf(d1, 0.f)) >= p.max_ratio * sqrtf(fmaxf(d2, 0.f))) return -1;
+    return idx;
+  }
+  // COLMAP/feature/sift.cc:759-783
+  const float t1 = (float)acos((double)fminf(p.inv_norm * best, 1.0f));
+  if (t1 > p.max_distance) return -1;
+  const float t2 = (float)acos((double)fminf(p.inv_norm * second, 1.0f));
+  if (t1 >= p.max_ratio * t2) return -1;
+  return idx;
+}
 
 int match_smem_bytes();
 cudaError_t launch_match_top2(const CUtensorMap& tmap, const MatchParams& p, int num_sms, bool debug,

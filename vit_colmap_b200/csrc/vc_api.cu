@@ -108,6 +108,8 @@ vc::MatchParams make_params(const int32_t* counts, const int32_t* pairs, int n_p
   p.inv_norm = opt->inv_norm;
   p.max_ratio = opt->max_ratio;
   p.max_distance = opt->max_distance;
+  p.rule = opt->rule;
+  p.l2_offset = opt->l2_offset;
   p.cross_check = opt->cross_check;
   p.m_out = m_out;
   return p;

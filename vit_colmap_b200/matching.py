@@ -42,6 +42,10 @@ class FeatureMatchingOptions:
     cross_check: bool = True
     # COLMAP/controllers/feature_matching_utils.cc:485-488 blanks pairs with fewer matches
     min_num_matches: int = 15
+    # "angular": COLMAP's GPU / brute-force rule (sift.cc:733-787); "l2": its CPU index rule done
+    # exactly (sift.cc:827-874) -- what the PyPI pycolmap (no CUDA) applies, and the only one under
+    # which uniform-random uint8 descriptors (the `dummy` extractor) produce matches
+    rule: str = "angular"
 
 
 def _ptr(t) -> int:
@@ -89,9 +93,9 @@ class Matcher:
         return self._ws, need
 
     @staticmethod
-    def _opts(max_ratio, max_distance, cross_check, inv_norm) -> _lib.MatchOptions:
+    def _opts(max_ratio, max_distance, cross_check, inv_norm, rule: int = 0, l2_offset: float = 0.0) -> _lib.MatchOptions:
         return _lib.MatchOptions(float(max_ratio), float(max_distance), int(bool(cross_check)),
-                                 float(inv_norm))
+                                 float(inv_norm), int(rule), float(l2_offset))
 
     def to_bf16(self, desc):
         """uint8 / float32 device tensor -> bf16 device tensor via the library's converters."""
@@ -155,13 +159,20 @@ class Matcher:
 
     # ------------------------------------------------------------------ host-buffer path
     def match_pairs_host(self, desc: np.ndarray, counts: np.ndarray, pairs: np.ndarray, max_ratio=0.8,
-                         max_distance=0.7, cross_check=True, inv_norm: Optional[float] = None):
-        """desc: host uint8 or float32 [n_images,kmax,d].  Returns a list of [n,2] uint32 arrays."""
+                         max_distance=0.7, cross_check=True, inv_norm: Optional[float] = None,
+                         rule: str = "angular"):
+        """desc: host uint8 or float32 [n_images,kmax,d].  Returns a list of [n,2] uint32 arrays.
+        rule "angular": COLMAP's brute-force / GPU semantics (sift.cc:733-787); rule "l2": the exact
+        form of its CPU index path (sift.cc:827-874), uint8 descriptors only."""
         desc = np.ascontiguousarray(desc)
         counts = np.ascontiguousarray(counts, dtype=np.int32)
         pairs = np.ascontiguousarray(pairs, dtype=np.int32).reshape(-1, 2)
         n_images, kmax, d = desc.shape
         n_pairs = pairs.shape[0]
+        if rule == "l2":
+            return self._match_pairs_host_l2(desc, counts, pairs, max_ratio, max_distance, cross_check)
+        if rule != "angular":
+            raise ValueError(f"unknown matching rule {rule!r} (angular | l2)")
         if desc.dtype == np.uint8:
             dtype = _lib.DTYPE_U8
             inv = 1.0 / SQ_SIFT_NORM if inv_norm is None else inv_norm
@@ -182,6 +193,49 @@ class Matcher:
         return [matches[i, :n_matches[i]].copy() for i in range(n_pairs)]
 
 
+    def _match_pairs_host_l2(self, desc, counts, pairs, max_ratio, max_distance, cross_check):
+        """Squared-L2 nearest neighbours through the SAME fused GEMM kernel: the descriptors are
+        augmented so that the dot product of an image-1 row with an image-2 row is exactly
+        K - |x - y|^2.  The two roles need different augmentations (K - d^2 is not a Gram matrix), so
+        the image axis is doubled: copies [0, n) play image 1, copies [n, 2n) image 2.
+            image 1: [2x, D0, D1, D2, 1, 1, 1, 1]             (|x|^2 = D0 + 256 D1 + 65536 D2)
+            image 2: [ y, -1, -256, -65536, -E0, -256 E1, -65536 E2, K]   (|y|^2 = E0 + 256 E1 + 65536 E2)
+        Every entry is an integer bf16 represents exactly and every partial sum stays below 2^24
+        (K = power of two > 2 max|x|^2 >= max d^2, required <= 2^23), so fp32 accumulation is exact
+        and ties resolve as in COLMAP (first minimum wins)."""
+        if desc.dtype != np.uint8:
+            raise TypeError("rule 'l2' is defined for uint8 descriptors (COLMAP FeatureDescriptors)")
+        n_images, kmax, d = desc.shape
+        x = desc.astype(np.int64)
+        norm2 = (x * x).sum(axis=2)
+        mask = np.arange(kmax)[None, :] < counts[:, None]
+        max_norm2 = int((norm2 * mask).max()) if mask.any() else 0
+        K = 1 << max(int(2 * max_norm2 + 1).bit_length(), 1)
+        if K > (1 << 23):
+            raise ValueError("descriptor norms too large for the exact l2 rule (need 2*max|x|^2 < 2^23)")
+        dig = np.stack([norm2 & 255, (norm2 >> 8) & 255, norm2 >> 16], axis=2).astype(np.float32)
+        aug = np.zeros((2 * n_images, kmax, d + 8), dtype=np.float32)
+        aug[:n_images, :, :d] = 2.0 * desc
+        aug[:n_images, :, d:d + 3] = dig
+        aug[:n_images, :, d + 3:d + 7] = 1.0
+        aug[n_images:, :, :d] = desc
+        aug[n_images:, :, d:d + 3] = np.array([-1.0, -256.0, -65536.0], np.float32)
+        aug[n_images:, :, d + 3:d + 6] = -dig * np.array([1.0, 256.0, 65536.0], np.float32)
+        aug[n_images:, :, d + 6] = float(K)
+        import torch
+        bits = torch.from_numpy(aug).to(torch.bfloat16).view(torch.int16).numpy().view(np.uint16)
+        assert np.array_equal(torch.from_numpy(bits.view(np.int16)).view(torch.bfloat16).float().numpy(), aug)
+        counts2 = np.concatenate([counts, counts]).astype(np.int32)
+        pairs2 = np.stack([pairs[:, 0], pairs[:, 1] + n_images], axis=1).astype(np.int32)
+        n_pairs = pairs2.shape[0]
+        matches = np.empty((max(n_pairs, 1), kmax, 2), dtype=np.uint32)
+        n_matches = np.zeros((max(n_pairs, 1),), dtype=np.int32)
+        opt = self._opts(max_ratio, max_distance, cross_check, 1.0 / SQ_SIFT_NORM, 1, float(K))
+        _lib.check(self.lib.vc_match_pairs_host(self.handle, bits.ctypes.data, _lib.DTYPE_BF16, counts2.ctypes.data,
+                                                2 * n_images, kmax, d + 8, pairs2.ctypes.data, n_pairs,
+                                                ctypes.byref(opt), matches.ctypes.data, n_matches.ctypes.data))
+        return [matches[i, :n_matches[i]].copy() for i in range(n_pairs)]
+
 def match_descriptor_sets(descriptors: Sequence[np.ndarray], pairs, options: Optional[FeatureMatchingOptions] = None,
                           matcher: Optional[Matcher] = None, device: int = 0):
     """Match host descriptor arrays (ragged list of [n_i, d] uint8 or float32) for the given index
@@ -200,8 +254,11 @@ def match_descriptor_sets(descriptors: Sequence[np.ndarray], pairs, options: Opt
         counts[i] = n
         if n:
             buf[i, :n] = x[:n]
+    rule = getattr(options, "rule", "angular")
+    if rule == "l2" and dtype != np.uint8:
+        raise TypeError("rule 'l2' is defined for uint8 descriptors")
     return matcher.match_pairs_host(buf, counts, np.asarray(pairs, dtype=np.int32),
-                                    options.max_ratio, options.max_distance, options.cross_check)
+                                    options.max_ratio, options.max_distance, options.cross_check, rule=rule)
 
 
 def match_exhaustive(database_path, matching_options: Optional[FeatureMatchingOptions] = None,

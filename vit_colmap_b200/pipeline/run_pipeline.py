@@ -84,7 +84,13 @@ class Pipeline:
         if self.config.do_matching:
             logger.info("Running feature matching...")
             from ..matching import match_exhaustive
-            match_exhaustive(database_path=str(db_path), matching_options=self.config.matching.to_matching_options())
+            opts = self.config.matching.to_matching_options()
+            if self.config.extractor.extractor_type == "dummy":
+                # uniform-random uint8 descriptors have norm >> 512, which saturates COLMAP's angular
+                # rule (theta = 0 everywhere, nothing matches); its CPU index rule works in L2 space
+                # and matches identical grid cells one-to-one
+                opts.rule = "l2"
+            match_exhaustive(database_path=str(db_path), matching_options=opts)
             if pycolmap is not None and hasattr(pycolmap, "verify_matches"):  # geometric verification: untouched
                 self._verify_with_pycolmap(db_path, output_dir)
             with ColmapDatabase.open_database(str(db_path)) as db_check:
