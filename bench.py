@@ -339,7 +339,8 @@ def run_ours(args):
 
 
 # ------------------------------------------------------------------------------------ extraction
-EXTRACT_MODEL, EXTRACT_SIZE, EXTRACT_BATCH = "dinov2_vitb14", 518, 32
+EXTRACT_MODEL, EXTRACT_SIZE = "dinov2_vitb14", 518
+EXTRACT_BATCH = int(os.environ.get("VC_BENCH_EXTRACT_BATCH", "32"))
 EXTRACT_KPTS, EXTRACT_DIM = 2048, 128  # reference defaults, vit_extractor.py:25-33
 
 

@@ -35,7 +35,6 @@ struct AttnParams {
   int B, T, heads;        // head_dim is 64
   float scale;            // 1/sqrt(64)
   __nv_bfloat16* out;     // [B*T, heads*64]
-  int alternate;          // tuning knob: softmax warpgroups take turns instead of running together
 };
 int attn_smem_bytes();
 // map_qkv: 3-D map over qkv bf16 [B, T, 3*heads*64] with box {64, 128, 1}
