@@ -158,6 +158,9 @@ typedef enum {
   VC_QUANT_COLMAP = 1,    /* min(255, round(512 v)), COLMAP/feature/utils.cc:56-71 */
   VC_QUANT_TRAINABLE = 2  /* trunc(clip((v + 1) * 127.5, 0, 255)), trainable_vit_extractor.py:265-267 */
 } vc_quant_mode;
+/* OR-ed into quant_mode: RootSIFT normalisation (L1-normalise, sqrt(clamp(., 1e-8)), then the usual
+ * L2 step) of the hybrid extractor, vit_colmap/features/hybrid_extractor.py:286-288. */
+#define VC_NORM_ROOTSIFT 0x10
 
 /* Sample, (project,) L2-normalise and pack descriptors at the selected keypoints.
  *   coords      : [n_images, capacity, 2] (y, x); int32 grid cells, or float32 grid units when

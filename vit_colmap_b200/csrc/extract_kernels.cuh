@@ -52,6 +52,7 @@ struct SampleParams {
   const float* proj_bias;   // [d] added after the projection, or nullptr
   int d;
   int quant_mode;      // 0: trunc(clip(512 v, 0, 255)) (vit); 1: round, COLMAP; 2: (v+1)*127.5
+  int rootsift;        // 1: L1-normalise + sqrt(clamp 1e-8) before the L2 step (hybrid_extractor.py:286-288)
   float norm_eps;      // F.normalize eps: 1e-12 (vit_extractor.py:243), 1e-8 (vit_feature_model.py:226)
   float sx1, sx2, sy1, sy2;  // keypoint scale factors: x = (col + .5) * sx1 * sx2
   float* keypoints;    // out [B, cap, 2] (x, y) or nullptr

@@ -99,6 +99,12 @@ __device__ __forceinline__ uint8_t quantise(float v, int mode) {
   return (uint8_t)(int)q;
 }
 
+// RootSIFT pre-step of hybrid_extractor.py:286-287: F.normalize(p=1) (eps 1e-12) then
+// sqrt(clamp(min=1e-8)); the L2 step that follows is the common one.
+__device__ __forceinline__ float rootsift(float v, float l1_den) {
+  return sqrtf(fmaxf(__fdiv_rn(v, l1_den), 1e-8f));
+}
+
 __device__ __forceinline__ void write_keypoint(const SampleParams& p, size_t kp, float fy, float fx) {
   if (p.keypoints == nullptr) return;
   float2 o;
@@ -156,6 +162,22 @@ __global__ void __launch_bounds__(256) sample_pack_direct(const SampleParams p) 
         acc[j].y = __fadd_rn(acc[j].y, __fmul_rn(x.y, w));
         acc[j].z = __fadd_rn(acc[j].z, __fmul_rn(x.z, w));
         acc[j].w = __fadd_rn(acc[j].w, __fmul_rn(x.w, w));
+      }
+    }
+  }
+  if (p.rootsift) {
+    float l1 = 0.f;
+#pragma unroll
+    for (int j = 0; j < kVec; ++j)
+      if (lane + 32 * j < nvec) l1 += fabsf(acc[j].x) + fabsf(acc[j].y) + fabsf(acc[j].z) + fabsf(acc[j].w);
+    const float den1 = fmaxf(warp_sum(l1), 1e-12f);
+#pragma unroll
+    for (int j = 0; j < kVec; ++j) {
+      if (lane + 32 * j < nvec) {
+        acc[j].x = rootsift(acc[j].x, den1);
+        acc[j].y = rootsift(acc[j].y, den1);
+        acc[j].z = rootsift(acc[j].z, den1);
+        acc[j].w = rootsift(acc[j].w, den1);
       }
     }
   }
@@ -261,7 +283,23 @@ __global__ void __launch_bounds__(256) sample_pack_project(const SampleParams p,
   // phase 3: normalise + pack (each warp finishes 2 keypoints)
   const int dvec = p.d >> 2;
   for (int kk = warp; kk < nk; kk += 8) {
-    const float* row = outp + (size_t)kk * p.d;
+    float* row = outp + (size_t)kk * p.d;
+    if (p.rootsift) {  // each lane rewrites only the elements it reads back below
+      float l1 = 0.f;
+      for (int v = lane; v < dvec; v += 32) {
+        const float4 x = *reinterpret_cast<const float4*>(row + 4 * v);
+        l1 += fabsf(x.x) + fabsf(x.y) + fabsf(x.z) + fabsf(x.w);
+      }
+      const float den1 = fmaxf(warp_sum(l1), 1e-12f);
+      for (int v = lane; v < dvec; v += 32) {
+        float4 x = *reinterpret_cast<const float4*>(row + 4 * v);
+        x.x = rootsift(x.x, den1);
+        x.y = rootsift(x.y, den1);
+        x.z = rootsift(x.z, den1);
+        x.w = rootsift(x.w, den1);
+        *reinterpret_cast<float4*>(row + 4 * v) = x;
+      }
+    }
     float ss = 0.f;
     for (int v = lane; v < dvec; v += 32) {
       const float4 x = *reinterpret_cast<const float4*>(row + 4 * v);

@@ -129,6 +129,8 @@ int vc_sample_pack(vc_handle* h, const void* tokens, int dtype, int n_images, in
   if (projection == nullptr && d != channels)
     return fail(VC_ERR_INVALID, "d=%d must equal C=%d when no projection is given", d, channels);
   if (d <= 0 || d % 4 != 0 || d > vc::kMaxChannels) return fail(VC_ERR_INVALID, "bad d=%d", d);
+  const int rootsift = (quant_mode & VC_NORM_ROOTSIFT) != 0;
+  quant_mode &= ~VC_NORM_ROOTSIFT;
   if (quant_mode < 0 || quant_mode > 2) return fail(VC_ERR_INVALID, "bad quant_mode");
   if (keypoints && !kp_scale) return fail(VC_ERR_INVALID, "keypoints requested without kp_scale");
   const int el = dtype == VC_DTYPE_F32 ? 4 : 2;
@@ -153,6 +155,7 @@ int vc_sample_pack(vc_handle* h, const void* tokens, int dtype, int n_images, in
   p.proj_bias = projection ? projection_bias : nullptr;
   p.d = d;
   p.quant_mode = quant_mode;
+  p.rootsift = rootsift;
   p.norm_eps = quant_mode == VC_QUANT_TRAINABLE ? 1e-8f : 1e-12f;
   if (kp_scale) {
     p.sx1 = kp_scale[0];
