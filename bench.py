@@ -396,17 +396,21 @@ def run_extract(args, torch, dist, dev, local, world):
     ms = timed(step, args.steps)
     ms_fwd = timed(forward_only, max(2, min(args.steps, 5))) / max(2, min(args.steps, 5))
     # end to end: host uint8 images in, host keypoints + descriptors out (public extractor API)
-    ex._extract_batch(host, wh, wh)
+    list(ex.extract_batches([(host, wh, wh, None)] * 4))  # warm-up: allocator pools for two batches in flight
     torch.cuda.synchronize()
-    n_e2e = max(1, min(args.steps, 3))
+    n_e2e = max(4, min(2 * args.steps, 20))
+    if world > 1:
+        dist.barrier()
     t0 = time.perf_counter()
-    for _ in range(n_e2e):
-        res, _ = ex._extract_batch(host, wh, wh)
+    res = None
+    ex.pipe_stats.update(stage_s=0.0, launch_s=0.0, finish_s=0.0, batches=0)
+    for _, res, _ in ex.extract_batches([(host, wh, wh, None)] * n_e2e):  # every batch: staged, uploaded, read back
+        assert res is not None
     torch.cuda.synchronize()
     dt = torch.tensor([time.perf_counter() - t0], dtype=torch.float64, device=dev)
     if world > 1:
         dist.all_reduce(dt, op=dist.ReduceOp.MAX)
-    kp_bytes = sum(k.nbytes + d.nbytes for k, d in res)
+    kp_bytes = int(ex.last_d2h_bytes)  # whole [B, cap, .] output buffers + counts, as copied
     peak_tf, _, peak_src = _peaks()
     tf = extract_flops_per_image() * EXTRACT_BATCH / (ms_fwd / 1e3) / 1e12
     return {
@@ -417,8 +421,11 @@ def run_extract(args, torch, dist, dev, local, world):
                    "mean_keypoints_per_image": float(out.counts.float().mean().item()),
                    "l2": "activations (134 MB residual stream, 269 MB qkv/MLP per batch) exceed the 126 MB L2"},
         "e2e": {"value": world * EXTRACT_BATCH * n_e2e / float(dt.item()), "unit": "images/s",
-                "h2d_bytes_per_step": int(imgs.numel()), "d2h_bytes_per_step": int(kp_bytes + 4 * EXTRACT_BATCH),
-                "api": "ViTExtractor._extract_batch (host BGR uint8 images -> host keypoints f32 + descriptors u8)"},
+                "h2d_bytes_per_step": int(imgs.numel()), "d2h_bytes_per_step": kp_bytes,
+                "host_ms_per_step": {k: round(1e3 * v / n_e2e, 3) for k, v in ex.pipe_stats.items() if k != "batches"},
+                "api": "ViTExtractor.extract_batches (host BGR uint8 images -> host keypoints f32 + descriptors u8; "
+                       "the pipeline extract() runs: two batches queued on the device, staging / upload / read-back on "
+                       "their own streams)"},
         "roofline": {"bound": "tensor", "achieved": tf, "peak": peak_tf, "unit": "TFLOP/s", "frac": tf / peak_tf,
                      "traffic": None, "peak_source": f"{peak_src} sustained bf16", "kernel": "vc_vit_forward (all launches)",
                      "kernel_ms": ms_fwd,
@@ -464,6 +471,26 @@ def run_extract_trainable(args, torch, dist, dev, local, world):
     ms = timed(lambda: ex._forward_device(imgs, wh, wh), n)
     ms_head = timed(lambda: ex.head.forward(tokens, (gh, gh), dense_descriptors=False), n)
     counts = ex._forward_device(imgs, wh, wh)[4]
+    host = [im.cpu().numpy() for im in imgs]
+    list(ex.extract_batches([(host, wh, wh, None)] * 4))  # warm-up: allocator pools for two batches in flight
+    torch.cuda.synchronize()
+    n_e2e = max(4, min(2 * args.steps, 20))
+    if world > 1:
+        dist.barrier()
+    t0 = time.perf_counter()
+    res = None
+    ex.pipe_stats.update(stage_s=0.0, launch_s=0.0, finish_s=0.0, batches=0)
+    for _, res, _ in ex.extract_batches([(host, wh, wh, None)] * n_e2e):
+        assert res is not None
+    torch.cuda.synchronize()
+    dt = torch.tensor([time.perf_counter() - t0], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(dt, op=dist.ReduceOp.MAX)
+    e2e = {"value": world * B * n_e2e / float(dt.item()), "unit": "images/s", "h2d_bytes_per_step": int(imgs.numel()),
+           "d2h_bytes_per_step": int(ex.last_d2h_bytes),
+           "host_ms_per_step": {k: round(1e3 * v / n_e2e, 3) for k, v in ex.pipe_stats.items() if k != "batches"},
+           "api": "TrainableViTExtractor.extract_batches (host BGR uint8 images -> host keypoints [n,6] f32 + "
+                  "descriptors u8)"}
     peak_tf, _, peak_src = _peaks()
     tf = ex.head.flops_per_image(gh, gh) * B / (ms_head / 1e3) / 1e12
     return {"metric": "extracted_images_per_sec@trainable_vitb14_518px_d128", "value": world * B / (ms / 1e3),
@@ -471,6 +498,7 @@ def run_extract_trainable(args, torch, dist, dev, local, world):
             "config": {"workload": f"{EXTRACT_MODEL} forward + conv head + NMS/top-8192 selection + sparse 128-d "
                                    f"descriptors, batch {B} x {EXTRACT_SIZE}x{EXTRACT_SIZE} per GPU per step",
                        "mean_keypoints_per_image": float(counts.float().mean().item())},
+            "e2e": e2e,
             "roofline": {"bound": "tensor", "achieved": tf, "peak": peak_tf, "unit": "TFLOP/s", "frac": tf / peak_tf,
                          "traffic": None, "peak_source": f"{peak_src} sustained bf16",
                          "kernel": "vc_conv_head_forward (conv_gemm_kernel launches)", "kernel_ms": ms_head,

@@ -175,7 +175,8 @@ typedef enum {
  *   desc_bf16   : bf16 [n_images, capacity, d], unit rows = matcher input         (may be NULL)
  *   desc_u8     : uint8 [n_images, capacity, d], database blob rows              (may be NULL)
  *   desc_f32    : f32 [n_images, capacity, d], unit rows                         (may be NULL)
- * Rows >= counts[i] are left untouched.
+ * Rows >= counts[i] (up to capacity) are zero-filled in every output given, so the buffers may be
+ * handed over uninitialised.
  * Replaces: _extract_descriptors_interp (F.grid_sample bilinear/border/align_corners=True)
  * vit_extractor.py:545-586, the projection apply :651, F.normalize :243 and the uint8
  * conversion :246-250. */

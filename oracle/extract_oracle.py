@@ -209,6 +209,55 @@ def synthetic_feature_map(seed: int, C: int, H: int, W: int) -> torch.Tensor:
     return torch.from_numpy(0.5 * base + low)
 
 
+# ------------------------------------------------------------------ hybrid extractor
+def hybrid_grid_coords(keypoints_xy: np.ndarray, orig_wh, feat_wh, grid_hw) -> np.ndarray:
+    """hybrid_extractor.py:247-255: detector pixels -> feature-map units, f32 array arithmetic with
+    Python-float scales.  Returns [n,2] (y, x) float32."""
+    H, W = grid_hw
+    w_orig, h_orig = orig_wh
+    w_feat, h_feat = feat_wh
+    kp = np.asarray(keypoints_xy, np.float32).reshape(-1, 2)
+    kx = kp[:, 0] * (w_feat / w_orig) * (W / w_feat)
+    ky = kp[:, 1] * (h_feat / h_orig) * (H / h_feat)
+    return np.stack([ky, kx], axis=1).astype(np.float32)
+
+
+def hybrid_sample(fm: torch.Tensor, coords_yx: np.ndarray) -> torch.Tensor:
+    """hybrid_extractor.py:257-279: grid_sample (bilinear, border, align_corners=True) at float
+    feature-map coordinates; [n, C] raw rows."""
+    C, H, W = fm.shape
+    gx = (2.0 * coords_yx[:, 1] / (W - 1) - 1.0).astype(np.float32)
+    gy = (2.0 * coords_yx[:, 0] / (H - 1) - 1.0).astype(np.float32)
+    grid = torch.stack([torch.from_numpy(gx), torch.from_numpy(gy)], dim=1).unsqueeze(0).unsqueeze(2)
+    d = F.grid_sample(fm.unsqueeze(0), grid, mode="bilinear", padding_mode="border", align_corners=True)
+    return d.squeeze(0).squeeze(2).t()
+
+
+def rootsift(desc: torch.Tensor) -> torch.Tensor:
+    """hybrid_extractor.py:286-288: L1 normalise, sqrt(clamp(min=1e-8)), L2 normalise."""
+    d = F.normalize(desc, p=1, dim=1)
+    d = torch.sqrt(torch.clamp(d, min=1e-8))
+    return F.normalize(d, p=2, dim=1)
+
+
+def hybrid_descriptors(fm: torch.Tensor, keypoints_xy: np.ndarray, orig_wh, feat_wh, descriptor_dim: int,
+                       projection=None):
+    """hybrid_extractor.py:224-294 (_extract_descriptors_at_keypoints)."""
+    C, H, W = fm.shape
+    if len(keypoints_xy) == 0:
+        return {"desc_float": np.zeros((0, descriptor_dim), np.float32),
+                "desc_u8": np.zeros((0, descriptor_dim), np.uint8), "projection": projection}
+    coords = hybrid_grid_coords(keypoints_xy, orig_wh, feat_wh, (H, W))
+    desc = hybrid_sample(fm, coords)
+    if desc.shape[1] > descriptor_dim:
+        if projection is None:
+            projection = fit_pca(desc, descriptor_dim)
+        desc = desc @ projection
+    dn = rootsift(desc)
+    return {"coords": coords, "desc_float": dn.numpy(), "projection": projection,
+            "desc_u8": (dn.numpy() * 512.0).clip(0, 255).astype(np.uint8)}
+
+
 # ------------------------------------------------------------------ trainable_vit extractor
 def simple_nms(scores: torch.Tensor, radius: int) -> torch.Tensor:
     """trainable_vit_extractor.py:114-138: keep == max_pool2d(k=2r+1, s=1, pad=r)."""

@@ -229,3 +229,53 @@ def test_trainable_select_large_map_and_tanh(pp):
         assert np.array_equal(gk[po][:, :3], rk[pg][:, :3])
         assert np.abs(gk[po][:, 3] - rk[pg][:, 3]).max() < 1e-6 and np.abs(gk[po][:, 4] - rk[pg][:, 4]).max() <= 1.2e-7
         assert np.abs(du8[i, :n].cpu().numpy()[po].astype(int) - rd[pg].astype(int)).max() <= 1
+
+
+HYBRID = sorted((Path(__file__).parent / "golden").glob("hybrid_*.npz"))
+
+
+@pytest.mark.parametrize("path", HYBRID, ids=[p.stem for p in HYBRID])
+def test_hybrid_rootsift_descriptors_match_reference(pp, path):
+    """vc_sample_pack (float coordinates, RootSIFT flag) vs the reference's own
+    _extract_descriptors_at_keypoints outputs (hybrid_extractor.py:224-294) and the oracle."""
+    import torch
+    from oracle import extract_oracle as eo
+    from vit_colmap_b200.features.hybrid_extractor import HybridViTExtractor
+    g = np.load(path)
+    seed, C, H, W, n, d, ow, oh, fw, fh = (int(x) for x in g["meta"])
+    fm = eo.synthetic_feature_map(seed, C, H, W)
+    proj = torch.from_numpy(g["projection"]) if g["projection"].size else None
+    yx = HybridViTExtractor.grid_coords(g["keypoints"], (ow, oh), (fw, fh), (H, W))
+    ref = eo.hybrid_descriptors(fm, g["keypoints"], (ow, oh), (fw, fh), d, projection=proj)
+    assert np.array_equal(yx, ref["coords"])
+    coords = torch.from_numpy(yx).cuda()[None].contiguous()
+    counts = torch.tensor([n], dtype=torch.int32, device="cuda")
+    _, dbf, du8, df32 = pp.sample_pack(_tokens(fm), (H, W), coords, counts, (ow, oh), (fw, fh), projection=proj,
+                                       want_f32=True, rootsift=True)
+    got = df32[0, :n].cpu().numpy()
+    assert np.abs(got - ref["desc_float"]).max() < 1e-5        # tolerance: fp32 summation order
+    diff = np.abs(du8[0, :n].cpu().numpy().astype(int) - g["desc_u8"].astype(int))
+    assert diff.max() <= 1 and (diff > 0).mean() < 2e-3         # trunc edge of 512 v
+    assert np.abs(dbf[0, :n].float().cpu().numpy() - got).max() <= 2 ** -8
+
+
+def test_rootsift_flag_batched_bf16_ragged(pp):
+    """Two images, ragged counts, bf16 tokens, no projection: rows >= count untouched, unit norm."""
+    import torch
+    from oracle import extract_oracle as eo
+    C, H, W = 128, 12, 17
+    fms = [eo.synthetic_feature_map(s, C, H, W) for s in (21, 22)]
+    tok = torch.cat([_tokens(f, torch.bfloat16) for f in fms])
+    rng = np.random.default_rng(5)
+    n = [40, 7]
+    yx = np.zeros((2, 40, 2), np.float32)
+    for i in range(2):
+        yx[i, : n[i]] = np.stack([rng.uniform(0, H - 1, n[i]), rng.uniform(0, W - 1, n[i])], 1)
+    counts = torch.tensor(n, dtype=torch.int32, device="cuda")
+    _, dbf, du8, df32 = pp.sample_pack(tok, (H, W), torch.from_numpy(yx).cuda(), counts, (W * 14, H * 14),
+                                       (W * 14, H * 14), want_f32=True, rootsift=True)
+    for i in range(2):
+        fm16 = fms[i].to(torch.bfloat16).float()
+        ref = eo.rootsift(eo.hybrid_sample(fm16, yx[i, : n[i]])).numpy()
+        assert np.abs(df32[i, : n[i]].cpu().numpy() - ref).max() < 1e-5
+        assert (du8[i, n[i]:] == 0).all() and (df32[i, n[i]:] == 0).all()

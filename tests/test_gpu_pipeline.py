@@ -139,3 +139,75 @@ def test_trainable_vit_pipeline_into_database(tmp_path):
     assert len(res) == 6
     assert con.execute("SELECT COUNT(*) FROM matches").fetchone()[0] == 6
     ex.backbone.close()
+
+
+def test_hybrid_extractor_into_database(tmp_path):
+    """Hybrid extractor (cv2 GFTT detector + ViT-S descriptors) end to end: _run_inference contract
+    of hybrid_extractor.py:326-357, descriptors equal to the oracle chained on the same tokens, and
+    rows in the COLMAP database."""
+    import cv2
+    import torch
+    from oracle import extract_oracle as eo
+    from vit_colmap_b200.database import ColmapDatabase
+    from vit_colmap_b200.features.hybrid_extractor import ViTExtractor as Hybrid
+    rng = np.random.default_rng(0)
+    img_dir = tmp_path / "images"
+    img_dir.mkdir()
+    base = cv2.GaussianBlur(rng.integers(0, 256, (300, 400, 3), dtype=np.uint8), (0, 0), 2.0)
+    base = cv2.normalize(base, None, 0, 255, cv2.NORM_MINMAX)
+    for i in range(3):
+        cv2.imwrite(str(img_dir / f"im{i}.png"), np.roll(base, 9 * i, axis=1))
+    ex = Hybrid(model_name="dinov2_vits14", num_keypoints=300, descriptor_dim=64, detector_type="gftt",
+                synthetic_seed=0)
+    img = cv2.imread(str(img_dir / "im0.png"))
+    kps, desc = ex._run_inference(img)
+    assert kps.dtype == np.float32 and kps.shape[1] == 2 and desc.dtype == np.uint8
+    assert desc.shape == (len(kps), 64) and len(kps) > 64
+    # oracle on the same device tokens
+    rimg, orig_wh, feat_wh = ex._resize(img)
+    tok = ex.model.forward_patch_tokens(torch.from_numpy(rimg)[None].cuda(), bgr=True)
+    gh, gw = rimg.shape[0] // 14, rimg.shape[1] // 14
+    fm = tok[0].float().cpu().reshape(gh, gw, -1).permute(2, 0, 1).contiguous()
+    ref = eo.hybrid_descriptors(fm, kps, orig_wh, feat_wh, 64, projection=ex.descriptor_projection.cpu())
+    diff = np.abs(desc.astype(int) - ref["desc_u8"].astype(int))
+    assert diff.max() <= 1 and (diff > 0).mean() < 5e-3
+    db_path = tmp_path / "db.db"
+    ex.extract(img_dir, db_path, "SIMPLE_PINHOLE")
+    with ColmapDatabase.open_database(str(db_path)) as db:
+        assert ColmapDatabase.get_db_count(db, "num_images") == 3
+        for i in (1, 2, 3):
+            assert db.exists_keypoints(i) and db.exists_descriptors(i)
+            assert db.read_descriptors(i).shape[1] == 64
+        k1 = db.read_keypoints(1)
+    assert np.array_equal(k1, kps)
+
+
+def test_pipelined_batches_equal_serial_batches(vit_s):
+    """BatchPipeline.extract_batches (upload of batch k+1 under the kernels of batch k, two input
+    slots) returns, in order, exactly what the serial _extract_batch returns; a failing batch is
+    reported through on_error and does not disturb its neighbours."""
+    rng = np.random.default_rng(3)
+    sizes = [(224, 224), (224, 224), (154, 238), (224, 224), (224, 224)]
+    batches = []
+    for k, (h, w) in enumerate(sizes):
+        imgs = [rng.integers(0, 256, (h, w, 3), dtype=np.uint8) for _ in range(1 + k % 3)]
+        batches.append((imgs, (w, h), (w, h), None))
+    vit_s._run_inference(batches[0][0][0])          # projection fitted before either schedule runs
+    serial = [vit_s._extract_batch(b[0], b[1], b[2])[0] for b in batches]
+    got = list(vit_s.extract_batches(batches))
+    assert [g[0] for g in got] == list(range(len(batches)))
+    for (_, out, _), ref in zip(got, serial):
+        assert len(out) == len(ref)
+        for (k1, d1), (k2, d2) in zip(out, ref):
+            assert np.array_equal(k1, k2) and np.array_equal(d1, d2)
+    # batch 1 is malformed (unequal image sizes): reported, skipped, the rest unaffected
+    bad = list(batches)
+    bad[1] = ([batches[1][0][0], batches[2][0][0]], (224, 224), (224, 224), None)
+    errors = []
+    got = list(vit_s.extract_batches(bad, on_error=lambda k, e: errors.append(k)))
+    assert errors == [1] and got[1][1] is None
+    for i in (0, 2, 3, 4):
+        for (k1, d1), (k2, d2) in zip(got[i][1], serial[i]):
+            assert np.array_equal(k1, k2) and np.array_equal(d1, d2)
+    with pytest.raises(ValueError):
+        list(vit_s.extract_batches(bad))

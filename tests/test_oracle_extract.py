@@ -83,3 +83,24 @@ def test_trainable_restatement_matches_reference_outputs(path):
     po, pg = key(kps), key(g["keypoints"])
     assert np.array_equal(kps[po], g["keypoints"][pg])
     assert np.array_equal(du8[po], g["desc_u8"][pg])
+
+
+HYBRID = sorted((Path(__file__).parent / "golden").glob("hybrid_*.npz"))
+
+
+@pytest.mark.parametrize("path", HYBRID, ids=[p.stem for p in HYBRID])
+def test_hybrid_restatement_matches_reference_outputs(path):
+    """oracle hybrid_descriptors vs the reference's own _extract_descriptors_at_keypoints
+    (hybrid_extractor.py:224-294; oracle/gen_golden_hybrid.py)."""
+    g = np.load(path)
+    seed, C, H, W, n, d, ow, oh, fw, fh = (int(x) for x in g["meta"])
+    fm = eo.synthetic_feature_map(seed, C, H, W)
+    proj = torch.from_numpy(g["projection"]) if g["projection"].size else None
+    out = eo.hybrid_descriptors(fm, g["keypoints"], (ow, oh), (fw, fh), d, projection=proj)
+    assert out["desc_u8"].shape == g["desc_u8"].shape == (n, d)
+    assert np.array_equal(out["desc_u8"], g["desc_u8"])
+
+
+def test_hybrid_empty_keypoints():
+    out = eo.hybrid_descriptors(eo.synthetic_feature_map(0, 8, 5, 5), np.zeros((0, 2), np.float32), (70, 70), (70, 70), 8)
+    assert out["desc_u8"].shape == (0, 8)

@@ -133,13 +133,30 @@ __device__ __forceinline__ void store4(const SampleParams& p, size_t row, int v,
   }
 }
 
+// Rows at or beyond counts[b] are zero-filled here, so the caller can hand over uninitialised
+// output buffers (saves a full extra write pass over [B, cap, d] x 3 outputs).
+__device__ __forceinline__ void zero_row(const SampleParams& p, size_t kp, int lane) {
+  const float4 z = make_float4(0.f, 0.f, 0.f, 0.f);
+  for (int v = lane; v < (p.d >> 2); v += 32) {
+    const size_t e = kp * p.d + 4 * (size_t)v;
+    if (p.desc_f32) *reinterpret_cast<float4*>(p.desc_f32 + e) = z;
+    if (p.desc_bf16) *reinterpret_cast<uint2*>(p.desc_bf16 + e) = make_uint2(0u, 0u);
+    if (p.desc_u8) *reinterpret_cast<uchar4*>(p.desc_u8 + e) = make_uchar4(0, 0, 0, 0);
+  }
+  if (lane == 0 && p.keypoints) reinterpret_cast<float2*>(p.keypoints)[kp] = make_float2(0.f, 0.f);
+}
+
 template <typename T>
 __global__ void __launch_bounds__(256) sample_pack_direct(const SampleParams p) {
   const int lane = threadIdx.x & 31;
   const long long wg = ((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
   const int b = (int)(wg / p.cap), k = (int)(wg - (long long)b * p.cap);
-  if (b >= p.B || k >= min(p.counts[b], p.cap)) return;
+  if (b >= p.B) return;
   const size_t kp = (size_t)b * p.cap + k;
+  if (k >= min(p.counts[b], p.cap)) {
+    zero_row(p, kp, lane);
+    return;
+  }
   float fy, fx;
   read_coord(p, kp, fy, fx);
   const Taps t = make_taps(fy, fx, p.H, p.W);
@@ -212,9 +229,10 @@ __global__ void __launch_bounds__(256) sample_pack_project(const SampleParams p,
   const int b = blockIdx.x / tiles_per_image;
   const int k0 = (blockIdx.x - b * tiles_per_image) * kTile;
   const int cnt = min(p.counts[b], p.cap);
-  if (k0 >= cnt) return;
-  const int nk = min(kTile, cnt - k0);
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int nk = max(0, min(kTile, cnt - k0));
+  for (int kk = nk + warp; kk < kTile && k0 + kk < p.cap; kk += 8) zero_row(p, (size_t)b * p.cap + k0 + kk, lane);
+  if (nk == 0) return;
   const T* img = static_cast<const T*>(p.tokens) + (int64_t)b * p.image_stride;
   const int nvec = p.C >> 2;
 

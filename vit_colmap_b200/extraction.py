@@ -16,6 +16,7 @@ import numpy as np
 from . import _lib
 
 METHODS = {"harris": 0, "dog": 1, "combined": 2}
+NORM_ROOTSIFT = 0x10  # VC_NORM_ROOTSIFT, include/vc_b200.h
 QUANT_VIT, QUANT_COLMAP, QUANT_TRAINABLE = 0, 1, 2
 
 
@@ -107,8 +108,12 @@ class PostProcessor:
         return coords, scores, counts
 
     def sample_pack(self, tokens, grid_hw, coords, counts, orig_wh, resized_wh, projection=None,
-                    quant_mode: int = QUANT_VIT, want_f32: bool = False, projection_bias=None):
+                    quant_mode: int = QUANT_VIT, want_f32: bool = False, projection_bias=None,
+                    rootsift: bool = False):
+        """rootsift: L1-normalise + sqrt before the L2 step (hybrid_extractor.py:286-288)."""
         torch = self.torch
+        if rootsift:
+            quant_mode = int(quant_mode) | NORM_ROOTSIFT
         H, W = grid_hw
         B, T, C = tokens.shape
         cap = int(coords.shape[1])
@@ -118,10 +123,11 @@ class PostProcessor:
         w_res, h_res = resized_wh
         w_orig, h_orig = orig_wh
         scale = (ctypes.c_float * 4)(w_res / W, w_orig / w_res, h_res / H, h_orig / h_res)
-        kps = torch.zeros((B, cap, 2), dtype=torch.float32, device=tokens.device)
-        dbf = torch.zeros((B, cap, d), dtype=torch.bfloat16, device=tokens.device)
-        du8 = torch.zeros((B, cap, d), dtype=torch.uint8, device=tokens.device)
-        df32 = torch.zeros((B, cap, d), dtype=torch.float32, device=tokens.device) if want_f32 else None
+        # vc_sample_pack zero-fills the rows beyond counts[i] itself: no memset pass over the outputs
+        kps = torch.empty((B, cap, 2), dtype=torch.float32, device=tokens.device)
+        dbf = torch.empty((B, cap, d), dtype=torch.bfloat16, device=tokens.device)
+        du8 = torch.empty((B, cap, d), dtype=torch.uint8, device=tokens.device)
+        df32 = torch.empty((B, cap, d), dtype=torch.float32, device=tokens.device) if want_f32 else None
         is_float = coords.dtype == torch.float32
         _lib.check(self.lib.vc_sample_pack(self.handle, _ptr(tokens), self._dtype_code(torch, tokens), B, H, W, C,
                                            int(tokens.stride(0)), _ptr(coords.contiguous()), int(is_float),
@@ -168,9 +174,9 @@ def trainable_select_pack(pp: PostProcessor, kp_map, desc_map, orig_wh, resized_
     _lib.check(pp.lib.vc_trainable_select(pp.handle, _ptr(kp_map), B, h4, w4, int(num_keypoints),
                                           float(score_threshold), int(nms_radius), int(bool(apply_tanh)), scale,
                                           _ptr(coords), _ptr(kps), _ptr(counts), cap, _ptr(ws), need, pp._stream()))
-    dbf = torch.zeros((B, cap, d), dtype=torch.bfloat16, device=kp_map.device)
-    du8 = torch.zeros((B, cap, d), dtype=torch.uint8, device=kp_map.device)
-    df32 = torch.zeros((B, cap, d), dtype=torch.float32, device=kp_map.device) if want_f32 else None
+    dbf = torch.empty((B, cap, d), dtype=torch.bfloat16, device=kp_map.device)  # tails zeroed by the kernel
+    du8 = torch.empty((B, cap, d), dtype=torch.uint8, device=kp_map.device)
+    df32 = torch.empty((B, cap, d), dtype=torch.float32, device=kp_map.device) if want_f32 else None
     tok = desc_map.reshape(B, h4 * w4, c)
     if projection is not None:
         projection = projection.to(device=kp_map.device, dtype=torch.float32).contiguous()

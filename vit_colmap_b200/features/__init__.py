@@ -12,4 +12,7 @@ def __getattr__(name):  # the GPU extractors import torch lazily
     if name == "TrainableViTExtractor":
         from .trainable_vit_extractor import TrainableViTExtractor
         return TrainableViTExtractor
+    if name == "HybridViTExtractor":
+        from .hybrid_extractor import HybridViTExtractor
+        return HybridViTExtractor
     raise AttributeError(name)

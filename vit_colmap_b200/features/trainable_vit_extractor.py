@@ -17,6 +17,7 @@ from typing import List, Optional, Tuple
 
 import numpy as np
 
+from ._pipelined import BatchPipeline
 from .base_extractor import BaseExtractor
 
 PATCH = 14
@@ -37,7 +38,7 @@ def split_checkpoint(checkpoint):
     return backbone, head
 
 
-class TrainableViTExtractor(BaseExtractor):
+class TrainableViTExtractor(BatchPipeline, BaseExtractor):
     def __init__(self, weights_path: Optional[str] = None, model_name: str = "dinov2_vitb14",
                  num_keypoints: int = 2048, descriptor_dim: int = 128, device: Optional[str] = None,
                  score_threshold: float = 0.0, nms_radius: int = 4, *, state_dict=None, head_state_dict=None,
@@ -135,48 +136,12 @@ class TrainableViTExtractor(BaseExtractor):
                                      self.num_keypoints, self.score_threshold, self.nms_radius, apply_tanh=False,
                                      want_f32=want_f32, projection=proj, projection_bias=bias)
 
-    def _upload(self, images_bgr: List[np.ndarray]):
-        """Host images -> one device batch [B, H, W, 3] uint8.  Each image is copied once into a
-        persistent pinned staging buffer and its host->device copy is enqueued immediately, so the
-        staging memcpy of image k+1 overlaps the DMA of image k."""
-        import torch
-        B = len(images_bgr)
-        shape = (B,) + tuple(images_bgr[0].shape)
-        n = int(np.prod(shape))
-        if getattr(self, "_pinned", None) is None or self._pinned.numel() < n:
-            self._pinned = torch.empty(n, dtype=torch.uint8).pin_memory()
-        stage = self._pinned[:n].view(shape)
-        dev = torch.empty(shape, dtype=torch.uint8, device=self.device)
-        stage_np = stage.numpy()
-        for i, img in enumerate(images_bgr):
-            np.copyto(stage_np[i], img)
-            dev[i].copy_(stage[i], non_blocking=True)
-        return dev
-
-    def _download(self, kps, du8, nmax: int):
-        """Only the populated rows ([:, :nmax]) come back, through persistent pinned buffers."""
-        import torch
-        outs = []
-        for name, t in (("_pin_kps", kps), ("_pin_desc", du8)):
-            t = t[:, :nmax].contiguous()
-            buf = getattr(self, name, None)
-            if buf is None or buf.numel() < t.numel() or buf.dtype != t.dtype:
-                buf = torch.empty(max(t.numel(), 1), dtype=t.dtype).pin_memory()
-                setattr(self, name, buf)
-            host = buf[: t.numel()].view(t.shape)
-            host.copy_(t, non_blocking=True)
-            outs.append(host)
-        torch.cuda.current_stream(self.device).synchronize()
-        return outs[0].numpy(), outs[1].numpy()
+    def _device_stage(self, batch, orig_wh, resized_wh, extra=None):
+        kps, du8, dbf, _, counts = self._forward_device(batch, orig_wh, resized_wh)
+        return kps, du8, counts, (counts, dbf)
 
     def _extract_batch(self, images_bgr: List[np.ndarray], orig_wh, resized_wh):
-        import torch
-        batch = self._upload(images_bgr)
-        kps, du8, dbf, _, counts = self._forward_device(batch, orig_wh, resized_wh)
-        n = counts.cpu().numpy()
-        kps_h, du8_h = self._download(kps, du8, int(n.max()) if len(n) else 0)
-        out = [(kps_h[i, : n[i]].copy(), du8_h[i, : n[i]].copy()) for i in range(len(images_bgr))]
-        return out, (counts, dbf)
+        return self._run_batch(images_bgr, orig_wh, resized_wh)
 
     def _run_inference(self, image_bgr: np.ndarray):
         """Single image -> (keypoints f32 [N,6] = x, y, 1, orientation, score, 0; descriptors u8 [N,d])
@@ -219,44 +184,36 @@ class TrainableViTExtractor(BaseExtractor):
         camera_id = db.db.write_camera(make_camera(camera_model, width, height, camera_params))
         print(f"Camera ID: {camera_id}\n")
 
-        pending: List[Tuple[int, np.ndarray, tuple, tuple, str]] = []
-
-        def flush():
-            if not pending:
-                return
-            try:
-                out, _ = self._extract_batch([p[1] for p in pending], pending[0][2], pending[0][3])
-            except Exception as e:  # noqa: BLE001  per-image skip semantics, trainable_vit_extractor.py:381-386
-                print(f"  Error during feature extraction: {e}")
-                import traceback
-                traceback.print_exc()
-                pending.clear()
-                return
-            for (image_id, _, _, _, name), (kps, desc) in zip(pending, out):
-                print(f"{name}: extracted {len(kps)} keypoints, descriptor shape {desc.shape}")
-                if len(kps) == 0:
-                    print("  Warning: No keypoints extracted")
+        def items():
+            for idx, f in enumerate(files, start=1):
+                img = cv2.imread(str(f))
+                if img is None:
+                    print(f"[{idx}/{len(files)}] {f.name}: Warning: Failed to read image, skipping")
                     continue
-                print(f"  Score range: [{kps[:, 4].min():.3f}, {kps[:, 4].max():.3f}]")
-                db.add_keypoints(image_id, kps)
-                db.add_descriptors(image_id, desc)
-            pending.clear()
+                image_id = db.add_image(f.name, camera_id=camera_id)
+                try:
+                    img, orig_wh, resized_wh = self._resize(img)
+                except Exception as e:  # noqa: BLE001
+                    print(f"  Error during feature extraction: {e}")
+                    continue
+                yield (image_id, f.name), img, orig_wh, resized_wh, None
 
-        for idx, f in enumerate(files, start=1):
-            img = cv2.imread(str(f))
-            if img is None:
-                print(f"[{idx}/{len(files)}] {f.name}: Warning: Failed to read image, skipping")
-                continue
-            image_id = db.add_image(f.name, camera_id=camera_id)
-            try:
-                img, orig_wh, resized_wh = self._resize(img)
-            except Exception as e:  # noqa: BLE001
-                print(f"  Error during feature extraction: {e}")
-                continue
-            if pending and (pending[0][2] != orig_wh or len(pending) >= self.batch_size):
-                flush()
-            pending.append((image_id, img, orig_wh, resized_wh, f.name))
-        flush()
+        def write(meta, kps, desc):
+            image_id, name = meta
+            print(f"{name}: extracted {len(kps)} keypoints, descriptor shape {desc.shape}")
+            if len(kps) == 0:
+                print("  Warning: No keypoints extracted")
+                return
+            print(f"  Score range: [{kps[:, 4].min():.3f}, {kps[:, 4].max():.3f}]")
+            db.add_keypoints(image_id, kps)
+            db.add_descriptors(image_id, desc)
+
+        def on_error(k, e):  # per-image skip semantics, trainable_vit_extractor.py:381-386
+            print(f"  Error during feature extraction: {e}")
+            import traceback
+            traceback.print_exception(type(e), e, e.__traceback__)
+
+        self.extract_stream(items(), self.batch_size, write, on_error)
         db.commit()
         db.close()
         print(f"\n{'=' * 60}\nFeature extraction complete!\n{'=' * 60}\n")

@@ -14,12 +14,13 @@ from typing import List, Optional, Tuple
 
 import numpy as np
 
+from ._pipelined import BatchPipeline
 from .base_extractor import BaseExtractor, default_camera_params, list_images
 
 PATCH = 14
 
 
-class ViTExtractor(BaseExtractor):
+class ViTExtractor(BatchPipeline, BaseExtractor):
     def __init__(self, weights_path: Optional[str] = None, model_name: str = "dinov2_vitb14",
                  num_keypoints: int = 2048, descriptor_dim: int = 128, device: Optional[str] = None,
                  detection_method: str = "harris", *, state_dict=None, synthetic_seed: Optional[int] = None,
@@ -106,45 +107,8 @@ class ViTExtractor(BaseExtractor):
         self.descriptor_projection = proj.to(self.device)
 
     # ------------------------------------------------------------------ batched core
-    def _upload(self, images_bgr: List[np.ndarray]):
-        """Host images -> one device batch [B, H, W, 3] uint8.  Each image is copied once into a
-        persistent pinned staging buffer and its host->device copy is enqueued immediately, so the
-        staging memcpy of image k+1 overlaps the DMA of image k."""
-        import torch
-        B = len(images_bgr)
-        shape = (B,) + tuple(images_bgr[0].shape)
-        n = int(np.prod(shape))
-        if getattr(self, "_pinned", None) is None or self._pinned.numel() < n:
-            self._pinned = torch.empty(n, dtype=torch.uint8).pin_memory()
-        stage = self._pinned[:n].view(shape)
-        dev = torch.empty(shape, dtype=torch.uint8, device=self.device)
-        stage_np = stage.numpy()
-        for i, img in enumerate(images_bgr):
-            np.copyto(stage_np[i], img)
-            dev[i].copy_(stage[i], non_blocking=True)
-        return dev
-
-    def _download(self, kps, du8, nmax: int):
-        """Only the populated rows ([:, :nmax]) come back, through persistent pinned buffers."""
-        import torch
-        outs = []
-        for name, t in (("_pin_kps", kps), ("_pin_desc", du8)):
-            t = t[:, :nmax].contiguous()
-            buf = getattr(self, name, None)
-            if buf is None or buf.numel() < t.numel() or buf.dtype != t.dtype:
-                buf = torch.empty(max(t.numel(), 1), dtype=t.dtype).pin_memory()
-                setattr(self, name, buf)
-            host = buf[: t.numel()].view(t.shape)
-            host.copy_(t, non_blocking=True)
-            outs.append(host)
-        torch.cuda.current_stream(self.device).synchronize()
-        return outs[0].numpy(), outs[1].numpy()
-
-    def _extract_batch(self, images_bgr: List[np.ndarray], orig_wh, resized_wh):
-        """images: equally sized BGR uint8 arrays (already multiples of 14).  Returns per-image
-        (keypoints f32 [n,2], descriptors u8 [n,d]) plus the device-resident SparseFeatures."""
-        import torch
-        batch = self._upload(images_bgr)
+    def _device_stage(self, batch, orig_wh, resized_wh, extra=None):
+        """Device half of one batch: ViT forward, score map, selection, sampling / PCA / packing."""
         gh, gw = batch.shape[1] // PATCH, batch.shape[2] // PATCH
         self._grid = (gh, gw)
         tokens = self.model.forward_patch_tokens(batch, bgr=True)
@@ -155,10 +119,12 @@ class ViTExtractor(BaseExtractor):
             self._fit_projection(tokens, coords, int(counts[0]))
         proj = self.descriptor_projection if C > self.descriptor_dim else None
         kps, dbf, du8, _ = self.post.sample_pack(tokens, (gh, gw), coords, counts, orig_wh, resized_wh, projection=proj)
-        n = counts.cpu().numpy()
-        kps_h, du8_h = self._download(kps, du8, int(n.max()) if len(n) else 0)
-        out = [(kps_h[i, : n[i]].copy(), du8_h[i, : n[i]].copy()) for i in range(len(images_bgr))]
-        return out, (counts, dbf)
+        return kps, du8, counts, (counts, dbf)
+
+    def _extract_batch(self, images_bgr: List[np.ndarray], orig_wh, resized_wh):
+        """images: equally sized BGR uint8 arrays (already multiples of 14).  Returns per-image
+        (keypoints f32 [n,2], descriptors u8 [n,d]) plus the device-resident (counts, bf16 rows)."""
+        return self._run_batch(images_bgr, orig_wh, resized_wh)
 
     def _run_inference(self, image_bgr: np.ndarray):
         """Single-image convenience over the batched path (vit_extractor.py:106-166)."""
@@ -190,47 +156,38 @@ class ViTExtractor(BaseExtractor):
         print(f"Image dimensions: {width}x{height}\nCamera model: {camera_model}\nCamera ID: {camera_id}\n")
 
         # image ids follow the sorted file order (single writer); features are computed in batches
-        pending: List[Tuple[int, np.ndarray, tuple, tuple]] = []
-
-        def flush():
-            if not pending:
-                return
-            try:
-                out, _ = self._extract_batch([p[1] for p in pending], pending[0][2], pending[0][3])
-            except Exception as e:  # noqa: BLE001  per-image skip semantics, vit_extractor.py:757-762
-                print(f"  ✗ Error during feature extraction: {e}")
-                import traceback
-                traceback.print_exc()
-                pending.clear()
-                return
-            for (image_id, _, _, _), (kps, desc) in zip(pending, out):
-                if len(kps) == 0:
-                    print("  ⚠ Warning: No keypoints extracted")
+        # through BatchPipeline.extract_stream: decoding / staging of the next batch and the database
+        # writes of the previous one run under the current batch's kernels
+        def items():
+            for idx, f in enumerate(files, start=1):
+                img = cv2.imread(str(f))
+                if img is None:
+                    print(f"[{idx}/{len(files)}] {f.name}: ⚠ Warning: Failed to read image, skipping")
                     continue
-                db.add_keypoints(image_id, kps)
-                db.add_descriptors(image_id, desc)
-            pending.clear()
+                image_id = db.add_image(f.name, camera_id=camera_id)
+                try:
+                    img, orig_wh, resized_wh = self._resize(img)
+                except Exception as e:  # noqa: BLE001
+                    print(f"  ✗ Error during feature extraction: {e}")
+                    continue
+                yield image_id, img, orig_wh, resized_wh, None
 
-        for idx, f in enumerate(files, start=1):
-            img = cv2.imread(str(f))
-            if img is None:
-                print(f"[{idx}/{len(files)}] {f.name}: ⚠ Warning: Failed to read image, skipping")
-                continue
-            image_id = db.add_image(f.name, camera_id=camera_id)
-            try:
-                img, orig_wh, resized_wh = self._resize(img)
-            except Exception as e:  # noqa: BLE001
-                print(f"  ✗ Error during feature extraction: {e}")
-                continue
-            same = pending and pending[0][2] == orig_wh
-            # the PCA projection is fitted on the first image alone, as in the reference
-            first_alone = self.descriptor_projection is None and self.model.embed_dim > self.descriptor_dim
-            if pending and (not same or len(pending) >= self.batch_size or first_alone):
-                flush()
-            pending.append((image_id, img, orig_wh, resized_wh))
-            if first_alone:
-                flush()
-        flush()
+        def write(image_id, kps, desc):
+            if len(kps) == 0:
+                print("  ⚠ Warning: No keypoints extracted")
+                return
+            db.add_keypoints(image_id, kps)
+            db.add_descriptors(image_id, desc)
+
+        def on_error(k, e):  # per-image skip semantics, vit_extractor.py:757-762
+            print(f"  ✗ Error during feature extraction: {e}")
+            import traceback
+            traceback.print_exception(type(e), e, e.__traceback__)
+
+        # the PCA projection is fitted on the first image alone, as in the reference
+        self.extract_stream(items(), self.batch_size, write, on_error,
+                            first_alone=lambda: self.descriptor_projection is None
+                            and self.model.embed_dim > self.descriptor_dim)
         db.commit()
         db.close()
         print(f"\n{'=' * 60}\n✓ Feature extraction complete!\n{'=' * 60}\n")
