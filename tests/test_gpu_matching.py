@@ -200,3 +200,55 @@ def test_l2_rule_matches_oracle(matcher):
                 ref = om.match_l2_numpy(desc[i1, : counts[i1]], desc[i2, : counts[i2]], ratio, dist, cross)
                 assert got[k].tolist() == ref.tolist(), (k, cross, len(got[k]), len(ref))
     assert len(matcher.match_pairs_host(dummy, np.array(counts, np.int32), np.array([[0, 1]], np.int32), rule="l2")[0]) >= 140
+
+
+@pytest.mark.parametrize("dtype", ["f32", "bf16", "u8"])
+def test_host_entry_chunked_upload_groups(matcher, dtype):
+    """vc_match_pairs_host above its chunking threshold (>= 8 images, >= 32 MB): the upload is cut
+    into four image chunks, the pairs are re-ordered by the chunk they wait for and the packed match
+    lists are scattered back.  Results must come back in the CALLER's pair order and equal the
+    device-resident entry (itself held to the oracle above), for shuffled / repeated / swapped /
+    self pairs and ragged counts; three pairs are also checked against the C oracle directly."""
+    import torch
+    from oracle import matching as om
+    rng = np.random.default_rng(77)
+    n_images, kmax, d = 10, 2304 if dtype == "bf16" else 1536, 2304 if dtype == "u8" else 768
+    counts = [kmax, 1500, 0, kmax, 777, kmax, 1, kmax, 1290, kmax]
+    desc = _make_set(rng, n_images, kmax, d, counts)
+    all_pairs = [(i, j) for i in range(n_images) for j in range(n_images) if i != j]
+    pairs = [all_pairs[k] for k in rng.permutation(len(all_pairs))[:40]] + [(3, 3), (9, 0), (9, 0), (0, 9)]
+    pairs_np = np.array(pairs, np.int32)
+    cnt = np.array(counts, np.int32)
+    if dtype == "u8":
+        host = np.zeros(desc.shape, np.uint8)
+        for i, n in enumerate(counts):
+            host[i, :n] = om.to_uint8_colmap(np.abs(desc[i, :n]))   # non-negative, like SIFT rows
+        dev = torch.from_numpy(host).cuda().to(torch.bfloat16)
+        inv = 1.0 / 512.0 ** 2
+    elif dtype == "bf16":
+        host = torch.from_numpy(desc).to(torch.bfloat16).view(torch.int16).numpy().view(np.uint16)
+        dev = torch.from_numpy(desc).cuda().to(torch.bfloat16)
+        inv = 1.0
+    else:
+        host = desc
+        dev = torch.from_numpy(desc).cuda().to(torch.bfloat16)
+        inv = 1.0
+    assert host.nbytes >= 32 << 20
+    got = matcher.match_pairs_host(host, cnt, pairs_np, 0.8, 0.7, True)
+    m, n = matcher.match_pairs(dev, torch.from_numpy(cnt).cuda(), torch.from_numpy(pairs_np).cuda(), 0.8, 0.7, True, inv)
+    torch.cuda.synchronize()
+    total = 0
+    for k in range(len(pairs)):
+        ref = m[k, : int(n[k])].cpu().numpy().astype(np.uint32)
+        assert got[k].tolist() == ref.tolist(), (k, pairs[k])
+        total += len(ref)
+    assert total > 2000
+    for k in (0, 1, len(pairs) - 1) if dtype != "u8" else ():
+        i1, i2 = pairs[k]
+        ref = om.match_c(desc[i1, : counts[i1]], desc[i2, : counts[i2]], 0.8, 0.7, True)
+        assert got[k].tolist() == ref.tolist()
+    # a second call with fewer pairs re-uses the staging buffers
+    got2 = matcher.match_pairs_host(host, cnt, pairs_np[:5], 0.8, 0.7, True)
+    assert [g.tolist() for g in got2] == [g.tolist() for g in got[:5]]
+    with pytest.raises(Exception):
+        matcher.match_pairs_host(host, cnt, np.array([[0, n_images]], np.int32))

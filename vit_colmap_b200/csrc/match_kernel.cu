@@ -340,6 +340,67 @@ cudaError_t launch_emit_matches(const MatchParams& p, uint32_t* matches, int32_t
   return cudaGetLastError();
 }
 
+namespace {
+
+// single CTA: exclusive scan of counts[0..n) into offsets[0..n]
+__global__ void __launch_bounds__(1024) scan_counts_kernel(const int32_t* __restrict__ counts, int n,
+                                                           int32_t* __restrict__ offsets) {
+  __shared__ int warp_tot[32];
+  __shared__ int carry;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  if (threadIdx.x == 0) carry = 0;
+  __syncthreads();
+  for (int base = 0; base < n; base += 1024) {
+    const int i = base + threadIdx.x;
+    const int v = i < n ? counts[i] : 0;
+    int x = v;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const int t = __shfl_up_sync(0xffffffffu, x, o);
+      if (lane >= o) x += t;
+    }
+    if (lane == 31) warp_tot[warp] = x;
+    __syncthreads();
+    if (warp == 0) {
+      int w = warp_tot[lane];
+#pragma unroll
+      for (int o = 1; o < 32; o <<= 1) {
+        const int t = __shfl_up_sync(0xffffffffu, w, o);
+        if (lane >= o) w += t;
+      }
+      warp_tot[lane] = w;  // inclusive over warps
+    }
+    __syncthreads();
+    const int before = carry + (warp ? warp_tot[warp - 1] : 0) + x - v;
+    if (i < n) offsets[i] = before;
+    __syncthreads();
+    if (threadIdx.x == 1023) carry = before + v;
+    __syncthreads();
+  }
+  if (threadIdx.x == 0) offsets[n] = carry;
+}
+
+__global__ void __launch_bounds__(256) pack_matches_kernel(const uint32_t* __restrict__ matches,
+                                                           const int32_t* __restrict__ n_matches,
+                                                           const int32_t* __restrict__ offsets, int kmax,
+                                                           uint32_t* __restrict__ packed) {
+  const int pair = blockIdx.x;
+  const int n = n_matches[pair];
+  const uint2* src = reinterpret_cast<const uint2*>(matches) + (size_t)pair * kmax;
+  uint2* dst = reinterpret_cast<uint2*>(packed) + offsets[pair];
+  for (int i = threadIdx.x; i < n; i += blockDim.x) dst[i] = src[i];
+}
+
+}  // namespace
+
+cudaError_t launch_compact_matches(const uint32_t* matches, const int32_t* n_matches, int n_pairs, int kmax,
+                                   int32_t* offsets, uint32_t* packed, cudaStream_t stream) {
+  if (n_pairs <= 0) return cudaSuccess;
+  scan_counts_kernel<<<1, 1024, 0, stream>>>(n_matches, n_pairs, offsets);
+  pack_matches_kernel<<<n_pairs, 256, 0, stream>>>(matches, n_matches, offsets, kmax, packed);
+  return cudaGetLastError();
+}
+
 cudaError_t launch_u8_to_bf16(const uint8_t* src, void* dst, size_t n, cudaStream_t stream) {
   if (n == 0) return cudaSuccess;
   const size_t threads = (n + 15) / 16;

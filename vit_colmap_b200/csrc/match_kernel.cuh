@@ -62,6 +62,11 @@ cudaError_t launch_match_fused(const CUtensorMap& tmap, const MatchParams& p, in
                                cudaStream_t stream);
 cudaError_t launch_emit_matches(const MatchParams& p, uint32_t* matches, int32_t* n_matches,
                                 cudaStream_t stream);
+// Packs the filled prefix of every pair's [kmax, 2] slot into one dense [total, 2] list (offsets =
+// exclusive scan of n_matches, written to offsets[0..n_pairs]) so that the host entry point reads
+// the matches of a pair group back with a single copy.
+cudaError_t launch_compact_matches(const uint32_t* matches, const int32_t* n_matches, int n_pairs, int kmax,
+                                   int32_t* offsets, uint32_t* packed, cudaStream_t stream);
 cudaError_t launch_u8_to_bf16(const uint8_t* src, void* dst, size_t n, cudaStream_t stream);
 cudaError_t launch_f32_to_bf16(const float* src, void* dst, size_t n, cudaStream_t stream);
 

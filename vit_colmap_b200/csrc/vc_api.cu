@@ -3,6 +3,7 @@
 // sm_100 device every entry point fails with VC_ERR_NO_DEVICE.
 #include "../../include/vc_b200.h"
 
+#include <algorithm>
 #include <cstdarg>
 #include <cstdio>
 #include <cstdlib>
@@ -161,6 +162,11 @@ int vc_destroy(vc_handle* h) {
   cudaSetDevice(h->device);
   cudaDeviceSynchronize();
   if (h->stage) cudaFree(h->stage);
+  if (h->pin) cudaFreeHost(h->pin);
+  for (auto st : h->host_streams)
+    if (st) cudaStreamDestroy(st);
+  for (auto ev : h->host_events)
+    if (ev) cudaEventDestroy(ev);
   delete h;
   return VC_OK;
 }
@@ -274,6 +280,10 @@ int vc_convert_f32_to_bf16(const float* src, void* dst_bf16, size_t n, void* str
   return VC_OK;
 }
 
+// Host-buffer entry.  The descriptor upload is cut into up to four image chunks on an upload stream
+// and the pairs are ordered by the last chunk they need, so group g is matched while chunk g+1 is
+// still in flight; each group's match lists are packed on the device and read back with two copies
+// on a download stream while the next group runs.
 int vc_match_pairs_host(vc_handle* h, const void* desc, int dtype, const int32_t* counts,
                         int n_images, int kmax, int d, const int32_t* pairs, int n_pairs,
                         const vc_match_options* opt, uint32_t* matches, int32_t* n_matches) {
@@ -285,18 +295,45 @@ int vc_match_pairs_host(vc_handle* h, const void* desc, int dtype, const int32_t
   if (n_images <= 0 || kmax <= 0 || n_pairs < 0 || d <= 0 || d % 8 != 0)
     return fail(VC_ERR_INVALID, "bad sizes");
   if (n_pairs == 0) return VC_OK;
+  for (int i = 0; i < 2 * n_pairs; ++i)
+    if (pairs[i] < 0 || pairs[i] >= n_images)
+      return fail(VC_ERR_INVALID, "pair %d names image %d of %d", i / 2, pairs[i], n_images);
   VC_CUDA(cudaSetDevice(h->device));
-  const size_t n_el = (size_t)n_images * kmax * d;
+  if (!h->host_streams[0]) {
+    for (auto& st : h->host_streams) VC_CUDA(cudaStreamCreateWithFlags(&st, cudaStreamNonBlocking));
+    for (auto& ev : h->host_events) VC_CUDA(cudaEventCreateWithFlags(&ev, cudaEventDisableTiming));
+  }
+  cudaStream_t s = h->host_streams[0], s_up = h->host_streams[1], s_down = h->host_streams[2];
+
+  const size_t img_el = (size_t)kmax * d;
+  const size_t n_el = (size_t)n_images * img_el;
   const size_t el = dtype == VC_DTYPE_U8 ? 1 : (dtype == VC_DTYPE_F32 ? 4 : 2);
+  // pair groups: chunk c holds images [c*per, (c+1)*per); a pair belongs to the chunk of its larger index
+  const int n_groups = (n_images >= 8 && n_el * el >= (size_t)(32u << 20)) ? 4 : 1;
+  const int per = (n_images + n_groups - 1) / n_groups;
+  std::vector<int> start(n_groups + 1, 0), order(n_pairs);
+  for (int i = 0; i < n_pairs; ++i) ++start[std::max(pairs[2 * i], pairs[2 * i + 1]) / per + 1];
+  for (int g = 0; g < n_groups; ++g) start[g + 1] += start[g];
+  {
+    std::vector<int> fill(start.begin(), start.end() - 1);
+    for (int i = 0; i < n_pairs; ++i) order[fill[std::max(pairs[2 * i], pairs[2 * i + 1]) / per]++] = i;
+  }
+  int max_group = 0;
+  for (int g = 0; g < n_groups; ++g) max_group = std::max(max_group, start[g + 1] - start[g]);
+
   const size_t src_bytes = dtype == VC_DTYPE_BF16 ? 0 : align_up(n_el * el, 256);
   const size_t bf_bytes = align_up(n_el * 2, 256);
   const size_t cnt_bytes = align_up((size_t)n_images * 4, 256);
   const size_t pair_bytes = align_up((size_t)n_pairs * 8, 256);
   const size_t out_bytes = align_up((size_t)n_pairs * kmax * 8, 256);
   const size_t nm_bytes = align_up((size_t)n_pairs * 4, 256);
-  const size_t ws_bytes = vc_match_workspace_bytes(n_pairs, kmax);
-  const size_t total = src_bytes + bf_bytes + cnt_bytes + pair_bytes + out_bytes + nm_bytes + ws_bytes;
+  const size_t off_bytes = align_up((size_t)(n_pairs + n_groups) * 4, 256);
+  const size_t pack_bytes = out_bytes;
+  const size_t ws_bytes = vc_match_workspace_bytes(max_group, kmax);
+  const size_t total =
+      src_bytes + bf_bytes + cnt_bytes + pair_bytes + out_bytes + nm_bytes + off_bytes + pack_bytes + ws_bytes;
   if (h->stage_bytes < total) {
+    VC_CUDA(cudaDeviceSynchronize());
     if (h->stage) cudaFree(h->stage);
     h->stage = nullptr;
     h->stage_bytes = 0;
@@ -304,6 +341,28 @@ int vc_match_pairs_host(vc_handle* h, const void* desc, int dtype, const int32_t
     h->stage_bytes = total;
     h->map_ptr = nullptr;
   }
+  // pinned scratch: sorted pair list, counts and offsets per sorted pair, packed match rows
+  const size_t pin_pairs = align_up((size_t)n_pairs * 8, 256);
+  const size_t pin_small = align_up((size_t)(n_pairs + n_groups) * 4, 256);
+  const size_t pin_total = pin_pairs + 2 * pin_small + out_bytes;
+  if (h->pin_bytes < pin_total) {
+    VC_CUDA(cudaDeviceSynchronize());
+    if (h->pin) cudaFreeHost(h->pin);
+    h->pin = nullptr;
+    h->pin_bytes = 0;
+    VC_CUDA(cudaHostAlloc(&h->pin, pin_total, cudaHostAllocDefault));
+    h->pin_bytes = pin_total;
+  }
+  uint8_t* pin = static_cast<uint8_t*>(h->pin);
+  int32_t* p_pairs = reinterpret_cast<int32_t*>(pin);
+  int32_t* p_nm = reinterpret_cast<int32_t*>(pin + pin_pairs);
+  int32_t* p_off = reinterpret_cast<int32_t*>(pin + pin_pairs + pin_small);
+  uint32_t* p_rows = reinterpret_cast<uint32_t*>(pin + pin_pairs + 2 * pin_small);
+  for (int k = 0; k < n_pairs; ++k) {
+    p_pairs[2 * k] = pairs[2 * order[k]];
+    p_pairs[2 * k + 1] = pairs[2 * order[k] + 1];
+  }
+
   uint8_t* base = static_cast<uint8_t*>(h->stage);
   uint8_t* d_src = base;
   uint8_t* d_bf = d_src + src_bytes;
@@ -311,32 +370,64 @@ int vc_match_pairs_host(vc_handle* h, const void* desc, int dtype, const int32_t
   int32_t* d_pairs = reinterpret_cast<int32_t*>(reinterpret_cast<uint8_t*>(d_cnt) + cnt_bytes);
   uint32_t* d_out = reinterpret_cast<uint32_t*>(reinterpret_cast<uint8_t*>(d_pairs) + pair_bytes);
   int32_t* d_nm = reinterpret_cast<int32_t*>(reinterpret_cast<uint8_t*>(d_out) + out_bytes);
-  void* d_ws = reinterpret_cast<uint8_t*>(d_nm) + nm_bytes;
-  cudaStream_t s = 0;
-  if (dtype == VC_DTYPE_U8) {
-    VC_CUDA(cudaMemcpyAsync(d_src, desc, n_el, cudaMemcpyHostToDevice, s));
-    VC_CUDA(vc::launch_u8_to_bf16(d_src, d_bf, n_el, s));
-    ++g_launches;
-  } else if (dtype == VC_DTYPE_F32) {
-    VC_CUDA(cudaMemcpyAsync(d_src, desc, n_el * 4, cudaMemcpyHostToDevice, s));
-    VC_CUDA(vc::launch_f32_to_bf16(reinterpret_cast<const float*>(d_src), d_bf, n_el, s));
-    ++g_launches;
-  } else {
-    VC_CUDA(cudaMemcpyAsync(d_bf, desc, n_el * 2, cudaMemcpyHostToDevice, s));
-  }
+  int32_t* d_off = reinterpret_cast<int32_t*>(reinterpret_cast<uint8_t*>(d_nm) + nm_bytes);
+  uint32_t* d_pack = reinterpret_cast<uint32_t*>(reinterpret_cast<uint8_t*>(d_off) + off_bytes);
+  void* d_ws = reinterpret_cast<uint8_t*>(d_pack) + pack_bytes;
+
   VC_CUDA(cudaMemcpyAsync(d_cnt, counts, (size_t)n_images * 4, cudaMemcpyHostToDevice, s));
-  VC_CUDA(cudaMemcpyAsync(d_pairs, pairs, (size_t)n_pairs * 8, cudaMemcpyHostToDevice, s));
-  int rc = vc_match_pairs(h, d_bf, d_cnt, n_images, kmax, d, d_pairs, n_pairs, opt, d_out, d_nm, d_ws,
-                          ws_bytes, s);
-  if (rc != VC_OK) return rc;
-  VC_CUDA(cudaMemcpyAsync(n_matches, d_nm, (size_t)n_pairs * 4, cudaMemcpyDeviceToHost, s));
-  VC_CUDA(cudaStreamSynchronize(s));
-  // download only the filled prefix of every pair's slot
-  for (int i = 0; i < n_pairs; ++i) {
-    const int n = n_matches[i];
-    if (n > 0)
-      VC_CUDA(cudaMemcpyAsync(matches + (size_t)i * kmax * 2, d_out + (size_t)i * kmax * 2,
-                              (size_t)n * 8, cudaMemcpyDeviceToHost, s));
+  VC_CUDA(cudaMemcpyAsync(d_pairs, p_pairs, (size_t)n_pairs * 8, cudaMemcpyHostToDevice, s));
+  for (int g = 0; g < n_groups; ++g) {
+    const int i0 = std::min(n_images, g * per), i1 = std::min(n_images, (g + 1) * per);
+    const size_t off = (size_t)i0 * img_el, cnt = (size_t)(i1 - i0) * img_el;
+    if (cnt) {
+      uint8_t* dst = dtype == VC_DTYPE_BF16 ? d_bf : d_src;
+      VC_CUDA(cudaMemcpyAsync(dst + off * el, static_cast<const uint8_t*>(desc) + off * el, cnt * el,
+                              cudaMemcpyHostToDevice, s_up));
+    }
+    VC_CUDA(cudaEventRecord(h->host_events[g], s_up));
+    VC_CUDA(cudaStreamWaitEvent(s, h->host_events[g], 0));
+    if (cnt && dtype == VC_DTYPE_U8) {
+      VC_CUDA(vc::launch_u8_to_bf16(d_src + off, d_bf + off * 2, cnt, s));
+      ++g_launches;
+    } else if (cnt && dtype == VC_DTYPE_F32) {
+      VC_CUDA(vc::launch_f32_to_bf16(reinterpret_cast<const float*>(d_src) + off, d_bf + off * 2, cnt, s));
+      ++g_launches;
+    }
+    const int p0 = start[g], np = start[g + 1] - start[g];
+    if (np > 0) {
+      int rc = vc_match_pairs(h, d_bf, d_cnt, n_images, kmax, d, d_pairs + 2 * (size_t)p0, np, opt,
+                              d_out + (size_t)p0 * kmax * 2, d_nm + p0, d_ws, ws_bytes, s);
+      if (rc != VC_OK) {
+        cudaDeviceSynchronize();
+        return rc;
+      }
+      VC_CUDA(vc::launch_compact_matches(d_out + (size_t)p0 * kmax * 2, d_nm + p0, np, kmax, d_off + p0 + g,
+                                         d_pack + (size_t)p0 * kmax * 2, s));
+      g_launches += 2;
+    }
+    VC_CUDA(cudaEventRecord(h->host_events[8 + g], s));
+  }
+  // read-back, group by group, while later groups are still being matched
+  for (int g = 0; g < n_groups; ++g) {
+    const int p0 = start[g], np = start[g + 1] - start[g];
+    if (np == 0) continue;
+    VC_CUDA(cudaStreamWaitEvent(s_down, h->host_events[8 + g], 0));
+    VC_CUDA(cudaMemcpyAsync(p_nm + p0, d_nm + p0, (size_t)np * 4, cudaMemcpyDeviceToHost, s_down));
+    VC_CUDA(cudaMemcpyAsync(p_off + p0 + g, d_off + p0 + g, (size_t)(np + 1) * 4, cudaMemcpyDeviceToHost, s_down));
+    VC_CUDA(cudaStreamSynchronize(s_down));
+    const int32_t* off = p_off + p0 + g;
+    const size_t rows = (size_t)off[np];
+    uint32_t* host_rows = p_rows + (size_t)p0 * kmax * 2;
+    if (rows) {
+      VC_CUDA(cudaMemcpyAsync(host_rows, d_pack + (size_t)p0 * kmax * 2, rows * 8, cudaMemcpyDeviceToHost, s_down));
+      VC_CUDA(cudaStreamSynchronize(s_down));
+    }
+    for (int k = 0; k < np; ++k) {
+      const int orig = order[p0 + k];
+      const int n = p_nm[p0 + k];
+      n_matches[orig] = n;
+      if (n > 0) std::memcpy(matches + (size_t)orig * kmax * 2, host_rows + (size_t)off[k] * 2, (size_t)n * 8);
+    }
   }
   VC_CUDA(cudaStreamSynchronize(s));
   return VC_OK;

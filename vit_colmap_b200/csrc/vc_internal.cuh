@@ -42,4 +42,9 @@ struct vc_handle {
   // device staging owned by the host-buffer entry point
   void* stage = nullptr;
   size_t stage_bytes = 0;
+  // streams / events / pinned scratch of the host-buffer entry point (created on first use)
+  cudaStream_t host_streams[3] = {nullptr, nullptr, nullptr};  // compute, upload, download
+  cudaEvent_t host_events[16] = {};                           // [0..7] chunk uploaded, [8..15] group matched
+  void* pin = nullptr;
+  size_t pin_bytes = 0;
 };
