@@ -98,6 +98,8 @@ def _compare_with_oracle(matcher, desc, counts, pairs, max_ratio, max_distance, 
     (300, 64, [300, 129, 1, 0]),       # ragged, single row, empty image
     (1000, 384, [1000, 777, 513]),
     (2048, 768, [2048, 2047, 1739]),   # north-star d; 1739 = reference keypoint yield at DTU size
+    (1100, 1024, [1100, 1025, 640]),   # ViT-L width: the two-SM (cta_group::2) kernel; odd row-tile counts
+    (700, 1024, [700, 100, 129]),      # two-SM kernel with a single row tile (second CTA of the pair idles)
 ])
 def test_match_pairs_float_mode(matcher, kmax, d, counts):
     rng = np.random.default_rng(kmax + d)

@@ -15,7 +15,14 @@ ROOT = Path(__file__).resolve().parent.parent
 sys.path.insert(0, str(ROOT))
 
 
+ONCE = "--once" in sys.argv   # one launch per stage, for an ncu capture
+if ONCE:
+    sys.argv.remove("--once")
+
+
 def timed(fn, iters=20, warm=3, flush=None):
+    if ONCE:
+        iters, warm = 1, 0
     for _ in range(warm):
         fn()
     ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(iters)]

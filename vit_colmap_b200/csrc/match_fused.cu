@@ -27,7 +27,12 @@ namespace {
 
 constexpr int BM = 128, BN = 256, BK = 64, kStages = 4;
 constexpr int kABytes = BM * BK * 2, kBBytes = BN * BK * 2, kStageBytes = kABytes + kBBytes;
-constexpr int kThreads = 384;  // warp0 TMA, warp1 MMA, warp2 TMEM alloc, warps 4-11 epilogue
+// warp0 TMA, warp1 MMA, warp2 TMEM alloc, warps 4-15 epilogue: three warps per TMEM lane quarter, each
+// on 3 / 3 / 2 of the tile's eight 32-column chunks (the epilogue, not the MMA, paced the kernel with
+// two warps per quarter: profiles/r01_v8_match_fused_ncu_summary.json)
+constexpr int kEpiGroups = 3;
+constexpr int kEpiThreads = kEpiGroups * 128;
+constexpr int kThreads = 128 + kEpiThreads;
 constexpr int kTmemCols = 512;
 constexpr int kColStateBytes = BN * 8 + BN * 4;
 constexpr int kSmemBytes = kStages * kStageBytes + 1024 + 256 + kColStateBytes;
@@ -49,11 +54,11 @@ __device__ __forceinline__ FItem decode_fitem(const MatchParams& p, int item) {
   it.valid = it.cb * BN < it.n2 && it.nrt > 0;
   // stagger the sweep so CTAs on different column blocks of a pair sit on different row tiles:
   // their published hints are then useful to each other
-  it.start = it.nrt > 0 ? (it.cb * 2) % it.nrt : 0;
+  it.start = it.nrt > 0 ? (it.cb * p.stagger) % it.nrt : 0;
   return it;
 }
 
-__device__ __forceinline__ void epi_bar_sync() { asm volatile("bar.sync 1, 256;" ::: "memory"); }
+__device__ __forceinline__ void epi_bar_sync() { asm volatile("bar.sync 1, %0;" ::"n"(kEpiThreads) : "memory"); }
 
 }  // namespace
 
@@ -87,7 +92,7 @@ match_fused_kernel(const __grid_constant__ CUtensorMap tmap, const MatchParams p
     }
     for (int s = 0; s < 2; ++s) {
       mbar_init(tfull_bar(s), 1);
-      mbar_init(tempty_bar(s), 256);
+      mbar_init(tempty_bar(s), kEpiThreads);
     }
     fence_mbar_init();
   }
@@ -153,22 +158,24 @@ match_fused_kernel(const __grid_constant__ CUtensorMap tmap, const MatchParams p
       }
     }
   } else if (warp >= 4) {
-    // ------------------------------------------------------------ epilogue (8 warps)
-    // warp -> TMEM lane quarter q = warp % 4 (hardware rule) and column half h of the tile
+    // ------------------------------------------------------------ epilogue (12 warps)
+    // warp -> TMEM lane quarter q = warp % 4 (hardware rule) and column group h of the tile
     const int q = warp & 3;
     const int h = (warp - 4) >> 2;
-    const int et = threadIdx.x - 128;  // 0..255
+    const int et = threadIdx.x - 128;  // 0..kEpiThreads-1
     uint32_t tile = 0;
     for (int item = blockIdx.x; item < p.n_items; item += gridDim.x) {
       const FItem it = decode_fitem(p, item);
       if (!it.valid) continue;
-      colkey[et] = 0ull;
-      colsec[et] = 0u;
+      if (et < BN) {
+        colkey[et] = 0ull;
+        colsec[et] = 0u;
+      }
       epi_bar_sync();
       const int ncols = min(BN, it.n2 - it.cb * BN);  // valid columns of this block
-      // this warp's chunks: columns [h*128, h*128+128) of the block, 32 per chunk
-      const int c_begin = h * 4;
-      const int c_end = min(c_begin + 4, (ncols + 31) >> 5);
+      // this warp's chunks (32 columns each): group 0 -> 0..2, group 1 -> 3..5, group 2 -> 6..7
+      const int c_begin = h * 3;
+      const int c_end = min(min(c_begin + 3, BN / 32), (ncols + 31) >> 5);
       const size_t pair_row0 = (size_t)it.pair * p.kmax;
       for (int s = 0; s < it.nrt; ++s, ++tile) {
         int rt = it.start + s;
@@ -268,7 +275,7 @@ match_fused_kernel(const __grid_constant__ CUtensorMap tmap, const MatchParams p
         tc_fence_before();
         mbar_arrive(tempty_bar(as));
         if (row_ok) {
-          const size_t o = ((size_t)it.pair * p.cb_per_img * 2 + it.cb * 2 + h) * p.kmax + row;
+          const size_t o = ((size_t)it.pair * p.cb_per_img * kEpiGroups + it.cb * kEpiGroups + h) * p.kmax + row;
           p.part_best[o] = best;
           p.part_second[o] = second;
           p.part_idx[o] = bidx;
@@ -307,11 +314,11 @@ __global__ void merge_rows_kernel(const MatchParams p) {
   const int i0 = p.pairs[2 * pair], i1 = p.pairs[2 * pair + 1];
   const int n1 = min(p.counts[i0], p.kmax), n2 = min(p.counts[i1], p.kmax);
   if (row >= n1) return;
-  const int nparts = (n2 + 127) / 128;  // one partial per 128 columns (epilogue warp half)
+  const int nparts = ((n2 + BN - 1) / BN) * kEpiGroups;  // one partial per (column block, epilogue column group)
   float best = 0.f, second = 0.f;
   int idx = -1;
   for (int cb = 0; cb < nparts; ++cb) {
-    const size_t o = ((size_t)pair * p.cb_per_img * 2 + cb) * p.kmax + row;
+    const size_t o = ((size_t)pair * p.cb_per_img * kEpiGroups + cb) * p.kmax + row;
     const float pb = p.part_best[o], ps = p.part_second[o];
     const int pi = p.part_idx[o];
     if (pi < 0) continue;

@@ -28,6 +28,9 @@ struct MatchParams {
   int dbg_ld;
   // single-pass kernel (match_fused.cu) only
   int cb_per_img;         // ceil(kmax / 256)
+  unsigned long long* col_key;  // two-SM kernel: [n_pairs, 2 (cta rank), kmax] column states
+  unsigned int* col_sec;
+  int stagger;            // row-tile offset per column block (0 = every CTA of a pair sweeps in the same order)
   unsigned int* rowthr;   // [n_pairs, kmax] float bits: lower bound of each row's final second-best
   float* part_best;       // [n_pairs, 2*cb_per_img, kmax] row partials, one per 128 columns
   float* part_second;
@@ -60,6 +63,9 @@ int match_fused_smem_bytes();
 // memset(rowthr) + fused kernel + row-partial merge; n_items must be n_pairs * cb_per_img
 cudaError_t launch_match_fused(const CUtensorMap& tmap, const MatchParams& p, int num_sms,
                                cudaStream_t stream);
+// two-SM (cta_group::2) variant, match_fused2.cu: + merge of the two CTAs' column states
+cudaError_t launch_match_fused2(const CUtensorMap& tmap, const MatchParams& p, int num_sms,
+                                cudaStream_t stream);
 cudaError_t launch_emit_matches(const MatchParams& p, uint32_t* matches, int32_t* n_matches,
                                 cudaStream_t stream);
 // Packs the filled prefix of every pair's [kmax, 2] slot into one dense [total, 2] list (offsets =

@@ -72,8 +72,12 @@ size_t m_out_bytes(int n_pairs, int kmax) {
   return align_up((size_t)n_pairs * 2 * (size_t)kmax * sizeof(int32_t), 256);
 }
 size_t rowthr_bytes(int n_pairs, int kmax) { return align_up((size_t)n_pairs * kmax * 4, 256); }
+size_t colstate_bytes(int n_pairs, int kmax) {  // two-SM kernel: u64 key + u32 second per (pair, rank, column)
+  return align_up((size_t)n_pairs * 2 * kmax * 8, 256) + align_up((size_t)n_pairs * 2 * kmax * 4, 256);
+}
 size_t part_bytes(int n_pairs, int kmax) {
-  return align_up((size_t)n_pairs * 2 * ((kmax + 255) / 256) * (size_t)kmax * 4, 256);
+  // row partials: one per (column block, epilogue column group); up to 3 groups per 256-column block
+  return align_up((size_t)n_pairs * 3 * ((kmax + 255) / 256) * (size_t)kmax * 4, 256);
 }
 
 // Kernel choice: the single-pass kernel halves the tensor work but has a heavier epilogue, which
@@ -173,7 +177,8 @@ int vc_destroy(vc_handle* h) {
 
 size_t vc_match_workspace_bytes(int n_pairs, int kmax) {
   if (n_pairs <= 0 || kmax <= 0) return 256;
-  return m_out_bytes(n_pairs, kmax) + rowthr_bytes(n_pairs, kmax) + 3 * part_bytes(n_pairs, kmax);
+  return m_out_bytes(n_pairs, kmax) + rowthr_bytes(n_pairs, kmax) + 3 * part_bytes(n_pairs, kmax) +
+         colstate_bytes(n_pairs, kmax);
 }
 
 static int match_impl(vc_handle* h, const void* desc, const int32_t* counts, int n_images, int kmax,
@@ -206,8 +211,29 @@ static int match_impl(vc_handle* h, const void* desc, const int32_t* counts, int
     p.part_idx = reinterpret_cast<int32_t*>(w);
     p.cb_per_img = (kmax + 255) / 256;
     p.n_items = n_pairs * p.cb_per_img;
-    VC_CUDA(vc::launch_match_fused(h->map, p, h->num_sms, s));
-    g_launches += 2;
+    static const int stagger = [] {
+      const char* e = getenv("VC_MATCH_STAGGER");
+      return e ? atoi(e) : 2;
+    }();
+    p.stagger = stagger;
+    w += part_bytes(n_pairs, kmax);
+    p.col_key = reinterpret_cast<unsigned long long*>(w);
+    p.col_sec = reinterpret_cast<unsigned int*>(w + align_up((size_t)n_pairs * 2 * kmax * 8, 256));
+    // two-SM kernel (cta_group::2): a third less L2->SM operand traffic, but its accumulator hand-over
+    // spans two CTAs.  Measured on B200 at 8192 x 8192 (tools/time_match_dims.py): d=768 92.6 vs 86.8
+    // us/pair, d=1024 116.7 vs 131.4 us/pair -> used from d >= 1024.  VC_MATCH_2CTA=0/1 forces a choice.
+    static const int two_sm_env = [] {
+      const char* e = getenv("VC_MATCH_2CTA");
+      return e ? atoi(e) : -1;
+    }();
+    const bool two_sm = two_sm_env >= 0 ? two_sm_env != 0 : d >= 1024;
+    if (two_sm) {
+      VC_CUDA(vc::launch_match_fused2(h->map, p, h->num_sms, s));
+      g_launches += 3;
+    } else {
+      VC_CUDA(vc::launch_match_fused(h->map, p, h->num_sms, s));
+      g_launches += 2;
+    }
   } else {
     VC_CUDA(vc::launch_match_top2(h->map, p, h->num_sms, false, s));
     ++g_launches;
