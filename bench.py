@@ -29,7 +29,7 @@ UNIT = "pairs/s"
 N_IMAGES, KPTS, DIM = 32, 8192, 768
 FLOP_PER_PAIR = 2.0 * KPTS * KPTS * DIM  # 2*N*M*d
 # dram__bytes_read.sum + dram__bytes_write.sum of one match_fused_kernel launch (496 pairs), ncu --set full
-NCU_TRAFFIC_BYTES = 8.593394e9 + 3.149852e9
+NCU_TRAFFIC_BYTES = 8.972257e9 + 3.153844e9
 
 
 def _peaks():
@@ -116,11 +116,16 @@ def all_pairs(n):
 
 
 # ------------------------------------------------------------------------------------------- CPU
+def _host_cores() -> int:
+    return len(os.sched_getaffinity(0)) if hasattr(os, "sched_getaffinity") else (os.cpu_count() or 1)
+
+
 def cpu_sample(seconds_target: float = 12.0, seed: int = 0):
     """Reference CPU path (oracle port of COLMAP/feature/sift.cc:733-825,922-971) on a bounded
     sample of the same workload: R rows of image 1 against all 8192 rows of image 2, d=768,
     float32 SIMD dot products, OpenMP over all host threads."""
     from oracle import matching as om
+    om.set_num_threads(_host_cores())  # launchers such as torchrun export OMP_NUM_THREADS=1
     rng = np.random.default_rng(seed)
     a = rng.standard_normal((KPTS, DIM)).astype(np.float32)
     a /= np.linalg.norm(a, axis=1, keepdims=True)
@@ -143,6 +148,9 @@ def run_reference(args):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
+    # torchrun exports OMP_NUM_THREADS=1; the reference arm uses every host core the box has
+    import torch
+    torch.set_num_threads(_host_cores())
     vals, rows_used = [], 0
     per_step = max(2.0, min(12.0, 90.0 / max(args.steps + args.warmup, 1)))
     for i in range(args.warmup + args.steps):
@@ -316,7 +324,8 @@ def run_ours(args):
                          "kernel": "match_fused_kernel", "kernel_ms": kern_ms,
                          "note": "achieved = 2*N*M*d per pair (one MMA sweep gives row and column top-2) "
                                  "over the top-2 stage (memset + fused kernel + row-partial merge); traffic "
-                                 "from profiles/r01_v2_fused_ncu_summary.json (dram read+write per launch)"},
+                                 "from profiles/r01_v8_match_fused_ncu_summary.json (dram read+write per launch, captured before "
+                                 "the 12-warp epilogue, which adds 1.6 GB of row-partial writes per launch)"},
             "clocks": clocks,
         }
         if extract is not None:
@@ -512,6 +521,7 @@ def cpu_extract_sample(n_images=2):
     import torch
     from oracle import extract_oracle as eo
     from oracle import vit_oracle as vo
+    torch.set_num_threads(_host_cores())
     sd = vo.synthetic_state_dict(EXTRACT_MODEL, 0)
     rng = np.random.default_rng(0)
     t0 = time.perf_counter()

@@ -264,6 +264,15 @@ int64_t vc_oracle_pair_id(uint32_t id1, uint32_t id2) {
   return kMaxNumImages * (int64_t)id1 + (int64_t)id2;
 }
 
+/* Launchers such as torchrun export OMP_NUM_THREADS=1; the timed CPU baseline asks for all cores. */
+void vc_oracle_set_num_threads(int n) {
+#ifdef _OPENMP
+  if (n > 0) omp_set_num_threads(n);
+#else
+  (void)n;
+#endif
+}
+
 int vc_oracle_num_threads(void) {
 #ifdef _OPENMP
   return omp_get_max_threads();

@@ -55,8 +55,14 @@ def _load():
         lib.vc_oracle_pair_id.restype = ctypes.c_int64
         lib.vc_oracle_pair_id.argtypes = [ctypes.c_uint32, ctypes.c_uint32]
         lib.vc_oracle_num_threads.restype = ctypes.c_int
+        lib.vc_oracle_set_num_threads.argtypes = [ctypes.c_int]
+        lib.vc_oracle_set_num_threads.restype = None
         _lib = lib
     return _lib
+
+
+def set_num_threads(n: int) -> None:
+    _load().vc_oracle_set_num_threads(int(n))
 
 
 def num_threads() -> int:
