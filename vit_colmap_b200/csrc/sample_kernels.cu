@@ -146,7 +146,9 @@ __device__ __forceinline__ void zero_row(const SampleParams& p, size_t kp, int l
   if (lane == 0 && p.keypoints) reinterpret_cast<float2*>(p.keypoints)[kp] = make_float2(0.f, 0.f);
 }
 
-template <typename T>
+// KV = float4 slots per lane = ceil(C / 128): sized to the channel count so that no dead accumulator
+// registers limit the occupancy of this bandwidth-bound kernel.
+template <typename T, int KV>
 __global__ void __launch_bounds__(256) sample_pack_direct(const SampleParams p) {
   const int lane = threadIdx.x & 31;
   const long long wg = ((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
@@ -162,16 +164,16 @@ __global__ void __launch_bounds__(256) sample_pack_direct(const SampleParams p) 
   const Taps t = make_taps(fy, fx, p.H, p.W);
   const T* img = static_cast<const T*>(p.tokens) + (int64_t)b * p.image_stride;
   const int nvec = p.C >> 2;
-  float4 acc[kVec];
+  float4 acc[KV];
 #pragma unroll
-  for (int j = 0; j < kVec; ++j) acc[j] = make_float4(0, 0, 0, 0);
+  for (int j = 0; j < KV; ++j) acc[j] = make_float4(0, 0, 0, 0);
 #pragma unroll
   for (int s = 0; s < 4; ++s) {
     if (t.idx[s] < 0) continue;  // warp-uniform
     const T* row = img + (size_t)t.idx[s] * p.C;
     const float w = t.w[s];
 #pragma unroll
-    for (int j = 0; j < kVec; ++j) {
+    for (int j = 0; j < KV; ++j) {
       const int v = lane + 32 * j;
       if (v < nvec) {
         const float4 x = ld4(row, v);
@@ -185,11 +187,11 @@ __global__ void __launch_bounds__(256) sample_pack_direct(const SampleParams p) 
   if (p.rootsift) {
     float l1 = 0.f;
 #pragma unroll
-    for (int j = 0; j < kVec; ++j)
+    for (int j = 0; j < KV; ++j)
       if (lane + 32 * j < nvec) l1 += fabsf(acc[j].x) + fabsf(acc[j].y) + fabsf(acc[j].z) + fabsf(acc[j].w);
     const float den1 = fmaxf(warp_sum(l1), 1e-12f);
 #pragma unroll
-    for (int j = 0; j < kVec; ++j) {
+    for (int j = 0; j < KV; ++j) {
       if (lane + 32 * j < nvec) {
         acc[j].x = rootsift(acc[j].x, den1);
         acc[j].y = rootsift(acc[j].y, den1);
@@ -200,12 +202,12 @@ __global__ void __launch_bounds__(256) sample_pack_direct(const SampleParams p) 
   }
   float ss = 0.f;
 #pragma unroll
-  for (int j = 0; j < kVec; ++j)
+  for (int j = 0; j < KV; ++j)
     ss += acc[j].x * acc[j].x + acc[j].y * acc[j].y + acc[j].z * acc[j].z + acc[j].w * acc[j].w;
   ss = warp_sum(ss);
   const float den = fmaxf(sqrtf(ss), p.norm_eps);  // F.normalize eps
 #pragma unroll
-  for (int j = 0; j < kVec; ++j) {
+  for (int j = 0; j < KV; ++j) {
     const int v = lane + 32 * j;
     if (v < nvec) {
       float4 o;
@@ -344,10 +346,21 @@ cudaError_t launch_sample_pack(const SampleParams& p, cudaStream_t stream) {
     const long long warps = (long long)p.B * p.cap;
     const int blocks = (int)((warps * 32 + 255) / 256);
     if (blocks == 0) return cudaSuccess;
-    if (p.is_bf16)
-      sample_pack_direct<__nv_bfloat16><<<blocks, 256, 0, stream>>>(p);
-    else
-      sample_pack_direct<float><<<blocks, 256, 0, stream>>>(p);
+    const int kv = (p.C / 4 + 31) / 32;
+#define VC_LAUNCH_DIRECT(KV)                                                    \
+  do {                                                                          \
+    if (p.is_bf16)                                                              \
+      sample_pack_direct<__nv_bfloat16, KV><<<blocks, 256, 0, stream>>>(p);     \
+    else                                                                        \
+      sample_pack_direct<float, KV><<<blocks, 256, 0, stream>>>(p);             \
+  } while (0)
+    if (kv <= 1) VC_LAUNCH_DIRECT(1);
+    else if (kv <= 2) VC_LAUNCH_DIRECT(2);
+    else if (kv <= 3) VC_LAUNCH_DIRECT(3);
+    else if (kv <= 4) VC_LAUNCH_DIRECT(4);
+    else if (kv <= 6) VC_LAUNCH_DIRECT(6);
+    else VC_LAUNCH_DIRECT(8);
+#undef VC_LAUNCH_DIRECT
     return cudaGetLastError();
   }
   const int smem = (p.C * kTile + kTile * p.d) * (int)sizeof(float);

@@ -40,7 +40,7 @@ __device__ __forceinline__ float warp_sum(float v) {
   return v;
 }
 
-template <typename T>
+template <typename T, int KV>  // KV = ceil(C / 128) float4 slots per lane
 __global__ void __launch_bounds__(256)
 moments_kernel(const T* __restrict__ tokens, int64_t image_stride, int B, int H, int W, int C,
                float* __restrict__ moments) {
@@ -60,9 +60,9 @@ moments_kernel(const T* __restrict__ tokens, int64_t image_stride, int B, int H,
   float* mom = moments + (size_t)b * 4 * plane;
   const float inv_c = 1.0f / (float)C;
 
-  float4 cur[kVec], nxt[kVec];
+  float4 cur[KV], nxt[KV];
 #pragma unroll
-  for (int k = 0; k < kVec; ++k) {
+  for (int k = 0; k < KV; ++k) {
     const int v = lane + 32 * k;
     cur[k] = v < nvec ? ld4(img + (size_t)(y * W + x0) * C, v) : make_float4(0, 0, 0, 0);
   }
@@ -72,7 +72,7 @@ moments_kernel(const T* __restrict__ tokens, int64_t image_stride, int B, int H,
     const T* row_d = img + (size_t)((y + 1) * W + x) * C;
     float sxx = 0.f, syy = 0.f, sxy = 0.f, sav = 0.f;
 #pragma unroll
-    for (int k = 0; k < kVec; ++k) {
+    for (int k = 0; k < KV; ++k) {
       const int v = lane + 32 * k;
       const bool ok = v < nvec;
       const float4 c = cur[k];
@@ -99,7 +99,7 @@ moments_kernel(const T* __restrict__ tokens, int64_t image_stride, int B, int H,
       mom[3 * plane + o] = sav * inv_c;
     }
 #pragma unroll
-    for (int k = 0; k < kVec; ++k) cur[k] = nxt[k];
+    for (int k = 0; k < KV; ++k) cur[k] = nxt[k];
   }
 }
 
@@ -230,12 +230,23 @@ cudaError_t launch_score_map(const ScoreParams& p, cudaStream_t stream) {
   const int strips = (p.W + kStrip - 1) / kStrip;
   const long long warps = (long long)p.B * p.H * strips;
   const int blocks = (int)((warps * 32 + 255) / 256);
-  if (p.is_bf16)
-    moments_kernel<__nv_bfloat16><<<blocks, 256, 0, stream>>>(
-        static_cast<const __nv_bfloat16*>(p.tokens), p.image_stride, p.B, p.H, p.W, p.C, p.moments);
-  else
-    moments_kernel<float><<<blocks, 256, 0, stream>>>(static_cast<const float*>(p.tokens),
-                                                      p.image_stride, p.B, p.H, p.W, p.C, p.moments);
+  const int kv = (p.C / 4 + 31) / 32;
+#define VC_LAUNCH_MOMENTS(KV)                                                                          \
+  do {                                                                                                 \
+    if (p.is_bf16)                                                                                     \
+      moments_kernel<__nv_bfloat16, KV><<<blocks, 256, 0, stream>>>(                                   \
+          static_cast<const __nv_bfloat16*>(p.tokens), p.image_stride, p.B, p.H, p.W, p.C, p.moments); \
+    else                                                                                               \
+      moments_kernel<float, KV><<<blocks, 256, 0, stream>>>(static_cast<const float*>(p.tokens),       \
+                                                            p.image_stride, p.B, p.H, p.W, p.C, p.moments); \
+  } while (0)
+  if (kv <= 1) VC_LAUNCH_MOMENTS(1);
+  else if (kv <= 2) VC_LAUNCH_MOMENTS(2);
+  else if (kv <= 3) VC_LAUNCH_MOMENTS(3);
+  else if (kv <= 4) VC_LAUNCH_MOMENTS(4);
+  else if (kv <= 6) VC_LAUNCH_MOMENTS(6);
+  else VC_LAUNCH_MOMENTS(8);
+#undef VC_LAUNCH_MOMENTS
   cudaError_t e = cudaGetLastError();
   if (e != cudaSuccess) return e;
   const int smem = (p.method == 0) ? 0 : p.H * p.W * (int)sizeof(float);
