@@ -321,9 +321,9 @@ def run_ours(args):
             "roofline": {"bound": "tensor", "achieved": achieved_tf, "peak": peak_tf, "unit": "TFLOP/s",
                          "frac": achieved_tf / peak_tf, "traffic": NCU_TRAFFIC_BYTES,
                          "peak_source": f"{peak_src} sustained bf16",
-                         "kernel": "match_fused_kernel", "kernel_ms": kern_ms,
+                         "kernel": "match_fused2_kernel (two-SM cta_group::2 form of match_fused_kernel)", "kernel_ms": kern_ms,
                          "note": "achieved = 2*N*M*d per pair (one MMA sweep gives row and column top-2) "
-                                 "over the top-2 stage (memset + fused kernel + row-partial merge); traffic "
+                                 "over the top-2 stage (memset + fused kernel + row / column partial merges); traffic "
                                  "from profiles/r01_v8_match_fused_ncu_summary.json (dram read+write per launch, captured before "
                                  "the 12-warp epilogue, which adds 1.6 GB of row-partial writes per launch)"},
             "clocks": clocks,

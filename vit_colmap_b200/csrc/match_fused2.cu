@@ -253,7 +253,7 @@ match_fused2_kernel(const __grid_constant__ CUtensorMap tmap, const MatchParams 
       if (!it.valid) continue;
       if (et < BN) {
         colkey[et] = 0ull;
-        colsec[et] = 0u;
+        colsec[et] = __float_as_uint(p.prune);  // scores at or below the bound never reach the column state
       }
       epi_bar_sync();
       const int ncols = min(BN, it.n2 - it.cb * BN);  // valid columns of this block
@@ -269,7 +269,7 @@ match_fused2_kernel(const __grid_constant__ CUtensorMap tmap, const MatchParams 
         const bool row_ok = row < it.n1;
         // hint: lower bound of this row's final second-best (L2 load, may be stale)
         float thr = 0.f;
-        if (row_ok) thr = __uint_as_float(__ldcg(p.rowthr + pair_row0 + row));
+        if (row_ok) thr = fmaxf(p.prune, __uint_as_float(__ldcg(p.rowthr + pair_row0 + row)));
         const unsigned long long row_tag = 0xFFFFFFFFu - (unsigned)row;
         float best = 0.f, second = 0.f;
         int bidx = -1;

@@ -30,6 +30,7 @@ struct MatchParams {
   int cb_per_img;         // ceil(kmax / 256)
   unsigned long long* col_key;  // two-SM kernel: [n_pairs, 2 (cta rank), kmax] column states
   unsigned int* col_sec;
+  float prune;            // raw-score bound below which a score can change no accept / reject decision (0 = off)
   int stagger;            // row-tile offset per column block (0 = every CTA of a pair sweeps in the same order)
   unsigned int* rowthr;   // [n_pairs, kmax] float bits: lower bound of each row's final second-best
   float* part_best;       // [n_pairs, 2*cb_per_img, kmax] row partials, one per 128 columns

@@ -4,6 +4,7 @@
 #include "../../include/vc_b200.h"
 
 #include <algorithm>
+#include <cmath>
 #include <cstdarg>
 #include <cstdio>
 #include <cstdlib>
@@ -211,6 +212,19 @@ static int match_impl(vc_handle* h, const void* desc, const int32_t* counts, int
     p.part_idx = reinterpret_cast<int32_t*>(w);
     p.cb_per_img = (kmax + 255) / 256;
     p.n_items = n_pairs * p.cb_per_img;
+    // Exact pruning bound (angular rule, match lists only): a score s with acos(inv_norm * s) >
+    // max_distance / max_ratio can neither be the best of an accepted match (distance test,
+    // sift.cc:765-771) nor, as second-best, make the ratio test fail for one (t1 <= max_distance <
+    // max_ratio * t2, sift.cc:773-780), so the epilogue never has to track it.  The diagnostics entry
+    // (vc_match_pairs_top2) keeps the bound at 0 and returns exact top-2 values for every row.
+    p.prune = 0.f;
+    if (opt->rule == 0 && best == nullptr && opt->max_ratio > 0.f && opt->inv_norm > 0.f && !getenv("VC_MATCH_NO_PRUNE")) {
+      const double a = std::max((double)opt->max_distance / (double)opt->max_ratio, (double)opt->max_distance);
+      if (a < 1.5707) {
+        const double c = cos(a) - 1e-3;
+        if (c > 0.0) p.prune = (float)(c / (double)opt->inv_norm);
+      }
+    }
     static const int stagger = [] {
       const char* e = getenv("VC_MATCH_STAGGER");
       return e ? atoi(e) : 2;
@@ -220,13 +234,14 @@ static int match_impl(vc_handle* h, const void* desc, const int32_t* counts, int
     p.col_key = reinterpret_cast<unsigned long long*>(w);
     p.col_sec = reinterpret_cast<unsigned int*>(w + align_up((size_t)n_pairs * 2 * kmax * 8, 256));
     // two-SM kernel (cta_group::2): a third less L2->SM operand traffic, but its accumulator hand-over
-    // spans two CTAs.  Measured on B200 at 8192 x 8192 (tools/time_match_dims.py): d=768 92.6 vs 86.8
-    // us/pair, d=1024 116.7 vs 131.4 us/pair -> used from d >= 1024.  VC_MATCH_2CTA=0/1 forces a choice.
+    // spans two CTAs.  Measured on B200 at 8192 x 8192 with the pruning bound above
+    // (tools/time_match_dims.py, us/pair, single-CTA vs two-SM): d=384 40.3 vs 41.5, d=768 83.4 vs 79.3,
+    // d=1024 138.5 vs 102.2 -> used from d >= 768.  VC_MATCH_2CTA=0/1 forces a choice.
     static const int two_sm_env = [] {
       const char* e = getenv("VC_MATCH_2CTA");
       return e ? atoi(e) : -1;
     }();
-    const bool two_sm = two_sm_env >= 0 ? two_sm_env != 0 : d >= 1024;
+    const bool two_sm = two_sm_env >= 0 ? two_sm_env != 0 : d >= 768;
     if (two_sm) {
       VC_CUDA(vc::launch_match_fused2(h->map, p, h->num_sms, s));
       g_launches += 3;
