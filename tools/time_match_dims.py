@@ -16,7 +16,7 @@ m = Matcher(0)
 pairs = torch.tensor([(i, j) for i in range(n_img) for j in range(i + 1, n_img)], dtype=torch.int32, device="cuda")
 counts = torch.full((n_img,), K, dtype=torch.int32, device="cuda")
 opt = m._opts(0.8, 0.7, True, 1.0)
-for d in (128, 256, 384, 768, 1024):
+for d in (64, 128, 256, 384, 768, 1024):
     g = torch.Generator(device="cuda").manual_seed(d)
     x = torch.randn((n_img, K, d), device="cuda", generator=g)
     x = (x / x.norm(dim=2, keepdim=True)).to(torch.bfloat16)
