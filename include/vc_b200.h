@@ -80,6 +80,11 @@ size_t vc_match_workspace_bytes(int n_pairs, int kmax);
  * sift.cc:922-971); replaces SiftMatchGPU::GetSiftMatch (SIFTGPU/SiftMatchCU.cpp:161-199) and
  * the kernels SIFTGPU/ProgramCU.cu:1411-1495,1696-1797.  The N x M score matrix stays in
  * tensor memory; only (best, second, index) per row/column reaches HBM.
+ * Under the angular rule the epilogue does not track scores with acos(inv_norm * s) >
+ * max_distance / max_ratio: they can change no accept / reject decision of sift.cc:765-780, so the
+ * match lists are identical (vc_match_pairs_top2 returns exact values for every row regardless).
+ * Environment overrides for comparisons: VC_MATCH_KERNEL=dual|fused, VC_MATCH_2CTA=0|1 (two-SM
+ * cta_group::2 kernel, default from d >= 768), VC_MATCH_NO_PRUNE=1.
  */
 int vc_match_pairs(vc_handle* h, const void* desc, const int32_t* counts, int n_images, int kmax,
                    int d, const int32_t* pairs, int n_pairs, const vc_match_options* opt,
