@@ -75,36 +75,62 @@ layernorm_kernel(const float* __restrict__ x, const float* __restrict__ w, const
   }
 }
 
+// One thread produces 8 consecutive bf16 of a patch row (one 16-byte store).  The per-channel
+// ToTensor + Normalize value of every byte, (u / 255 - mean) / std in the reference's fp32 order
+// (vit_extractor.py:117-132), comes from a 3 x 256 table built once per CTA, so the result is bit-identical
+// to evaluating the two divisions per element.
 __global__ void __launch_bounds__(256)
 patchify_kernel(const uint8_t* __restrict__ images, int B, int img_h, int img_w, int bgr,
                 __nv_bfloat16* __restrict__ patches, int kpad, const float* __restrict__ cls_token,
                 const float* __restrict__ pos, float* __restrict__ x, int C) {
+  __shared__ float lut[3][256];
+  for (int e = threadIdx.x; e < 768; e += blockDim.x) {
+    const int c = e >> 8, u = e & 255;
+    const float mean = c == 0 ? 0.485f : (c == 1 ? 0.456f : 0.406f);
+    const float sd = c == 0 ? 0.229f : (c == 1 ? 0.224f : 0.225f);
+    lut[c][u] = __fdiv_rn(__fsub_rn(__fdiv_rn((float)u, 255.0f), mean), sd);
+  }
+  __syncthreads();
   const int gw = img_w / 14, gh = img_h / 14;
-  const size_t total = (size_t)B * gh * gw * kpad;
+  const int vec_per_patch = kpad >> 3;
+  const size_t total = (size_t)B * gh * gw * vec_per_patch;
   const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (i < total) {
-    const int k = (int)(i % kpad);
-    const size_t patch = i / kpad;
-    float val = 0.f;
-    if (k < 588) {
-      const int c = k / 196, r = k - c * 196, dy = r / 14, dx = r - dy * 14;
-      const int px = (int)(patch % gw);
-      const size_t t = patch / gw;
-      const int py = (int)(t % gh), img = (int)(t / gh);
-      const uint8_t u = images[(((size_t)img * img_h + py * 14 + dy) * img_w + px * 14 + dx) * 3 +
-                               (bgr ? 2 - c : c)];
-      // ToTensor (u8 / 255) then Normalize((x - mean) / std), torchvision semantics in fp32
-      const float mean = c == 0 ? 0.485f : (c == 1 ? 0.456f : 0.406f);
-      const float sd = c == 0 ? 0.229f : (c == 1 ? 0.224f : 0.225f);
-      val = __fdiv_rn(__fsub_rn(__fdiv_rn((float)u, 255.0f), mean), sd);
+    const int k0 = (int)(i % vec_per_patch) << 3;
+    const size_t patch = i / vec_per_patch;
+    const int px = (int)(patch % gw);
+    const size_t t = patch / gw;
+    const int py = (int)(t % gh), img = (int)(t / gh);
+    const uint8_t* base = images + (((size_t)img * img_h + py * 14) * img_w + px * 14) * 3;
+    int c = k0 / 196, r = k0 - c * 196, dy = r / 14, dx = r - dy * 14;
+    float v[8];
+#pragma unroll
+    for (int e = 0; e < 8; ++e) {
+      float val = 0.f;
+      if (k0 + e < 588) val = lut[c][base[((size_t)dy * img_w + dx) * 3 + (bgr ? 2 - c : c)]];
+      v[e] = val;
+      if (++dx == 14) {
+        dx = 0;
+        if (++dy == 14) {
+          dy = 0;
+          ++c;
+        }
+      }
     }
-    patches[i] = __float2bfloat16_rn(val);
+    uint4 o;
+    __nv_bfloat162 h0 = __floats2bfloat162_rn(v[0], v[1]), h1 = __floats2bfloat162_rn(v[2], v[3]);
+    __nv_bfloat162 h2 = __floats2bfloat162_rn(v[4], v[5]), h3 = __floats2bfloat162_rn(v[6], v[7]);
+    o.x = *reinterpret_cast<unsigned*>(&h0);
+    o.y = *reinterpret_cast<unsigned*>(&h1);
+    o.z = *reinterpret_cast<unsigned*>(&h2);
+    o.w = *reinterpret_cast<unsigned*>(&h3);
+    *reinterpret_cast<uint4*>(patches + patch * kpad + k0) = o;
   }
   // cls rows of the residual stream: cls_token + pos[0]
   const int T = gh * gw + 1;
-  if (i < (size_t)B * C) {
-    const int img = (int)(i / C), n = (int)(i % C);
-    x[(size_t)img * T * C + n] = cls_token[n] + pos[n];
+  for (size_t n = i; n < (size_t)B * C; n += (size_t)gridDim.x * blockDim.x) {
+    const int img = (int)(n / C), ch = (int)(n % C);
+    x[(size_t)img * T * C + ch] = cls_token[ch] + pos[ch];
   }
 }
 
@@ -130,7 +156,7 @@ cudaError_t launch_layernorm_final(const float* x, const float* w, const float* 
 cudaError_t launch_patchify(const uint8_t* images, int B, int img_h, int img_w, int bgr,
                             __nv_bfloat16* patches, int kpad, const float* cls_token, const float* pos,
                             float* x, int C, cudaStream_t stream) {
-  const size_t total = (size_t)B * (img_h / 14) * (img_w / 14) * kpad;
+  const size_t total = (size_t)B * (img_h / 14) * (img_w / 14) * (kpad / 8);  // kpad is a multiple of 64
   if (total == 0) return cudaSuccess;
   const unsigned blocks = (unsigned)((total + 255) / 256);
   patchify_kernel<<<blocks, 256, 0, stream>>>(images, B, img_h, img_w, bgr, patches, kpad, cls_token, pos,
