@@ -111,6 +111,24 @@ def make_descriptors_device(torch, dev, n_images=N_IMAGES, kpts=KPTS, dim=DIM, s
     return out
 
 
+def bench_config():
+    """The workload both arms (--impl ours / reference) report: identical dict, static keys only."""
+    n_pairs = N_IMAGES * (N_IMAGES - 1) // 2
+    return {"workload": f"exhaustive matching of one resident block: {N_IMAGES} images x {KPTS} kpts x d={DIM} "
+                        f"({n_pairs} pairs/step/GPU), ratio 0.8, distance 0.7, cross-check",
+            "kpts": KPTS, "d": DIM, "pairs_per_step_per_gpu": n_pairs,
+            "l2": "inputs 403 MB > 126 MB L2"}
+
+
+def make_descriptors_nonneg(torch, dev, n_images=N_IMAGES, kpts=KPTS, dim=DIM, seed=0):
+    """Descriptors shaped like the product path's uint8 rows (vit_extractor.py:243-250: L2-normalise,
+    x512, clip negatives to 0): |unit rows| re-normalised, so unrelated rows have cosine ~ 2/pi = 0.64
+    instead of ~0 -- at the default options that is AT the pruning bound (cos(0.7/0.8) = 0.64), i.e.
+    the bound removes about half of the unrelated scores instead of all of them."""
+    x = make_descriptors_device(torch, dev, n_images, kpts, dim, seed).float().abs()
+    return (x / x.norm(dim=2, keepdim=True)).to(torch.bfloat16)
+
+
 def all_pairs(n):
     return np.array([(i, j) for i in range(n) for j in range(i + 1, n)], dtype=np.int32)
 
@@ -163,7 +181,7 @@ def run_reference(args):
         "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1000.0 / value if value else None,
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": {"workload": "exhaustive matching, 8192 kpts/image, d=768 (CPU sample)", "kpts": KPTS, "d": DIM},
+        "config": bench_config(),
         "cpu_baseline": {"value": value, "unit": UNIT, "cores": threads, "kind": "port", "sample": sample},
         "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
@@ -270,6 +288,42 @@ def run_ours(args):
     peak_tf, peak_hbm, peak_src = _peaks()
     achieved_tf = FLOP_PER_PAIR * n_pairs / (kern_ms / 1e3) / 1e12
 
+    mean_matches = float(n_matches.float().mean().item())
+
+    # The pruning bound is data dependent: the same stage (a) with the bound switched off,
+    # (b) on non-negative rows shaped like the product path's uint8 descriptors, with and without it.
+    def time_variant(d_tensor, no_prune):
+        if no_prune:
+            os.environ["VC_MATCH_NO_PRUNE"] = "1"
+        try:
+            def run():
+                _lib.check(matcher.lib.vc_match_pairs(matcher.handle, d_tensor.data_ptr(), counts.data_ptr(), N_IMAGES,
+                                                      KPTS, DIM, pairs.data_ptr(), n_pairs, ctypes.byref(opt), None,
+                                                      None, ws.data_ptr(), need, matcher._stream()))
+            run(); run(); torch.cuda.synchronize()
+            v0, v1 = torch.cuda.Event(True), torch.cuda.Event(True)
+            v0.record()
+            for _ in range(reps):
+                run()
+            v1.record(); torch.cuda.synchronize()
+        finally:
+            os.environ.pop("VC_MATCH_NO_PRUNE", None)
+        v_ms = v0.elapsed_time(v1) / reps
+        v_tf = FLOP_PER_PAIR * n_pairs / (v_ms / 1e3) / 1e12
+        return {"kernel_ms": v_ms, "pairs_per_s": n_pairs / (v_ms / 1e3), "achieved_tflops": v_tf, "frac": v_tf / peak_tf}
+
+    variants = None
+    if rank == 0 and not args.skip_variants:
+        nonneg = make_descriptors_nonneg(torch, dev, N_IMAGES, KPTS, DIM, seed=0)
+        variants = {"signed_unit_rows_no_prune": time_variant(desc, True),
+                    "nonneg_rows": time_variant(nonneg, False),
+                    "nonneg_rows_no_prune": time_variant(nonneg, True),
+                    "note": "same top-2 stage as roofline; nonneg = |unit rows| renormalised (cosine of unrelated rows ~0.64, "
+                            "like clipped uint8 ViT descriptors); no_prune = VC_MATCH_NO_PRUNE=1"}
+        del nonneg
+    if world > 1:
+        dist.barrier()
+
     # end to end through the host-buffer C entry: pinned bf16 descriptors in, matches out
     e2e = None
     if rank == 0 or world > 1:
@@ -313,10 +367,8 @@ def run_ours(args):
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
             "warmup": max(args.warmup, 3), "ms_per_step": ms_total / args.steps, "higher_is_better": True,
             "scaling": "weak", "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
-            "config": {"workload": f"exhaustive matching of one resident block: {N_IMAGES} images x {KPTS} "
-                                   f"kpts x d={DIM} bf16 ({n_pairs} pairs/step/GPU), ratio 0.8, distance 0.7, "
-                                   "cross-check", "kpts": KPTS, "d": DIM, "pairs_per_step_per_gpu": n_pairs,
-                       "l2": "inputs 403 MB > 126 MB L2", "mean_matches_per_pair": float(n_matches.float().mean().item())},
+            "config": bench_config(),
+            "observed": {"mean_matches_per_pair": mean_matches},
             "e2e": e2e, "gpu_launches": int(launches),
             "roofline": {"bound": "tensor", "achieved": achieved_tf, "peak": peak_tf, "unit": "TFLOP/s",
                          "frac": achieved_tf / peak_tf, "traffic": NCU_TRAFFIC_BYTES,
@@ -337,6 +389,8 @@ def run_ours(args):
                                                      "reference post-processing restatement"}
             line["extract"] = extract
             line["extract_trainable"] = extract_tr
+        if variants is not None:
+            line["roofline_variants"] = variants
         if allgather_ms is not None:
             line["allgather_ms"] = allgather_ms
         if cpu_v is not None:
@@ -542,6 +596,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--skip-extract", action="store_true", help="matcher half of the metric only")
+    ap.add_argument("--skip-variants", action="store_true", help="skip the unpruned / non-negative-data matcher timings")
     args = ap.parse_args()
     if args.impl == "reference":
         run_reference(args)

@@ -120,11 +120,33 @@ int vc_match_pairs_host(vc_handle* h, const void* desc, int dtype, const int32_t
                         int n_images, int kmax, int d, const int32_t* pairs, int n_pairs,
                         const vc_match_options* opt, uint32_t* matches, int32_t* n_matches);
 
+/* Same call for descriptors that are ALREADY resident in HBM (bf16 [n_images, kmax, d], device
+ * pointer, written before the call on a stream the caller has synchronised): nothing but the pair
+ * list is uploaded; match lists come back to host memory, the read-back of one pair group overlapping
+ * the matching of the next.  This is what vit_colmap_b200.matching.match_exhaustive loops over pair
+ * chunks after uploading the database's descriptors ONCE.
+ * Replaces: the per-pair descriptor re-upload of SiftGPUFeatureMatcher::Match
+ * (COLMAP/feature/sift.cc:1270-1284, SIFTGPU/SiftMatchCU.cpp:99-112). */
+int vc_match_pairs_resident(vc_handle* h, const void* desc_bf16, const int32_t* counts, int n_images,
+                            int kmax, int d, const int32_t* pairs, int n_pairs,
+                            const vc_match_options* opt, uint32_t* matches, int32_t* n_matches);
+
 /* Element-wise converters used by the host entry and the Python mirror (device pointers).
  * u8 -> bf16 is exact (0..255 fit bf16's 8-bit significand), so uint8 d<=258 matching through
  * the bf16 tensor-core path reproduces COLMAP's int32 dot products bit for bit. */
 int vc_convert_u8_to_bf16(const uint8_t* src, void* dst_bf16, size_t n, void* stream);
 int vc_convert_f32_to_bf16(const float* src, void* dst_bf16, size_t n, void* stream);
+
+/* Rule VC_RULE_L2 preparation, on the device: uint8 descriptors [n_images, kmax, d] -> bf16
+ * [2*n_images, kmax, d+8] whose rows are augmented so that (row of copy i) . (row of copy
+ * n_images + j) = K - |x - y|^2 exactly (integers of at most 8 significant bits, partial sums below
+ * 2^24: fp32 accumulation is exact, ties resolve as in COLMAP).  Match pair (i, j) as
+ * (i, n_images + j) with opt.rule = VC_RULE_L2, opt.l2_offset = *l2_offset (= K, returned to the
+ * host; the call synchronises `stream` once to read the largest squared norm).
+ * Replaces: the squared-L2 search of COLMAP/feature/sift.cc:827-874 / feature/index.cc:41-131 (done
+ * exactly instead of through FAISS IVF). */
+int vc_l2_augment(vc_handle* h, const uint8_t* desc_u8, int n_images, int kmax, int d, void* out_bf16,
+                  float* l2_offset, void* stream);
 
 /* ------------------------------------------------------------------------------------------
  * Extraction post-processing (vit_colmap/features/vit_extractor.py ViTExtractor._dense_to_sparse

@@ -280,3 +280,111 @@ def test_pruning_bound_is_exact_near_the_bound(matcher, max_ratio, max_distance,
     pairs = [(0, 1), (1, 2), (2, 0), (1, 1)]
     n_exact = _compare_with_oracle(matcher, desc, counts, pairs, max_ratio, max_distance, cross_check)
     assert n_exact >= 2
+
+
+def test_resident_entry_equals_host_entry_and_oracle(matcher):
+    """Matcher.upload (ONE upload) + match_resident (vc_match_pairs_resident: only pair lists go up,
+    packed match lists come back) against vc_match_pairs_host and the C oracle, for uint8 and float
+    descriptors, more pairs than one call takes (pairs_per_call) and ragged counts."""
+    from oracle import matching as om
+    rng = np.random.default_rng(31)
+    n_images, kmax, d = 7, 500, 128
+    counts = [500, 499, 0, 257, 1, 500, 333]
+    f = _make_set(rng, n_images, kmax, d, counts)
+    u8 = np.zeros(f.shape, np.uint8)
+    for i, n in enumerate(counts):
+        u8[i, :n] = om.to_uint8_colmap(om.l2_normalize(np.abs(f[i, :n]))) if n else 0
+    pairs = np.array([(i, j) for i in range(n_images) for j in range(n_images) if i != j] + [(0, 0)], np.int32)
+    cnt = np.array(counts, np.int32)
+    for host in (u8, f):
+        resident = matcher.upload(host, cnt)
+        got = matcher.match_resident(resident, pairs, 0.8, 0.7, True, pairs_per_call=16)
+        ref = matcher.match_pairs_host(host, cnt, pairs, 0.8, 0.7, True)
+        assert [g.tolist() for g in got] == [r.tolist() for r in ref]
+        for k in (0, 5, 17, len(pairs) - 1):
+            i1, i2 = pairs[k]
+            exact = om.match_c(host[i1, : counts[i1]], host[i2, : counts[i2]], 0.8, 0.7, True)
+            assert got[k].tolist() == exact.tolist()
+    assert sum(len(g) for g in got) > 500
+    with pytest.raises(ValueError):
+        matcher.match_resident(resident, np.array([[0, n_images]], np.int32))
+    with pytest.raises(Exception):  # a host pointer is not a resident descriptor set
+        import ctypes
+        from vit_colmap_b200 import _lib
+        opt = matcher._opts(0.8, 0.7, True, 1.0)
+        out, nm = np.zeros((1, kmax, 2), np.uint32), np.zeros(1, np.int32)
+        _lib.check(matcher.lib.vc_match_pairs_resident(matcher.handle, f.ctypes.data, cnt.ctypes.data, n_images, kmax,
+                                                       d, pairs.ctypes.data, 1, ctypes.byref(opt), out.ctypes.data,
+                                                       nm.ctypes.data))
+
+
+def test_l2_augment_kernel_is_exact(matcher):
+    """vc_l2_augment (device) against the integer construction it documents: rows of role 1 dotted
+    with rows of role 2 give K - |x - y|^2 exactly in fp32."""
+    import ctypes
+    import torch
+    from vit_colmap_b200 import _lib
+    rng = np.random.default_rng(3)
+    n_images, kmax, d = 3, 37, 128
+    u8 = rng.integers(0, 256, (n_images, kmax, d), dtype=np.uint8)
+    u8[1, 5] = 180                                     # 2 |x|^2 + 1 just below 2^23: the largest K allowed
+    u8[2, 7] = 0
+    src = torch.from_numpy(u8).cuda()
+    out = torch.empty((2 * n_images, kmax, d + 8), dtype=torch.bfloat16, device="cuda")
+    k = ctypes.c_float(0)
+    _lib.check(matcher.lib.vc_l2_augment(matcher.handle, src.data_ptr(), n_images, kmax, d, out.data_ptr(),
+                                         ctypes.byref(k), 0))
+    torch.cuda.synchronize()
+    aug = out.float().cpu().numpy().astype(np.float64)
+    K = float(k.value)
+    norm2 = (u8.astype(np.int64) ** 2).sum(-1)
+    assert K == 2.0 ** np.ceil(np.log2(2 * norm2.max() + 2)) == 2 ** 23
+    a, b = aug[:n_images].reshape(-1, d + 8), aug[n_images:].reshape(-1, d + 8)
+    x = u8.reshape(-1, d).astype(np.int64)
+    dist2 = ((x[:, None, :] - x[None, :, :]) ** 2).sum(-1)
+    assert np.array_equal(a @ b.T, K - dist2)
+    assert np.abs(aug).max() <= max(K, 65536 * 255) and np.array_equal(aug, np.round(aug))
+
+
+def test_more_pairs_than_a_grid_dimension(matcher):
+    """n_pairs > 65535: the merge kernels index pairs on gridDim.x (a y-dimension launch would fail
+    with an invalid configuration after the main kernel has already run)."""
+    import torch
+    from oracle import matching as om
+    rng = np.random.default_rng(9)
+    n_images, kmax, d = 6, 24, 32
+    counts = [24, 24, 17, 24, 1, 24]
+    desc = _make_set(rng, n_images, kmax, d, counts)
+    base = [(i, j) for i in range(n_images) for j in range(n_images) if i != j]
+    pairs = np.array([base[k % len(base)] for k in range(70001)], np.int32)
+    t = torch.from_numpy(desc).cuda().to(torch.bfloat16)
+    m, n = matcher.match_pairs(t, torch.tensor(counts, dtype=torch.int32, device="cuda"),
+                               torch.from_numpy(pairs).cuda(), 0.9, 1.2, True, 1.0)
+    torch.cuda.synchronize()
+    m, n = m.cpu().numpy().astype(np.uint32), n.cpu().numpy()
+    for k in list(range(len(base))) + [65535, 65536, 70000]:
+        i1, i2 = pairs[k]
+        ref = om.match_c(desc[i1, : counts[i1]], desc[i2, : counts[i2]], 0.9, 1.2, True)
+        assert m[k, : n[k]].tolist() == ref.tolist(), k
+    assert np.array_equal(n[: len(base)], n[len(base): 2 * len(base)]) and n.sum() > 70001
+
+
+def test_two_handles_on_two_devices():
+    """A second vc_handle on another GPU of the same process: the > 48 KB shared-memory opt-in is per
+    (kernel, device), so every kernel family must work on both.  Needs two GPUs."""
+    import torch
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs two GPUs")
+    from oracle import matching as om
+    from vit_colmap_b200.matching import Matcher
+    rng = np.random.default_rng(2)
+    kmax, counts = 300, [300, 280]
+    for d in (128, 768):  # single-CTA and two-SM kernels
+        desc = _make_set(rng, 2, kmax, d, counts)
+        ref = om.match_c(desc[0, :300], desc[1, :280], 0.8, 0.7, True)
+        for dev in (0, 1, 0):
+            m = Matcher(dev)
+            with torch.cuda.device(dev):
+                got = m.match_pairs_host(desc, np.array(counts, np.int32), np.array([[0, 1]], np.int32))
+            assert got[0].tolist() == ref.tolist(), (d, dev)
+            m.close()

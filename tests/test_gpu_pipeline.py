@@ -211,3 +211,76 @@ def test_pipelined_batches_equal_serial_batches(vit_s):
             assert np.array_equal(k1, k2) and np.array_equal(d1, d2)
     with pytest.raises(ValueError):
         list(vit_s.extract_batches(bad))
+
+
+@pytest.mark.parametrize("rule", ["angular", "l2"])
+def test_match_exhaustive_uploads_once_and_equals_oracle(tmp_path, rule):
+    """match_exhaustive end to end over a database of SIFT-like uint8 descriptors (13 images, ragged
+    counts, one image without descriptors): every written `matches` row equals the CPU oracle pair by
+    pair (including the < min_num_matches blanking and the pair_id / column-swap rule), the resident
+    path (one upload) and the per-pairing-block path (forced by max_resident_bytes) agree, a second
+    call finds nothing to do (resume semantics), and the kernel-launch count shows the descriptors were
+    converted ONCE rather than once per pair chunk."""
+    from oracle import matching as om
+    from vit_colmap_b200 import _lib
+    from vit_colmap_b200.database import ColmapDatabase, Database
+    from vit_colmap_b200.matching import FeatureMatchingOptions, match_exhaustive
+    rng = np.random.default_rng(4)
+    n_images, d = 13, 128
+    counts = [int(c) for c in rng.integers(150, 420, n_images)]
+    counts[5] = 0
+    base = rng.standard_normal((600, d)).astype(np.float32)
+    descs = []
+    for n in counts:
+        rows = np.abs(base[rng.permutation(600)[:n]] + 0.15 * rng.standard_normal((n, d)).astype(np.float32))
+        descs.append(om.to_uint8_colmap(om.l2_normalize(rows)) if n else np.zeros((0, d), np.uint8))
+
+    def make_db(path):
+        db = ColmapDatabase(str(path))
+        cam = db.add_pinhole_camera(640, 480, 500.0, 500.0, 320.0, 240.0)
+        ids = [db.add_image(f"im{i:02d}.png", camera_id=cam) for i in range(n_images)]
+        for i, image_id in enumerate(ids):
+            if counts[i]:
+                db.add_keypoints(image_id, rng.uniform(0, 400, (counts[i], 2)).astype(np.float32))
+                db.add_descriptors(image_id, descs[i])
+        db.close()
+        return ids
+
+    class Blocks:
+        block_size = 5
+
+    opts = FeatureMatchingOptions(max_ratio=0.85, max_distance=0.9, min_num_matches=15, rule=rule)
+    lib = _lib.load()
+    ids = make_db(tmp_path / "a.db")
+    lib.vc_launch_count(1)
+    res = match_exhaustive(str(tmp_path / "a.db"), opts, Blocks(), pairs_per_launch=16)
+    launches_once = lib.vc_launch_count(1)
+    make_db(tmp_path / "b.db")
+    res_blocks = match_exhaustive(str(tmp_path / "b.db"), opts, Blocks(), max_resident_bytes=1)
+    assert len(res) == n_images * (n_images - 1) // 2 and set(res) == set(res_blocks)
+    n_nonempty = 0
+    for (a, b), m in res.items():
+        i, j = ids.index(a), ids.index(b)
+        if rule == "l2":
+            ref = om.match_l2_numpy(descs[i], descs[j], opts.max_ratio, opts.max_distance, True)
+        else:
+            ref = om.match_c(descs[i], descs[j], opts.max_ratio, opts.max_distance, True) if counts[i] and counts[j] \
+                else np.zeros((0, 2), np.uint32)
+        if len(ref) < 15:
+            ref = np.zeros((0, 2), np.uint32)
+        assert m.tolist() == ref.tolist(), (a, b)
+        assert res_blocks[(a, b)].tolist() == m.tolist()
+        n_nonempty += len(m) > 0
+    assert n_nonempty > 30
+    with Database.open(str(tmp_path / "a.db")) as db:
+        assert db.num_matched_image_pairs() == len(res)
+        for (a, b), m in list(res.items())[:20]:
+            assert db.read_matches(a, b).tolist() == m.tolist()           # re-oriented to the (a, b) order asked for
+            assert db.read_matches(b, a).tolist() == m[:, ::-1].tolist()  # stored once, columns follow min/max id
+    assert match_exhaustive(str(tmp_path / "a.db"), opts, Blocks()) == {}
+    # 78 pairs in chunks of <= 16 per pairing block: per chunk memset-free launches are the fused kernel,
+    # its merge(s), emit, scan + pack; the u8 -> bf16 conversion (or the two l2 kernels) runs once
+    from vit_colmap_b200.pairing import ExhaustivePairGenerator
+    n_chunks = sum(-(-len(b) // 16) for b in ExhaustivePairGenerator(ids, 5).blocks())
+    per_chunk = (launches_once - (2 if rule == "l2" else 1)) / n_chunks
+    assert per_chunk == int(per_chunk) and 4 <= per_chunk <= 7, (launches_once, n_chunks)

@@ -42,6 +42,9 @@ SIGNATURES = {
                                 c_void_p, c_int, c_void_p]),
     "vc_match_pairs_host": (c_int, [c_void_p, c_void_p, c_int, c_void_p, c_int, c_int, c_int,
                                     c_void_p, c_int, POINTER(MatchOptions), c_void_p, c_void_p]),
+    "vc_match_pairs_resident": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_void_p, c_int,
+                                        POINTER(MatchOptions), c_void_p, c_void_p]),
+    "vc_l2_augment": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_void_p, POINTER(c_float), c_void_p]),
     "vc_convert_u8_to_bf16": (c_int, [c_void_p, c_void_p, c_size_t, c_void_p]),
     "vc_convert_f32_to_bf16": (c_int, [c_void_p, c_void_p, c_size_t, c_void_p]),
     "vc_score_workspace_bytes": (c_size_t, [c_int, c_int, c_int]),

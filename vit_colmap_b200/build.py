@@ -55,9 +55,13 @@ def build(force: bool = False, verbose: bool = False) -> Path:
     objdir = PKG / "build"
     objdir.mkdir(exist_ok=True)
     nvcc = _nvcc()
-    objs = []
-    for src in sources():
+    headers = list(CSRC.glob("*.cuh")) + [PKG.parent / "include" / "vc_b200.h"]
+    newest_header = max(h.stat().st_mtime for h in headers)
+
+    def compile_one(src: Path) -> str:
         obj = objdir / (src.stem + ".o")
+        if not force and obj.exists() and obj.stat().st_mtime > max(src.stat().st_mtime, newest_header):
+            return str(obj)  # object is newer than its source and every header
         cmd = [nvcc, *NVCC_FLAGS, "-c", str(src), "-o", str(obj)]
         res = subprocess.run(cmd, capture_output=True, text=True)
         if verbose or res.returncode != 0:
@@ -65,7 +69,11 @@ def build(force: bool = False, verbose: bool = False) -> Path:
         if res.returncode != 0:
             raise RuntimeError(f"nvcc failed on {src.name}")
         (objdir / (src.stem + ".ptxas.log")).write_text(res.stdout + res.stderr)
-        objs.append(str(obj))
+        return str(obj)
+
+    from concurrent.futures import ThreadPoolExecutor
+    with ThreadPoolExecutor(max_workers=min(8, os.cpu_count() or 1)) as pool:
+        objs = list(pool.map(compile_one, sources()))
     cmd = [nvcc, "-shared", "-o", str(OUT), *objs, "-gencode", "arch=compute_100a,code=sm_100a",
            "-cudart", "static"]
     res = subprocess.run(cmd, capture_output=True, text=True)

@@ -16,6 +16,7 @@
 
 #include "vc_epilogue.cuh"
 #include "vc_ptx.cuh"
+#include "vc_launch.cuh"
 
 namespace vc {
 
@@ -310,13 +311,8 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
 template <int EPI>
 cudaError_t launch_one(const CUtensorMap& map_a, const CUtensorMap& map_w, const ConvParams& p, int grid,
                        cudaStream_t stream) {
-  static bool configured = false;
-  if (!configured) {
-    cudaError_t e = cudaFuncSetAttribute(conv_gemm_kernel<EPI>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                         kSmemBytes);
-    if (e != cudaSuccess) return e;
-    configured = true;
-  }
+  static SmemOptIn opt_in;  // one per EPI instantiation
+  if (cudaError_t e = ensure_dynamic_smem(conv_gemm_kernel<EPI>, kSmemBytes, opt_in); e != cudaSuccess) return e;
   conv_gemm_kernel<EPI><<<grid, kThreads, kSmemBytes, stream>>>(map_a, map_w, p);
   return cudaGetLastError();
 }

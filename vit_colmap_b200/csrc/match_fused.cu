@@ -20,6 +20,7 @@
 #include <math.h>
 
 #include "vc_ptx.cuh"
+#include "vc_launch.cuh"
 
 namespace vc {
 
@@ -309,8 +310,8 @@ match_fused_kernel(const __grid_constant__ CUtensorMap tmap, const MatchParams p
 // Merge the per-column-block row partials in ascending column order (the reference's scan order,
 // sift.cc:745-757) and apply the distance / ratio tests -> m_out[pair][0][row].
 __global__ void merge_rows_kernel(const MatchParams p) {
-  const int pair = blockIdx.y;
-  const int row = blockIdx.x * blockDim.x + threadIdx.x;
+  const int pair = blockIdx.x;  // pairs on x: no 65535 limit
+  const int row = blockIdx.y * blockDim.x + threadIdx.x;
   const int i0 = p.pairs[2 * pair], i1 = p.pairs[2 * pair + 1];
   const int n1 = min(p.counts[i0], p.kmax), n2 = min(p.counts[i1], p.kmax);
   if (row >= n1) return;
@@ -343,13 +344,8 @@ int match_fused_smem_bytes() { return kSmemBytes; }
 
 cudaError_t launch_match_fused(const CUtensorMap& tmap, const MatchParams& p, int num_sms,
                                cudaStream_t stream) {
-  static bool configured = false;
-  if (!configured) {
-    cudaError_t e = cudaFuncSetAttribute(match_fused_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                         kSmemBytes);
-    if (e != cudaSuccess) return e;
-    configured = true;
-  }
+  static SmemOptIn opt_in;
+  if (cudaError_t e = ensure_dynamic_smem(match_fused_kernel, kSmemBytes, opt_in); e != cudaSuccess) return e;
   if (p.n_items <= 0) return cudaSuccess;
   cudaError_t e = cudaMemsetAsync(p.rowthr, 0, (size_t)p.n_pairs * p.kmax * sizeof(unsigned int), stream);
   if (e != cudaSuccess) return e;
@@ -357,7 +353,7 @@ cudaError_t launch_match_fused(const CUtensorMap& tmap, const MatchParams& p, in
   match_fused_kernel<<<grid, kThreads, kSmemBytes, stream>>>(tmap, p);
   e = cudaGetLastError();
   if (e != cudaSuccess) return e;
-  dim3 g((p.kmax + 255) / 256, p.n_pairs);
+  dim3 g(p.n_pairs, (p.kmax + 255) / 256);
   merge_rows_kernel<<<g, 256, 0, stream>>>(p);
   return cudaGetLastError();
 }

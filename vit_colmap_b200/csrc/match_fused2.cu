@@ -30,6 +30,7 @@
 #include <math.h>
 
 #include "vc_ptx.cuh"
+#include "vc_launch.cuh"
 
 namespace vc {
 
@@ -388,8 +389,8 @@ match_fused2_kernel(const __grid_constant__ CUtensorMap tmap, const MatchParams 
 // Column results: merge the two CTAs' (key, second) states.  key = score bits << 32 | ~row, so the
 // larger key is the better score (lowest row on ties); the loser's best score competes for second.
 __global__ void merge_cols2_kernel(const MatchParams p) {
-  const int pair = blockIdx.y;
-  const int col = blockIdx.x * blockDim.x + threadIdx.x;
+  const int pair = blockIdx.x;  // pairs on x: no 65535 limit
+  const int col = blockIdx.y * blockDim.x + threadIdx.x;
   const int i1 = p.pairs[2 * pair + 1];
   const int n2 = min(p.counts[i1], p.kmax);
   const int n1 = min(p.counts[p.pairs[2 * pair]], p.kmax);
@@ -414,8 +415,8 @@ __global__ void merge_cols2_kernel(const MatchParams p) {
 // Merge the per-column-block row partials in ascending column order (the reference's scan order,
 // sift.cc:745-757) and apply the distance / ratio tests -> m_out[pair][0][row].
 __global__ void merge_rows2_kernel(const MatchParams p) {
-  const int pair = blockIdx.y;
-  const int row = blockIdx.x * blockDim.x + threadIdx.x;
+  const int pair = blockIdx.x;  // pairs on x: no 65535 limit
+  const int row = blockIdx.y * blockDim.x + threadIdx.x;
   const int i0 = p.pairs[2 * pair], i1 = p.pairs[2 * pair + 1];
   const int n1 = min(p.counts[i0], p.kmax), n2 = min(p.counts[i1], p.kmax);
   if (row >= n1) return;
@@ -448,13 +449,8 @@ int match_fused2_smem_bytes() { return kSmemBytes; }
 
 cudaError_t launch_match_fused2(const CUtensorMap& tmap, const MatchParams& p, int num_sms,
                                cudaStream_t stream) {
-  static bool configured = false;
-  if (!configured) {
-    cudaError_t e = cudaFuncSetAttribute(match_fused2_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                         kSmemBytes);
-    if (e != cudaSuccess) return e;
-    configured = true;
-  }
+  static SmemOptIn opt_in;
+  if (cudaError_t e = ensure_dynamic_smem(match_fused2_kernel, kSmemBytes, opt_in); e != cudaSuccess) return e;
   if (p.n_items <= 0) return cudaSuccess;
   cudaError_t e = cudaMemsetAsync(p.rowthr, 0, (size_t)p.n_pairs * p.kmax * sizeof(unsigned int), stream);
   if (e != cudaSuccess) return e;
@@ -462,7 +458,7 @@ cudaError_t launch_match_fused2(const CUtensorMap& tmap, const MatchParams& p, i
   match_fused2_kernel<<<2 * clusters, kThreads, kSmemBytes, stream>>>(tmap, p);  // __cluster_dims__(2,1,1)
   e = cudaGetLastError();
   if (e != cudaSuccess) return e;
-  dim3 g((p.kmax + 255) / 256, p.n_pairs);
+  dim3 g(p.n_pairs, (p.kmax + 255) / 256);
   merge_rows2_kernel<<<g, 256, 0, stream>>>(p);
   merge_cols2_kernel<<<g, 256, 0, stream>>>(p);
   return cudaGetLastError();

@@ -18,6 +18,7 @@
 #include <math.h>
 
 #include "vc_ptx.cuh"
+#include "vc_launch.cuh"
 
 namespace vc {
 
@@ -313,6 +314,62 @@ __global__ void f32_to_bf16_kernel(const float* __restrict__ src, __nv_bfloat16*
   }
 }
 
+// Squared-L2 matching through the dot-product kernels (rule VC_RULE_L2): rows are augmented by 8
+// columns so that (image-1 row) . (image-2 row) = K - |x - y|^2 exactly,
+//   role 1: [2x | D0 D1 D2 | 1 1 1 1]              |x|^2 = D0 + 256 D1 + 65536 D2
+//   role 2: [ y | -1 -256 -65536 | -E0 -256 E1 -65536 E2 | K]   |y|^2 = E0 + 256 E1 + 65536 E2
+// every entry an integer with at most 8 significant bits (exact in bf16), every partial sum < 2^24.
+__global__ void l2_max_norm2_kernel(const uint8_t* __restrict__ src, size_t rows, int d, int* __restrict__ out) {
+  const size_t row = ((size_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const int lane = threadIdx.x & 31;
+  if (row >= rows) return;
+  const uint8_t* r = src + row * d;
+  int acc = 0;
+  for (int k = lane; k < d; k += 32) acc += (int)r[k] * (int)r[k];
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
+  if (lane == 0 && acc > 0) atomicMax(out, acc);
+}
+
+__global__ void l2_augment_kernel(const uint8_t* __restrict__ src, size_t rows, int d, float offset_k,
+                                  __nv_bfloat16* __restrict__ dst) {
+  const size_t row = ((size_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const int lane = threadIdx.x & 31;
+  if (row >= rows) return;
+  const uint8_t* r = src + row * d;
+  __nv_bfloat16* o1 = dst + row * (d + 8);
+  __nv_bfloat16* o2 = dst + (rows + row) * (d + 8);
+  int acc = 0;
+  for (int k = lane; k < d; k += 32) {
+    const int v = r[k];
+    acc += v * v;
+    o1[k] = __float2bfloat16_rn((float)(2 * v));
+    o2[k] = __float2bfloat16_rn((float)v);
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
+  if (lane < 8) {
+    const float dig[3] = {(float)(acc & 255), (float)((acc >> 8) & 255), (float)(acc >> 16)};
+    const float w[3] = {1.f, 256.f, 65536.f};
+    float a, b;
+    if (lane < 3) {
+      a = dig[lane];
+      b = -w[lane];
+    } else if (lane < 6) {
+      a = 1.f;
+      b = -dig[lane - 3] * w[lane - 3];
+    } else if (lane == 6) {
+      a = 1.f;
+      b = offset_k;
+    } else {
+      a = 0.f;  // 8th column: padding to a multiple of 8 (16-byte rows)
+      b = 0.f;
+    }
+    o1[d + lane] = __float2bfloat16_rn(a);
+    o2[d + lane] = __float2bfloat16_rn(b);
+  }
+}
+
 // ---------------------------------------------------------------------------------------------
 // Host launchers
 
@@ -320,13 +377,9 @@ int match_smem_bytes() { return kSmemBytes; }
 
 cudaError_t launch_match_top2(const CUtensorMap& tmap, const MatchParams& p, int num_sms, bool debug,
                               cudaStream_t stream) {
-  static bool configured[2] = {false, false};
+  static SmemOptIn opt_in[2];
   auto kern = debug ? match_top2_kernel<true> : match_top2_kernel<false>;
-  if (!configured[debug]) {
-    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes);
-    if (e != cudaSuccess) return e;
-    configured[debug] = true;
-  }
+  if (cudaError_t e = ensure_dynamic_smem(kern, kSmemBytes, opt_in[debug]); e != cudaSuccess) return e;
   if (p.n_items <= 0) return cudaSuccess;
   const int grid = p.n_items < num_sms ? p.n_items : num_sms;
   kern<<<grid, kThreads, kSmemBytes, stream>>>(tmap, p);
@@ -414,6 +467,21 @@ cudaError_t launch_f32_to_bf16(const float* src, void* dst, size_t n, cudaStream
   const size_t threads = (n + 7) / 8;
   f32_to_bf16_kernel<<<(unsigned)((threads + 255) / 256), 256, 0, stream>>>(
       src, reinterpret_cast<__nv_bfloat16*>(dst), n);
+  return cudaGetLastError();
+}
+
+cudaError_t launch_l2_max_norm2(const uint8_t* src, size_t rows, int d, int* out, cudaStream_t stream) {
+  cudaError_t e = cudaMemsetAsync(out, 0, sizeof(int), stream);
+  if (e != cudaSuccess || rows == 0) return e;
+  l2_max_norm2_kernel<<<(unsigned)((rows * 32 + 255) / 256), 256, 0, stream>>>(src, rows, d, out);
+  return cudaGetLastError();
+}
+
+cudaError_t launch_l2_augment(const uint8_t* src, size_t rows, int d, float offset_k, void* dst,
+                              cudaStream_t stream) {
+  if (rows == 0) return cudaSuccess;
+  l2_augment_kernel<<<(unsigned)((rows * 32 + 255) / 256), 256, 0, stream>>>(
+      src, rows, d, offset_k, reinterpret_cast<__nv_bfloat16*>(dst));
   return cudaGetLastError();
 }
 

@@ -76,5 +76,9 @@ cudaError_t launch_compact_matches(const uint32_t* matches, const int32_t* n_mat
                                    int32_t* offsets, uint32_t* packed, cudaStream_t stream);
 cudaError_t launch_u8_to_bf16(const uint8_t* src, void* dst, size_t n, cudaStream_t stream);
 cudaError_t launch_f32_to_bf16(const float* src, void* dst, size_t n, cudaStream_t stream);
+// rule VC_RULE_L2: max_i |row_i|^2 -> *out (device int), and the augmented bf16 rows [2*rows, d+8]
+cudaError_t launch_l2_max_norm2(const uint8_t* src, size_t rows, int d, int* out, cudaStream_t stream);
+cudaError_t launch_l2_augment(const uint8_t* src, size_t rows, int d, float offset_k, void* dst,
+                              cudaStream_t stream);
 
 }  // namespace vc

@@ -9,6 +9,7 @@
 //   sample_pack_project: 16 keypoints per CTA are staged in shared memory (channel-major), the
 //                        [C, d] projection streams through L2 once per CTA, fp32 SIMT FMAs.
 #include "extract_kernels.cuh"
+#include "vc_launch.cuh"
 
 namespace vc {
 
@@ -364,15 +365,11 @@ cudaError_t launch_sample_pack(const SampleParams& p, cudaStream_t stream) {
     return cudaGetLastError();
   }
   const int smem = (p.C * kTile + kTile * p.d) * (int)sizeof(float);
-  static int configured[2] = {0, 0};
-  if (smem > configured[p.is_bf16 ? 1 : 0]) {
-    cudaError_t e = p.is_bf16 ? cudaFuncSetAttribute(sample_pack_project<__nv_bfloat16>,
-                                                     cudaFuncAttributeMaxDynamicSharedMemorySize, smem)
-                              : cudaFuncSetAttribute(sample_pack_project<float>,
-                                                     cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
-    if (e != cudaSuccess) return e;
-    configured[p.is_bf16 ? 1 : 0] = smem;
-  }
+  static SmemOptIn opt_in[2];
+  if (cudaError_t e = p.is_bf16 ? ensure_dynamic_smem(sample_pack_project<__nv_bfloat16>, smem, opt_in[1])
+                                : ensure_dynamic_smem(sample_pack_project<float>, smem, opt_in[0]);
+      e != cudaSuccess)
+    return e;
   const int tiles = (p.cap + kTile - 1) / kTile;
   if (tiles == 0 || p.B == 0) return cudaSuccess;
   if (p.is_bf16)

@@ -9,6 +9,7 @@
 // Kernel 2 (response_kernel) is one CTA per image on the [H, W] moment maps: 3x3 / 7x7 / 11x11
 // zero-padded Gaussian stencils, corner/edge response, block-wide min / max, normalisation.
 #include "extract_kernels.cuh"
+#include "vc_launch.cuh"
 
 namespace vc {
 
@@ -220,13 +221,9 @@ __global__ void __launch_bounds__(1024, 1) response_kernel(const ScoreParams p) 
 }  // namespace
 
 cudaError_t launch_score_map(const ScoreParams& p, cudaStream_t stream) {
-  static bool configured = false;
-  if (!configured) {
-    cudaError_t e = cudaFuncSetAttribute(response_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                         kMaxGridCells * (int)sizeof(float));
-    if (e != cudaSuccess) return e;
-    configured = true;
-  }
+  static SmemOptIn opt_in;
+  if (cudaError_t e = ensure_dynamic_smem(response_kernel, kMaxGridCells * (int)sizeof(float), opt_in); e != cudaSuccess)
+    return e;
   const int strips = (p.W + kStrip - 1) / kStrip;
   const long long warps = (long long)p.B * p.H * strips;
   const int blocks = (int)((warps * 32 + 255) / 256);

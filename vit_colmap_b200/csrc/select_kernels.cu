@@ -13,6 +13,7 @@
 //      Decisions are final once taken, so the result equals the sequential greedy loop.
 //   4. block-wide exclusive scan -> (y, x), score in descending-score order.
 #include "extract_kernels.cuh"
+#include "vc_launch.cuh"
 
 namespace vc {
 
@@ -214,12 +215,8 @@ int select_smem_bytes(int H, int W, int K, int bin_size) {
 
 cudaError_t launch_select_keypoints(const SelectParams& p, cudaStream_t stream) {
   const int smem = select_smem_bytes(p.H, p.W, p.num_keypoints, p.bin_size);
-  static int configured = 0;
-  if (smem > configured) {
-    cudaError_t e = cudaFuncSetAttribute(select_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
-    if (e != cudaSuccess) return e;
-    configured = smem;
-  }
+  static SmemOptIn opt_in;
+  if (cudaError_t e = ensure_dynamic_smem(select_kernel, smem, opt_in); e != cudaSuccess) return e;
   select_kernel<<<p.B, kThreads, smem, stream>>>(p);
   return cudaGetLastError();
 }

@@ -324,13 +324,42 @@ int vc_convert_f32_to_bf16(const float* src, void* dst_bf16, size_t n, void* str
   return VC_OK;
 }
 
+}  // extern "C"
+
+extern "C" int vc_l2_augment(vc_handle* h, const uint8_t* desc_u8, int n_images, int kmax, int d, void* out_bf16,
+                             float* l2_offset, void* stream) {
+  if (!h || !desc_u8 || !out_bf16 || !l2_offset) return fail(VC_ERR_INVALID, "null pointer argument");
+  if (n_images <= 0 || kmax <= 0 || d <= 0 || d % 8 != 0) return fail(VC_ERR_INVALID, "bad sizes");
+  VC_CUDA(cudaSetDevice(h->device));
+  cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
+  const size_t rows = (size_t)n_images * kmax;
+  // the first word of the output doubles as the reduction cell; the augment pass overwrites it
+  int* cell = static_cast<int*>(out_bf16);
+  VC_CUDA(vc::launch_l2_max_norm2(desc_u8, rows, d, cell, s));
+  int max_norm2 = 0;
+  VC_CUDA(cudaMemcpyAsync(&max_norm2, cell, sizeof(int), cudaMemcpyDeviceToHost, s));
+  VC_CUDA(cudaStreamSynchronize(s));
+  // K: power of two above 2 max|x|^2 >= max |x - y|^2; partial sums stay below 2^24 while K <= 2^23
+  long long k = 2;
+  while (k <= 2LL * max_norm2 + 1) k <<= 1;
+  if (k > (1LL << 23))
+    return fail(VC_ERR_INVALID, "descriptor norms too large for the exact l2 rule (need 2*max|x|^2 < 2^23, have %d)",
+                max_norm2);
+  VC_CUDA(vc::launch_l2_augment(desc_u8, rows, d, (float)k, out_bf16, s));
+  g_launches += 2;
+  *l2_offset = (float)k;
+  return VC_OK;
+}
+
 // Host-buffer entry.  The descriptor upload is cut into up to four image chunks on an upload stream
 // and the pairs are ordered by the last chunk they need, so group g is matched while chunk g+1 is
 // still in flight; each group's match lists are packed on the device and read back with two copies
-// on a download stream while the next group runs.
-int vc_match_pairs_host(vc_handle* h, const void* desc, int dtype, const int32_t* counts,
-                        int n_images, int kmax, int d, const int32_t* pairs, int n_pairs,
-                        const vc_match_options* opt, uint32_t* matches, int32_t* n_matches) {
+// on a download stream while the next group runs.  With `resident` the descriptors are already bf16
+// in HBM (desc is a device pointer): nothing is uploaded and the pairs are cut into consecutive
+// groups only so that the read-back of one overlaps the matching of the next.
+static int match_host_impl(vc_handle* h, const void* desc, int dtype, bool resident, const int32_t* counts,
+                           int n_images, int kmax, int d, const int32_t* pairs, int n_pairs,
+                           const vc_match_options* opt, uint32_t* matches, int32_t* n_matches) {
   if (!h) return fail(VC_ERR_INVALID, "null handle");
   if (!desc || !counts || !opt || !matches || !n_matches || (n_pairs > 0 && !pairs))
     return fail(VC_ERR_INVALID, "null pointer argument");
@@ -353,20 +382,24 @@ int vc_match_pairs_host(vc_handle* h, const void* desc, int dtype, const int32_t
   const size_t n_el = (size_t)n_images * img_el;
   const size_t el = dtype == VC_DTYPE_U8 ? 1 : (dtype == VC_DTYPE_F32 ? 4 : 2);
   // pair groups: chunk c holds images [c*per, (c+1)*per); a pair belongs to the chunk of its larger index
-  const int n_groups = (n_images >= 8 && n_el * el >= (size_t)(32u << 20)) ? 4 : 1;
+  const int n_groups = resident ? std::min(4, (n_pairs + 63) / 64)
+                                : ((n_images >= 8 && n_el * el >= (size_t)(32u << 20)) ? 4 : 1);
   const int per = (n_images + n_groups - 1) / n_groups;
   std::vector<int> start(n_groups + 1, 0), order(n_pairs);
-  for (int i = 0; i < n_pairs; ++i) ++start[std::max(pairs[2 * i], pairs[2 * i + 1]) / per + 1];
-  for (int g = 0; g < n_groups; ++g) start[g + 1] += start[g];
-  {
+  if (resident) {
+    for (int g = 0; g <= n_groups; ++g) start[g] = (int)((long long)n_pairs * g / n_groups);
+    for (int i = 0; i < n_pairs; ++i) order[i] = i;
+  } else {
+    for (int i = 0; i < n_pairs; ++i) ++start[std::max(pairs[2 * i], pairs[2 * i + 1]) / per + 1];
+    for (int g = 0; g < n_groups; ++g) start[g + 1] += start[g];
     std::vector<int> fill(start.begin(), start.end() - 1);
     for (int i = 0; i < n_pairs; ++i) order[fill[std::max(pairs[2 * i], pairs[2 * i + 1]) / per]++] = i;
   }
   int max_group = 0;
   for (int g = 0; g < n_groups; ++g) max_group = std::max(max_group, start[g + 1] - start[g]);
 
-  const size_t src_bytes = dtype == VC_DTYPE_BF16 ? 0 : align_up(n_el * el, 256);
-  const size_t bf_bytes = align_up(n_el * 2, 256);
+  const size_t src_bytes = (resident || dtype == VC_DTYPE_BF16) ? 0 : align_up(n_el * el, 256);
+  const size_t bf_bytes = resident ? 0 : align_up(n_el * 2, 256);
   const size_t cnt_bytes = align_up((size_t)n_images * 4, 256);
   const size_t pair_bytes = align_up((size_t)n_pairs * 8, 256);
   const size_t out_bytes = align_up((size_t)n_pairs * kmax * 8, 256);
@@ -409,8 +442,8 @@ int vc_match_pairs_host(vc_handle* h, const void* desc, int dtype, const int32_t
 
   uint8_t* base = static_cast<uint8_t*>(h->stage);
   uint8_t* d_src = base;
-  uint8_t* d_bf = d_src + src_bytes;
-  int32_t* d_cnt = reinterpret_cast<int32_t*>(d_bf + bf_bytes);
+  uint8_t* d_bf = resident ? static_cast<uint8_t*>(const_cast<void*>(desc)) : d_src + src_bytes;
+  int32_t* d_cnt = reinterpret_cast<int32_t*>(base + src_bytes + bf_bytes);
   int32_t* d_pairs = reinterpret_cast<int32_t*>(reinterpret_cast<uint8_t*>(d_cnt) + cnt_bytes);
   uint32_t* d_out = reinterpret_cast<uint32_t*>(reinterpret_cast<uint8_t*>(d_pairs) + pair_bytes);
   int32_t* d_nm = reinterpret_cast<int32_t*>(reinterpret_cast<uint8_t*>(d_out) + out_bytes);
@@ -422,7 +455,7 @@ int vc_match_pairs_host(vc_handle* h, const void* desc, int dtype, const int32_t
   VC_CUDA(cudaMemcpyAsync(d_pairs, p_pairs, (size_t)n_pairs * 8, cudaMemcpyHostToDevice, s));
   for (int g = 0; g < n_groups; ++g) {
     const int i0 = std::min(n_images, g * per), i1 = std::min(n_images, (g + 1) * per);
-    const size_t off = (size_t)i0 * img_el, cnt = (size_t)(i1 - i0) * img_el;
+    const size_t off = (size_t)i0 * img_el, cnt = resident ? 0 : (size_t)(i1 - i0) * img_el;
     if (cnt) {
       uint8_t* dst = dtype == VC_DTYPE_BF16 ? d_bf : d_src;
       VC_CUDA(cudaMemcpyAsync(dst + off * el, static_cast<const uint8_t*>(desc) + off * el, cnt * el,
@@ -475,6 +508,29 @@ int vc_match_pairs_host(vc_handle* h, const void* desc, int dtype, const int32_t
   }
   VC_CUDA(cudaStreamSynchronize(s));
   return VC_OK;
+}
+
+extern "C" {
+
+int vc_match_pairs_host(vc_handle* h, const void* desc, int dtype, const int32_t* counts,
+                        int n_images, int kmax, int d, const int32_t* pairs, int n_pairs,
+                        const vc_match_options* opt, uint32_t* matches, int32_t* n_matches) {
+  return match_host_impl(h, desc, dtype, false, counts, n_images, kmax, d, pairs, n_pairs, opt, matches,
+                         n_matches);
+}
+
+int vc_match_pairs_resident(vc_handle* h, const void* desc_bf16, const int32_t* counts, int n_images,
+                            int kmax, int d, const int32_t* pairs, int n_pairs,
+                            const vc_match_options* opt, uint32_t* matches, int32_t* n_matches) {
+  if (desc_bf16) {
+    cudaPointerAttributes attr;
+    if (cudaPointerGetAttributes(&attr, desc_bf16) != cudaSuccess || attr.type != cudaMemoryTypeDevice) {
+      cudaGetLastError();
+      return fail(VC_ERR_INVALID, "vc_match_pairs_resident needs a device pointer to bf16 descriptors");
+    }
+  }
+  return match_host_impl(h, desc_bf16, VC_DTYPE_BF16, true, counts, n_images, kmax, d, pairs, n_pairs, opt,
+                         matches, n_matches);
 }
 
 }  // extern "C"

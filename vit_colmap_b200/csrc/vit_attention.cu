@@ -35,6 +35,7 @@
 #include <math.h>
 
 #include "vc_ptx.cuh"
+#include "vc_launch.cuh"
 
 namespace vc {
 
@@ -417,13 +418,8 @@ vit_attention_kernel(const __grid_constant__ CUtensorMap map_qkv, const AttnPara
 int attn_smem_bytes() { return kSmemBytes; }
 
 static cudaError_t launch_items(const CUtensorMap& map_qkv, const AttnParams& p, int num_sms, cudaStream_t stream) {
-  static bool configured = false;
-  if (!configured) {
-    cudaError_t e = cudaFuncSetAttribute(vit_attention_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                         kSmemBytes);
-    if (e != cudaSuccess) return e;
-    configured = true;
-  }
+  static SmemOptIn opt_in;
+  if (cudaError_t e = ensure_dynamic_smem(vit_attention_kernel, kSmemBytes, opt_in); e != cudaSuccess) return e;
   const int q_tiles = (p.T + kTile - 1) / kTile;
   const int total = p.B * p.heads * q_tiles;
   const int grid = (total + 1) / 2 < num_sms ? (total + 1) / 2 : num_sms;

@@ -128,22 +128,34 @@ def match_exhaustive_sharded(image_ids: Sequence[int], match_fn: Callable[[np.nd
     return gather_to_writer(local, 0)
 
 
-def gpu_match_fn(matcher, desc, counts, options, pairs_per_launch: int = 512) -> MatchFn:
-    """match_fn over device-resident descriptors (bf16 [n, K, d]) with the fused sm_100a matcher."""
-    import torch
+def gpu_match_fn(matcher, resident, options, pairs_per_call: int = 1024) -> MatchFn:
+    """match_fn over descriptors resident in HBM (`Matcher.upload`) with the fused sm_100a matcher:
+    per call only the pair list goes up and the packed match lists come back."""
 
     def fn(idx: np.ndarray) -> List[np.ndarray]:
-        out: List[np.ndarray] = []
-        inv = 1.0 if desc.dtype == torch.bfloat16 else None
-        for s in range(0, len(idx), pairs_per_launch):
-            chunk = torch.from_numpy(idx[s:s + pairs_per_launch]).to(desc.device)
-            m, n = matcher.match_pairs(desc, counts, chunk, options.max_ratio, options.max_distance,
-                                       options.cross_check, inv if inv is not None else 1.0)
-            n_h = n.cpu().numpy()
-            m_h = m.cpu().numpy().view(np.uint32)
-            out.extend(m_h[i, : n_h[i]].copy() for i in range(len(n_h)))
-        return out
+        return matcher.match_resident(resident, idx, options.max_ratio, options.max_distance,
+                                      options.cross_check, pairs_per_call)
     return fn
+
+
+def all_gather_objects(obj) -> list:
+    dist = _dist()
+    rank, world = world_info()
+    if world == 1:
+        return [obj]
+    bucket = [None] * world
+    dist.all_gather_object(bucket, obj)
+    return bucket
+
+
+def broadcast_object(obj, src: int = 0):
+    dist = _dist()
+    rank, world = world_info()
+    if world == 1:
+        return obj
+    box = [obj if rank == src else None]
+    dist.broadcast_object_list(box, src=src)
+    return box[0]
 
 
 def extract_and_match(image_dir, db_path, extractor, camera_model: str = "SIMPLE_PINHOLE", camera_params=None,
@@ -154,12 +166,15 @@ def extract_and_match(image_dir, db_path, extractor, camera_model: str = "SIMPLE
 
     Matching runs on the uint8 descriptors -- the bytes COLMAP would read back from the database --
     converted exactly to bf16 on the device (inv_norm = 1/512^2), so the result equals the
-    single-process `extract()` + `match_exhaustive()` pipeline.  Returns the matches dict on rank 0."""
+    single-process `extract()` + `match_exhaustive()` pipeline.  Unreadable files are reported and
+    skipped exactly as `extract()` does (no image row, vit_extractor.py:733-737); image ids are the ones
+    the single writer hands out (the database may already hold images).  Returns the matches dict on
+    rank 0."""
     import cv2
     import torch
     from .database import ColmapDatabase, make_camera
     from .features.base_extractor import default_camera_params, list_images
-    from .matching import FeatureMatchingOptions, Matcher, SQ_SIFT_NORM
+    from .matching import FeatureMatchingOptions, Matcher
     rank, world = world_info()
     options = matching_options or FeatureMatchingOptions()
     files = list_images(image_dir)
@@ -171,60 +186,82 @@ def extract_and_match(image_dir, db_path, extractor, camera_model: str = "SIMPLE
     K, d = extractor.num_keypoints, min(extractor.descriptor_dim, extractor.model.embed_dim)
     needs_pca = extractor.model.embed_dim > extractor.descriptor_dim
 
-    def run_batch(paths):
-        imgs, orig, res = [], None, None
-        for p in paths:
-            im, orig, res = extractor._resize(cv2.imread(str(p)))
-            imgs.append(im)
-        return extractor._extract_batch(imgs, orig, res)[0]
+    def load(i):
+        """(resized image, original size, resized size) or None for a file extract() would skip."""
+        img = cv2.imread(str(files[i]))
+        if img is None:
+            print(f"[{i + 1}/{n}] {files[i].name}: ⚠ Warning: Failed to read image, skipping")
+            return None
+        try:
+            return extractor._resize(img)
+        except Exception as e:  # noqa: BLE001  (vit_extractor.py:757-762: report and go on)
+            print(f"  ✗ Error during feature extraction: {e}")
+            return None
 
-    feats: Dict[int, Tuple[np.ndarray, np.ndarray]] = {}
-    if needs_pca:  # fitted on image 0 by its owner, then shared (vit_extractor.py:601-639)
-        if rank == 0:
-            feats[0] = run_batch([files[0]])[0]
+    def run_batch(items):
+        return extractor._extract_batch([it[0] for it in items], items[0][1], items[0][2])[0]
+
+    if needs_pca:  # fitted on the first readable image by rank 0, then shared (vit_extractor.py:601-639)
+        if rank == 0 and extractor.descriptor_projection is None:
+            for i in range(n):
+                it = load(i)
+                if it is not None:
+                    run_batch([it])
+                    break
         extractor.descriptor_projection = broadcast_projection(extractor.descriptor_projection,
                                                                extractor.model.embed_dim, d, dev)
-    todo = [i for i in range(lo, hi) if i not in feats]
-    for s in range(0, len(todo), extractor.batch_size):
-        chunk = todo[s:s + extractor.batch_size]
-        sizes = {cv2.imread(str(files[i])).shape[:2] for i in chunk} if len(chunk) > 1 else {None}
-        groups = [chunk] if len(sizes) == 1 else [[i] for i in chunk]
-        for g in groups:
-            for i, f in zip(g, run_batch([files[i] for i in g])):
+    feats: Dict[int, Tuple[np.ndarray, np.ndarray]] = {}
+    sizes: Dict[int, Tuple[int, int]] = {}
+    pending: list = []
+
+    def flush():
+        if pending:
+            for (i, _), f in zip(pending, run_batch([it for _, it in pending])):
                 feats[i] = f
-    # uint8 descriptors of this shard, padded to K rows -> one all-gather
+            pending.clear()
+
+    for i in range(lo, hi):
+        it = load(i)
+        if it is None:
+            continue
+        sizes[i] = it[1]
+        if pending and (pending[0][1][1:] != it[1:] or len(pending) == extractor.batch_size):
+            flush()  # a batch holds equally sized images
+        pending.append((i, it))
+    flush()
+    # uint8 descriptors of this shard, padded to K rows -> one all-gather (skipped files keep a
+    # zero-row slot so that the image axis is the file index on every rank)
     desc_local = torch.zeros((hi - lo, K, d), dtype=torch.uint8)
     counts_local = torch.zeros((hi - lo,), dtype=torch.int32)
-    for i in range(lo, hi):
-        m = min(len(feats[i][1]), K)
-        desc_local[i - lo, :m] = torch.from_numpy(feats[i][1][:m])
+    for i, (_, du8) in feats.items():
+        m = min(len(du8), K)
+        desc_local[i - lo, :m] = torch.from_numpy(du8[:m])
         counts_local[i - lo] = m
     desc_u8, counts = all_gather_descriptors(desc_local.to(dev), counts_local.to(dev), n)
     matcher = matcher or Matcher(extractor.device_index)
-    desc = matcher.to_bf16(desc_u8)
+    resident = matcher.upload(desc_u8, counts.cpu().numpy())
 
-    def fn(idx):
-        out = []
-        for s in range(0, len(idx), 512):
-            chunk = torch.from_numpy(idx[s:s + 512]).to(dev)
-            m, nm = matcher.match_pairs(desc, counts, chunk, options.max_ratio, options.max_distance,
-                                        options.cross_check, 1.0 / SQ_SIFT_NORM)
-            nm_h, m_h = nm.cpu().numpy(), m.cpu().numpy().view(np.uint32)
-            out.extend(m_h[k, : nm_h[k]].copy() for k in range(len(nm_h)))
-        return out
-
-    ids = list(range(1, n + 1))  # image ids are assigned in sorted file order by the single writer
-    matches = match_exhaustive_sharded(ids, fn, block_size, options.min_num_matches)
+    # rank 0 is the single writer: camera + image rows first, so that matching uses the ids it got
+    size_of = dict(kv for part in all_gather_objects(sorted(sizes.items())) for kv in part)
+    readable = sorted(size_of)
+    db, file_ids = None, None
+    if rank == 0:
+        if not readable:
+            raise ValueError(f"Failed to read any image in {image_dir}")
+        db = ColmapDatabase(str(db_path))
+        w, h = size_of[readable[0]]
+        params = camera_params if camera_params is not None else default_camera_params(camera_model, w, h)
+        cam = db.db.write_camera(make_camera(camera_model, w, h, params))
+        file_ids = [(i, db.add_image(files[i].name, camera_id=cam)) for i in readable]
+    file_ids = broadcast_object(file_ids, 0)
+    file_of_pos = np.array([i for i, _ in file_ids], dtype=np.int32)
+    inner = gpu_match_fn(matcher, resident, options)
+    matches = match_exhaustive_sharded([image_id for _, image_id in file_ids],
+                                       lambda idx: inner(file_of_pos[idx]), block_size, options.min_num_matches)
     all_feats = gather_to_writer(feats, 0)
     if rank != 0:
         return None
-    db = ColmapDatabase(str(db_path))
-    first = cv2.imread(str(files[0]))
-    h, w = first.shape[:2]
-    params = camera_params if camera_params is not None else default_camera_params(camera_model, w, h)
-    cam = db.db.write_camera(make_camera(camera_model, w, h, params))
-    for i, f in enumerate(files):
-        image_id = db.add_image(f.name, camera_id=cam)
+    for i, image_id in file_ids:
         kps, du8 = all_feats[i]
         if len(kps):
             db.add_keypoints(image_id, kps)

@@ -10,7 +10,7 @@ from __future__ import annotations
 
 import ctypes
 from dataclasses import dataclass
-from typing import Optional, Sequence
+from typing import List, Optional, Sequence
 
 import numpy as np
 
@@ -170,7 +170,8 @@ class Matcher:
         n_images, kmax, d = desc.shape
         n_pairs = pairs.shape[0]
         if rule == "l2":
-            return self._match_pairs_host_l2(desc, counts, pairs, max_ratio, max_distance, cross_check)
+            resident = self.upload(desc, counts, rule="l2")
+            return self.match_resident(resident, pairs, max_ratio, max_distance, cross_check)
         if rule != "angular":
             raise ValueError(f"unknown matching rule {rule!r} (angular | l2)")
         if desc.dtype == np.uint8:
@@ -192,123 +193,197 @@ class Matcher:
                                                 matches.ctypes.data, n_matches.ctypes.data))
         return [matches[i, :n_matches[i]].copy() for i in range(n_pairs)]
 
+    # ------------------------------------------------------------------ upload once, match many
+    def upload(self, desc, counts, rule: str = "angular", inv_norm: Optional[float] = None) -> "ResidentDescriptors":
+        """Make a padded descriptor set resident in HBM as the matcher's bf16 operand -- ONCE; every
+        later pair chunk only sends its pair list (vc_match_pairs_resident).  `desc`: host ndarray or
+        torch tensor (host or this device), uint8 / float32 / bf16, [n_images, kmax, d]; `counts`: host
+        int32 [n_images].  COLMAP's GPU matcher re-uploads descriptors per pair instead
+        (COLMAP/feature/sift.cc:1270-1284).
 
-    def _match_pairs_host_l2(self, desc, counts, pairs, max_ratio, max_distance, cross_check):
-        """Squared-L2 nearest neighbours through the SAME fused GEMM kernel: the descriptors are
-        augmented so that the dot product of an image-1 row with an image-2 row is exactly
-        K - |x - y|^2.  The two roles need different augmentations (K - d^2 is not a Gram matrix), so
-        the image axis is doubled: copies [0, n) play image 1, copies [n, 2n) image 2.
-            image 1: [2x, D0, D1, D2, 1, 1, 1, 1]             (|x|^2 = D0 + 256 D1 + 65536 D2)
-            image 2: [ y, -1, -256, -65536, -E0, -256 E1, -65536 E2, K]   (|y|^2 = E0 + 256 E1 + 65536 E2)
-        Every entry is an integer bf16 represents exactly and every partial sum stays below 2^24
-        (K = power of two > 2 max|x|^2 >= max d^2, required <= 2^23), so fp32 accumulation is exact
-        and ties resolve as in COLMAP (first minimum wins)."""
-        if desc.dtype != np.uint8:
-            raise TypeError("rule 'l2' is defined for uint8 descriptors (COLMAP FeatureDescriptors)")
-        n_images, kmax, d = desc.shape
-        x = desc.astype(np.int64)
-        norm2 = (x * x).sum(axis=2)
-        mask = np.arange(kmax)[None, :] < counts[:, None]
-        max_norm2 = int((norm2 * mask).max()) if mask.any() else 0
-        K = 1 << max(int(2 * max_norm2 + 1).bit_length(), 1)
-        if K > (1 << 23):
-            raise ValueError("descriptor norms too large for the exact l2 rule (need 2*max|x|^2 < 2^23)")
-        dig = np.stack([norm2 & 255, (norm2 >> 8) & 255, norm2 >> 16], axis=2).astype(np.float32)
-        aug = np.zeros((2 * n_images, kmax, d + 8), dtype=np.float32)
-        aug[:n_images, :, :d] = 2.0 * desc
-        aug[:n_images, :, d:d + 3] = dig
-        aug[:n_images, :, d + 3:d + 7] = 1.0
-        aug[n_images:, :, :d] = desc
-        aug[n_images:, :, d:d + 3] = np.array([-1.0, -256.0, -65536.0], np.float32)
-        aug[n_images:, :, d + 3:d + 6] = -dig * np.array([1.0, 256.0, 65536.0], np.float32)
-        aug[n_images:, :, d + 6] = float(K)
-        import torch
-        bits = torch.from_numpy(aug).to(torch.bfloat16).view(torch.int16).numpy().view(np.uint16)
-        assert np.array_equal(torch.from_numpy(bits.view(np.int16)).view(torch.bfloat16).float().numpy(), aug)
-        counts2 = np.concatenate([counts, counts]).astype(np.int32)
-        pairs2 = np.stack([pairs[:, 0], pairs[:, 1] + n_images], axis=1).astype(np.int32)
-        n_pairs = pairs2.shape[0]
-        matches = np.empty((max(n_pairs, 1), kmax, 2), dtype=np.uint32)
-        n_matches = np.zeros((max(n_pairs, 1),), dtype=np.int32)
-        opt = self._opts(max_ratio, max_distance, cross_check, 1.0 / SQ_SIFT_NORM, 1, float(K))
-        _lib.check(self.lib.vc_match_pairs_host(self.handle, bits.ctypes.data, _lib.DTYPE_BF16, counts2.ctypes.data,
-                                                2 * n_images, kmax, d + 8, pairs2.ctypes.data, n_pairs,
-                                                ctypes.byref(opt), matches.ctypes.data, n_matches.ctypes.data))
-        return [matches[i, :n_matches[i]].copy() for i in range(n_pairs)]
+        rule "l2" (uint8 only): the rows are augmented on the device (vc_l2_augment) so that the dot
+        product of image-1 copy i with image-2 copy n+j is K - |x - y|^2 exactly."""
+        torch = self.torch
+        if rule not in ("angular", "l2"):
+            raise ValueError(f"unknown matching rule {rule!r} (angular | l2)")
+        if isinstance(desc, np.ndarray):
+            if desc.dtype == np.uint16:  # raw bf16 bit patterns
+                t = torch.from_numpy(np.ascontiguousarray(desc).view(np.int16)).view(torch.bfloat16)
+            else:
+                t = torch.from_numpy(np.ascontiguousarray(desc))
+        else:
+            t = desc
+        if t.dim() != 3:
+            raise ValueError("descriptors must be [n_images, kmax, d]")
+        if t.dtype not in (torch.uint8, torch.float32, torch.bfloat16):
+            raise TypeError("descriptors must be uint8, float32 or bf16")
+        counts = np.ascontiguousarray(counts, dtype=np.int32)
+        n_images, kmax, d = (int(v) for v in t.shape)
+        if counts.shape != (n_images,):
+            raise ValueError("counts must be int32 [n_images]")
+        is_u8 = t.dtype == torch.uint8
+        if t.device.type != "cuda":
+            if not t.is_pinned() and t.numel() >= (1 << 20):
+                pinned = torch.empty(t.shape, dtype=t.dtype, pin_memory=True)
+                pinned.copy_(t)
+                t = pinned
+            t = t.to(self._dev(), non_blocking=True)
+        t = t.contiguous()
+        if rule == "l2":
+            if not is_u8:
+                raise TypeError("rule 'l2' is defined for uint8 descriptors (COLMAP FeatureDescriptors)")
+            out = torch.empty((2 * n_images, kmax, d + 8), dtype=torch.bfloat16, device=t.device)
+            k = ctypes.c_float(0.0)
+            _lib.check(self.lib.vc_l2_augment(self.handle, _ptr(t), n_images, kmax, d, _ptr(out), ctypes.byref(k),
+                                              self._stream()))
+            res = ResidentDescriptors(out, np.concatenate([counts, counts]), n_images, 1.0 / SQ_SIFT_NORM, 1,
+                                      float(k.value), n_images)
+        else:
+            inv = inv_norm if inv_norm is not None else (1.0 / SQ_SIFT_NORM if is_u8 else 1.0)
+            res = ResidentDescriptors(self.to_bf16(t), counts, n_images, inv, 0, 0.0, 0)
+        torch.cuda.current_stream(self._dev()).synchronize()  # the C entry runs on the handle's own streams
+        return res
+
+    def match_resident(self, resident: "ResidentDescriptors", pairs, max_ratio=0.8, max_distance=0.7,
+                       cross_check=True, pairs_per_call: int = 1024) -> List[np.ndarray]:
+        """Match index pairs [n, 2] (into the uploaded image axis) against resident descriptors.
+        Only the pair list goes up and only the packed match lists come back."""
+        pairs = np.ascontiguousarray(pairs, dtype=np.int32).reshape(-1, 2)
+        if pairs.size and (pairs.min() < 0 or pairs.max() >= resident.n_images):
+            raise ValueError("pair index outside the uploaded image range")
+        desc = resident.desc
+        n_dev, kmax, d = (int(v) for v in desc.shape)
+        opt = self._opts(max_ratio, max_distance, cross_check, resident.inv_norm, resident.rule, resident.l2_offset)
+        out: List[np.ndarray] = []
+        for s in range(0, pairs.shape[0], pairs_per_call):
+            chunk = pairs[s:s + pairs_per_call].copy()
+            chunk[:, 1] += resident.second_offset
+            n = chunk.shape[0]
+            matches = np.empty((n, kmax, 2), dtype=np.uint32)
+            n_matches = np.zeros((n,), dtype=np.int32)
+            _lib.check(self.lib.vc_match_pairs_resident(self.handle, _ptr(desc), resident.counts.ctypes.data, n_dev,
+                                                        kmax, d, chunk.ctypes.data, n, ctypes.byref(opt),
+                                                        matches.ctypes.data, n_matches.ctypes.data))
+            out.extend(matches[i, :n_matches[i]].copy() for i in range(n))
+        return out
+
+
+@dataclass
+class ResidentDescriptors:
+    """Descriptors of a set of images as the matcher reads them: bf16 [n_dev, kmax, d] in HBM."""
+    desc: object               # torch bf16 tensor on the matcher's device
+    counts: np.ndarray         # host int32 [n_dev]
+    n_images: int              # images the caller uploaded (n_dev = 2 * n_images under rule l2)
+    inv_norm: float
+    rule: int                  # vc_match_options.rule
+    l2_offset: float
+    second_offset: int         # added to the image-2 index of every pair (rule l2: its role-2 copy)
+
+    @property
+    def nbytes(self) -> int:
+        return int(self.desc.numel()) * 2
+
+
+def pad_descriptors(descriptors: Sequence[np.ndarray], max_rows: int, pinned: bool = True):
+    """Ragged list of [n_i, d] uint8 / float32 arrays -> (padded [n, kmax, d] torch host tensor, counts).
+    The buffer is written once, directly in page-locked memory, so the upload is one DMA."""
+    import torch
+    n_images = len(descriptors)
+    d = max((int(x.shape[1]) for x in descriptors if x.ndim == 2 and x.shape[0] > 0), default=128)
+    is_u8 = all(x.dtype == np.uint8 for x in descriptors)
+    kmax = max(max((int(x.shape[0]) for x in descriptors if x.ndim == 2), default=0), 1)
+    kmax = min(kmax, max_rows)  # SIFTGPU/SiftMatchCU.cpp:108 clamps inputs likewise
+    use_pin = pinned and torch.cuda.is_available()
+    buf = torch.zeros((n_images, kmax, d), dtype=torch.uint8 if is_u8 else torch.float32, pin_memory=use_pin)
+    view = buf.numpy()
+    counts = np.zeros((n_images,), dtype=np.int32)
+    for i, x in enumerate(descriptors):
+        n = min(int(x.shape[0]), kmax) if x.ndim == 2 else 0
+        counts[i] = n
+        if n:
+            view[i, :n] = x[:n]
+    return buf, counts
+
 
 def match_descriptor_sets(descriptors: Sequence[np.ndarray], pairs, options: Optional[FeatureMatchingOptions] = None,
                           matcher: Optional[Matcher] = None, device: int = 0):
     """Match host descriptor arrays (ragged list of [n_i, d] uint8 or float32) for the given index
-    pairs.  Pads to a common kmax, calls the host-buffer C entry, returns list of [n,2] uint32."""
+    pairs: pad + upload ONCE, then match every pair on the resident set.  Returns list of [n,2] uint32."""
     options = options or FeatureMatchingOptions()
     matcher = matcher or Matcher(device)
-    n_images = len(descriptors)
-    d = max((int(x.shape[1]) for x in descriptors if x.ndim == 2 and x.shape[0] > 0), default=128)
-    dtype = np.uint8 if all(x.dtype == np.uint8 for x in descriptors) else np.float32
-    kmax = max(max((int(x.shape[0]) for x in descriptors), default=0), 1)
-    kmax = min(kmax, options.max_num_matches)  # SIFTGPU/SiftMatchCU.cpp:108 clamps inputs likewise
-    buf = np.zeros((n_images, kmax, d), dtype=dtype)
-    counts = np.zeros((n_images,), dtype=np.int32)
-    for i, x in enumerate(descriptors):
-        n = min(int(x.shape[0]), kmax)
-        counts[i] = n
-        if n:
-            buf[i, :n] = x[:n]
+    buf, counts = pad_descriptors(descriptors, options.max_num_matches)
     rule = getattr(options, "rule", "angular")
-    if rule == "l2" and dtype != np.uint8:
-        raise TypeError("rule 'l2' is defined for uint8 descriptors")
-    return matcher.match_pairs_host(buf, counts, np.asarray(pairs, dtype=np.int32),
-                                    options.max_ratio, options.max_distance, options.cross_check, rule=rule)
+    resident = matcher.upload(buf, counts, rule=rule)
+    return matcher.match_resident(resident, np.asarray(pairs, dtype=np.int32), options.max_ratio,
+                                  options.max_distance, options.cross_check)
 
 
 def match_exhaustive(database_path, matching_options: Optional[FeatureMatchingOptions] = None,
                      pairing_options=None, verification_options=None, device=None, *,
                      matcher: Optional[Matcher] = None, rank: int = 0, world_size: int = 1,
-                     pairs_per_launch: int = 256):
+                     pairs_per_launch: int = 1024, max_resident_bytes: Optional[int] = None):
     """Drop-in for ``pycolmap.match_exhaustive(database_path, matching_options, ...)`` restricted to
     the matching half (PYCOLMAP/pipeline/match_features.cc:28-51; geometric verification stays with
     pycolmap and is invoked afterwards when pycolmap is importable).
 
-    Reads ``descriptors`` rows, generates exhaustive pairs block-wise (pairing.cc:202-236), matches
-    every block on the GPU and writes ``matches`` rows: pairs with fewer than ``min_num_matches``
-    matches are written empty (controllers/feature_matching_utils.cc:485-488), pairs that already
-    have a row are skipped (:443-449).  With world_size > 1 each rank matches its share of the pair
-    blocks (no collective); only rank 0's caller should write -- use ``return_only=True`` style via
-    the returned dict to gather.  Returns {(image_id1, image_id2): matches[n,2] uint32}.
+    Reads ``descriptors`` rows, uploads them ONCE (COLMAP's matcher cache + per-pair upload,
+    COLMAP/feature/matcher.cc:71-151 and sift.cc:1270-1284, become one resident bf16 tensor), generates
+    exhaustive pairs block-wise (pairing.cc:202-236), matches every block on the GPU and writes
+    ``matches`` rows: pairs with fewer than ``min_num_matches`` matches are written empty
+    (controllers/feature_matching_utils.cc:485-488), pairs that already have a row are skipped
+    (:443-449).  If the padded set exceeds ``max_resident_bytes`` (default: 60 % of the free device
+    memory) the upload happens per pairing block instead (the <= 2 x block_size images a block names),
+    still once per block rather than once per pair chunk.  With world_size > 1 each rank matches its
+    share of the pair blocks (no collective); only a single-process call writes.
+    Returns {(image_id1, image_id2): matches[n,2] uint32}.
     """
     from .database import Database
     options = matching_options or FeatureMatchingOptions()
     block_size = int(getattr(pairing_options, "block_size", 50)) if pairing_options is not None else 50
-    if isinstance(device, int):
-        dev_index = device
-    else:
-        dev_index = 0
+    dev_index = device if isinstance(device, int) else 0
     matcher = matcher or Matcher(dev_index)
+    rule = getattr(options, "rule", "angular")
     results = {}
     with Database.open(str(database_path)) as db:
         images = db.read_all_images()
         ids = [im.image_id for im in images]
         desc = {i: db.read_descriptors(i) for i in ids}
         desc = {i: (v if v.ndim == 2 and v.shape[0] > 0 else np.zeros((0, 128), np.uint8)) for i, v in desc.items()}
-        index_of = {i: k for k, i in enumerate(ids)}
         gen = ExhaustivePairGenerator(ids, block_size)
-        todo = []
-        for pair in gen.all_pairs():
-            if db.exists_matches(pair[0], pair[1]):  # resume semantics
-                continue
-            todo.append(pair)
-        lo = len(todo) * rank // world_size
-        hi = len(todo) * (rank + 1) // world_size
-        mine = todo[lo:hi]
-        arrays = [desc[i] for i in ids]
-        for s in range(0, len(mine), pairs_per_launch):
-            chunk = mine[s:s + pairs_per_launch]
-            idx_pairs = np.array([(index_of[a], index_of[b]) for a, b in chunk], dtype=np.int32)
-            out = match_descriptor_sets(arrays, idx_pairs, options, matcher)
-            for (a, b), m in zip(chunk, out):
-                if m.shape[0] < options.min_num_matches:
-                    m = np.zeros((0, 2), np.uint32)
-                results[(a, b)] = m
+        blocks = [[p for p in blk if not db.exists_matches(p[0], p[1])] for blk in gen.blocks()]  # resume semantics
+        n_todo = sum(len(b) for b in blocks)
+        lo, hi = n_todo * rank // world_size, n_todo * (rank + 1) // world_size
+        mine, seen = [], 0
+        for blk in blocks:  # this rank's contiguous share of the pair list, still grouped by block
+            part = blk[max(lo - seen, 0):max(hi - seen, 0)]
+            seen += len(blk)
+            if part:
+                mine.append(part)
+
+        def run(block_list, image_ids):
+            index_of = {i: k for k, i in enumerate(image_ids)}
+            buf, counts = pad_descriptors([desc[i] for i in image_ids], options.max_num_matches)
+            resident = matcher.upload(buf, counts, rule=rule)
+            for blk in block_list:
+                idx = np.array([(index_of[a], index_of[b]) for a, b in blk], dtype=np.int32)
+                out = matcher.match_resident(resident, idx, options.max_ratio, options.max_distance,
+                                             options.cross_check, pairs_per_launch)
+                for (a, b), m in zip(blk, out):
+                    results[(a, b)] = m if m.shape[0] >= options.min_num_matches else np.zeros((0, 2), np.uint32)
+
+        if mine:
+            kmax = min(max(max((int(v.shape[0]) for v in desc.values()), default=1), 1), options.max_num_matches)
+            dmax = max((int(v.shape[1]) for v in desc.values()), default=128)
+            need = len(ids) * kmax * (dmax + 8) * 2 * (2 if rule == "l2" else 1) + len(ids) * kmax * dmax
+            if max_resident_bytes is None:
+                free, _total = matcher.torch.cuda.mem_get_info(matcher._dev())
+                max_resident_bytes = int(free * 0.6)
+            if need <= max_resident_bytes:
+                run(mine, ids)
+            else:
+                for blk in mine:
+                    used = sorted({i for pr in blk for i in pr}, key=ids.index)
+                    run([blk], used)
         if rank == 0 and world_size == 1:
             with db.transaction():
                 for (a, b), m in results.items():

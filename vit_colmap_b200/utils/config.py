@@ -1,17 +1,17 @@
-"""Configuration dataclasses of the pipeline: same fields, defaults and methods as the reference's
-``vit_colmap/utils/config.py`` (:9-198).  Where the reference hands pycolmap option objects out,
-this mirror returns pycolmap's when pycolmap is importable and the equivalent plain dataclass of
-``vit_colmap_b200.matching`` otherwise (pycolmap is not installed in the build image)."""
+"""Pipeline configuration.  Field names, defaults and method names follow the reference's
+``vit_colmap/utils/config.py`` (:9-198) because they ARE the interface (``Config.from_args``,
+``config.matching.to_matching_options()``, ``config.extractor.extractor_type`` ...); the bodies are
+this package's own: argparse mapping is table driven, camera defaults come from the extractor base
+module, and pycolmap objects are only built in ``pycolmap_bridge`` (pycolmap is not in the image)."""
 from __future__ import annotations
 
 import logging
 from dataclasses import dataclass, field
 from typing import Optional
 
-try:  # pragma: no cover - absent in the build image
-    import pycolmap
-except Exception:  # noqa: BLE001
-    pycolmap = None
+from . import pycolmap_bridge
+
+pycolmap = pycolmap_bridge.pycolmap
 
 
 @dataclass
@@ -21,7 +21,7 @@ class LogConfig:
     datefmt: str = "%H:%M:%S"
 
     def apply(self):
-        logging.basicConfig(level=self.level, format=self.format, datefmt=self.datefmt, force=True)
+        logging.basicConfig(force=True, **{k: getattr(self, k) for k in ("level", "format", "datefmt")})
 
 
 @dataclass
@@ -32,14 +32,14 @@ class CameraConfig:
     params: Optional[list[float]] = None
 
     def get_default_params(self, width: int, height: int) -> list[float]:
+        """Explicit params win; otherwise f = max(w, h) and the principal point at the image centre
+        (SIMPLE_PINHOLE / PINHOLE only -- anything else raises ValueError, as in the reference)."""
         if self.params is not None:
             return self.params
-        f = max(width, height)
-        if self.model == "SIMPLE_PINHOLE":
-            return [f, width / 2.0, height / 2.0]
-        if self.model == "PINHOLE":
-            return [f, f, width / 2.0, height / 2.0]
-        raise ValueError(f"Unsupported camera model: {self.model}")
+        from ..features.base_extractor import default_camera_params
+        if self.model not in ("SIMPLE_PINHOLE", "PINHOLE"):
+            raise ValueError(f"Unsupported camera model: {self.model}")
+        return default_camera_params(self.model, width, height)
 
 
 @dataclass
@@ -50,27 +50,17 @@ class MatchingConfig:
     cross_check: bool = True
     num_threads: int = -1
 
+    def _thresholds(self) -> dict:
+        return dict(max_ratio=self.max_ratio, max_distance=self.max_distance, cross_check=self.cross_check)
+
     def to_matching_options(self):
-        """Options object for ``match_exhaustive`` (config.py:64-96 in the reference)."""
+        """What ``vit_colmap_b200.matching.match_exhaustive`` takes (reference: config.py:64-96 builds
+        the pycolmap object; see to_pycolmap_options for that one)."""
         from ..matching import FeatureMatchingOptions
-        return FeatureMatchingOptions(use_gpu=self.use_gpu, num_threads=self.num_threads, max_ratio=self.max_ratio,
-                                      max_distance=self.max_distance, cross_check=self.cross_check)
+        return FeatureMatchingOptions(use_gpu=self.use_gpu, num_threads=self.num_threads, **self._thresholds())
 
     def to_pycolmap_options(self):
-        """The pycolmap object the reference builds; only available with pycolmap installed."""
-        if pycolmap is None:
-            raise ImportError("pycolmap is not installed")
-        if hasattr(pycolmap, "FeatureMatchingOptions"):
-            opts = pycolmap.FeatureMatchingOptions()
-            if hasattr(opts, "use_gpu"):
-                opts.use_gpu = self.use_gpu
-            if hasattr(opts, "num_threads"):
-                opts.num_threads = self.num_threads
-            target = opts.sift
-        else:
-            opts = target = pycolmap.SiftMatchingOptions()
-        target.max_ratio, target.max_distance, target.cross_check = self.max_ratio, self.max_distance, self.cross_check
-        return opts
+        return pycolmap_bridge.matching_options(self.use_gpu, self.num_threads, **self._thresholds())
 
 
 @dataclass
@@ -79,23 +69,29 @@ class ReconstructionConfig:
     multiple_models: bool = True
 
     def to_mapper_options(self):
-        if pycolmap is None:
-            raise ImportError("3D reconstruction is delegated to pycolmap.incremental_mapping, which is not installed")
-        opts = pycolmap.IncrementalPipelineOptions()
-        opts.min_num_matches = self.min_num_matches
-        opts.multiple_models = self.multiple_models
-        return opts
+        return pycolmap_bridge.mapper_options(min_num_matches=self.min_num_matches,
+                                              multiple_models=self.multiple_models)
 
 
 @dataclass
 class ExtractorConfig:
     extractor_type: str = "vit"  # "vit" | "trainable_vit" | "dummy" | "colmap_sift"
     vit_weights_path: Optional[str] = None
-    # extensions (reference hard-codes these at the call site, run_pipeline.py:329-339)
+    # not in the reference's dataclass: it hard-codes these where the extractor is built
+    # (run_pipeline.py:329-339); same defaults
     model_name: str = "dinov2_vitb14"
     num_keypoints: int = 2048
     descriptor_dim: int = 128
     batch_size: int = 32
+
+
+# argparse attribute -> (section, field, transform); first truthy source of a group wins
+_ARG_TABLE = (
+    (("camera_model",), "camera", "model", None, False),
+    (("extractor",), "extractor", "extractor_type", None, True),
+    (("vit_weights", "model"), "extractor", "vit_weights_path", str, True),
+    (("use_gpu",), "matching", "use_gpu", None, False),
+)
 
 
 @dataclass
@@ -113,36 +109,35 @@ class Config:
 
     @classmethod
     def from_args(cls, args):
-        config = cls()
-        if hasattr(args, "camera_model"):
-            config.camera.model = args.camera_model
-        if getattr(args, "extractor", None):
-            config.extractor.extractor_type = args.extractor
-        elif getattr(args, "use_colmap_sift", False):
-            config.extractor.extractor_type = "colmap_sift"
-        if getattr(args, "vit_weights", None):
-            config.extractor.vit_weights_path = str(args.vit_weights)
-        elif getattr(args, "model", None):
-            config.extractor.vit_weights_path = str(args.model)
-        if hasattr(args, "use_gpu"):
-            config.matching.use_gpu = args.use_gpu
-        if hasattr(args, "skip_matching"):
-            config.do_matching = not args.skip_matching
-        if hasattr(args, "skip_reconstruction"):
-            config.do_reconstruction = not args.skip_reconstruction
+        """argparse namespace of ``run_pipeline.main`` -> Config (reference: config.py:152-181).
+        ``--extractor`` beats the legacy ``--use-colmap-sift``; ``--vit-weights`` beats ``--model``."""
+        cfg = cls()
+        for sources, section, name, cast, need_truthy in _ARG_TABLE:
+            for src in sources:
+                if not hasattr(args, src):
+                    continue
+                value = getattr(args, src)
+                if need_truthy and not value:
+                    continue
+                setattr(getattr(cfg, section), name, cast(value) if cast else value)
+                break
+        if not getattr(args, "extractor", None) and getattr(args, "use_colmap_sift", False):
+            cfg.extractor.extractor_type = "colmap_sift"
+        for flag, attr in (("skip_matching", "do_matching"), ("skip_reconstruction", "do_reconstruction")):
+            if hasattr(args, flag):
+                setattr(cfg, attr, not getattr(args, flag))
         if getattr(args, "verbose", False):
-            config.log.level = logging.DEBUG
-            config.log.apply()
-        return config
+            cfg.log.level = logging.DEBUG
+            cfg.log.apply()
+        return cfg
 
     def summary(self) -> str:
-        onoff = lambda b: "enabled" if b else "disabled"  # noqa: E731
-        return "\n".join([
-            "Configuration:",
-            f"  Extractor: {self.extractor.extractor_type}",
-            f"  Camera model: {self.camera.model}",
-            f"  Matching: {onoff(self.do_matching)}",
-            f"  Reconstruction: {onoff(self.do_reconstruction)}",
-            f"  GPU matching: {onoff(self.matching.use_gpu)}",
-            f"  Min matches: {self.reconstruction.min_num_matches}",
-        ])
+        rows = (("Extractor", self.extractor.extractor_type), ("Camera model", self.camera.model),
+                ("Matching", self.do_matching), ("Reconstruction", self.do_reconstruction),
+                ("GPU matching", self.matching.use_gpu), ("Min matches", self.reconstruction.min_num_matches))
+        text = ["Configuration:"]
+        for label, value in rows:
+            if isinstance(value, bool):
+                value = "enabled" if value else "disabled"
+            text.append(f"  {label}: {value}")
+        return "\n".join(text)
