@@ -99,6 +99,39 @@ int vc_match_pairs_top2(vc_handle* h, const void* desc, const int32_t* counts, i
                         const vc_match_options* opt, float* best, float* second, int32_t* index,
                         void* workspace, size_t workspace_bytes, void* stream);
 
+/*
+ * Guided matching: the same exhaustive search with a geometric gate on every candidate
+ * (i, j): keypoint i of image 1 and keypoint j of image 2 must agree with the pair's two-view geometry
+ * within `max_error` pixels, otherwise the candidate does not take part (angular rule: score 0; l2 rule:
+ * squared distance 512^2).  The gate is evaluated in the GEMM epilogue on the accumulator tile -- the
+ * dot matrix is never written, where SIFTGPU's MultiplyDescriptorG_Kernel writes it gated to HBM.
+ *   keypoints : device f32 [n_images (n_images / 2 under rule l2), kmax, 2] = (x, y) per descriptor row
+ *   geometry  : device vc_pair_geometry [n_pairs]
+ * mode VC_GUIDED_SIFTGPU: keep iff |hnorm(H p1) - p2|^2 < max_h AND (p2^T F p1)^2 / (|F p1|_xy^2 +
+ *   |F^T p2|_xy^2) < max_f  (ProgramCU.cu:1573-1600; an absent H or F is passed as identity with bound
+ *   1e20, SiftMatch.cpp:676-689);
+ * mode VC_GUIDED_F / VC_GUIDED_H: COLMAP's CPU MatchGuided (feature/sift.cc:1093-1122): one test by
+ *   TwoViewGeometry::config, a candidate is dropped iff its residual is > the bound.
+ * Every residual operation is a separately rounded fp32 op (documented in match_kernel.cuh); candidates
+ * whose residual is within rounding of the bound are the only place results may differ from a build of
+ * the reference with other FMA contraction.
+ * Replaces: SiftMatchGPU::GetGuidedSiftMatch (SIFTGPU/SiftMatchCU.cpp:148-159, ProgramCU.cu:1521-1663),
+ * SiftCPUFeatureMatcher::MatchGuided (COLMAP/feature/sift.cc:1058-1157), as driven by
+ * COLMAP/controllers/feature_matching_utils.cc:129-146.
+ */
+enum { VC_GUIDED_SIFTGPU = 0, VC_GUIDED_F = 1, VC_GUIDED_H = 2 };
+typedef struct {
+  float h[9];      /* row-major homography, image 1 -> image 2 (TwoViewGeometry::H) */
+  float f[9];      /* row-major fundamental matrix, p2^T F p1 (TwoViewGeometry::F) */
+  int32_t mode;
+  float max_h;     /* max_error^2 (1e20 when H is absent under VC_GUIDED_SIFTGPU) */
+  float max_f;
+} vc_pair_geometry;
+int vc_match_pairs_guided(vc_handle* h, const void* desc, const float* keypoints, const int32_t* counts,
+                          int n_images, int kmax, int d, const int32_t* pairs, const vc_pair_geometry* geometry,
+                          int n_pairs, const vc_match_options* opt, uint32_t* matches, int32_t* n_matches,
+                          void* workspace, size_t workspace_bytes, void* stream);
+
 /* Test hook: dense score matrix of ONE pair through the same TMA/tcgen05 main loop.
  * scores: device float [kmax, ld] (only [count1, count2] written). */
 int vc_debug_scores(vc_handle* h, const void* desc, const int32_t* counts, int n_images, int kmax,

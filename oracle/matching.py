@@ -186,7 +186,7 @@ def match_python(desc1, desc2, max_ratio=0.8, max_distance=0.7, cross_check=True
     return np.asarray(out, dtype=np.uint32).reshape(-1, 2)
 
 
-def match_l2_numpy(desc1, desc2, max_ratio=0.8, max_distance=0.7, cross_check=True):
+def match_l2_numpy(desc1, desc2, max_ratio=0.8, max_distance=0.7, cross_check=True, filtered=None):
     """FindBestMatchesIndex / FindBestMatchesOneWayIndex (COLMAP/feature/sift.cc:827-915) with the
     index replaced by an exact search: uint8 descriptors, squared L2 distances (exact in int64),
     first minimum wins (strict '<'), best > 512^2 * max_distance^2 rejected, sqrt(best) >=
@@ -196,6 +196,8 @@ def match_l2_numpy(desc1, desc2, max_ratio=0.8, max_distance=0.7, cross_check=Tr
     if a.shape[0] == 0 or b.shape[0] == 0:
         return np.zeros((0, 2), np.uint32)
     d2 = (a * a).sum(1)[:, None] + (b * b).sum(1)[None, :] - 2 * (a @ b.T)
+    if filtered is not None:  # guided matching: ComputeSiftDistanceMatrix(L2, guided_filter), sift.cc:945-946
+        d2 = np.where(filtered, np.int64(SQ_SIFT_NORM), d2)
     max_l2 = np.float32(SQ_SIFT_NORM) * np.float32(max_distance) * np.float32(max_distance)
 
     def one_way(mat):
@@ -219,6 +221,75 @@ def match_l2_numpy(desc1, desc2, max_ratio=0.8, max_distance=0.7, cross_check=Tr
     else:
         keep = [(i, j) for i, j in enumerate(m12) if j >= 0]
     return np.array(keep, dtype=np.uint32).reshape(-1, 2)
+
+
+# TwoViewGeometry::ConfigurationType values that carry F resp. H (scene/two_view_geometry.h:40-61)
+F_CONFIGS, H_CONFIGS = (2, 9, 3), (4, 5, 6)
+
+
+def guided_residuals(H, F, kp1, kp2):
+    """fp32 residuals of every candidate (i, j), each operation separately rounded (numpy float32):
+    hd[i, j] = |hnormalized(H p1_i) - p2_j|^2                      (sift.cc:1116-1121, ProgramCU.cu:1576-1583)
+    se[i, j] = (p2_j^T F p1_i)^2 / (Fp1_x^2 + Fp1_y^2 + Ftp2_x^2 + Ftp2_y^2)   (sift.cc:1099-1110, ProgramCU.cu:1586-1597)"""
+    f32 = np.float32
+    H, F = np.asarray(H, f32).reshape(3, 3), np.asarray(F, f32).reshape(3, 3)
+    x1, y1 = np.asarray(kp1, f32)[:, 0][:, None], np.asarray(kp1, f32)[:, 1][:, None]
+    x2, y2 = np.asarray(kp2, f32)[:, 0][None, :], np.asarray(kp2, f32)[:, 1][None, :]
+    with np.errstate(all="ignore"):
+        a = (H[0, 0] * x1 + H[0, 1] * y1) + H[0, 2]
+        b = (H[1, 0] * x1 + H[1, 1] * y1) + H[1, 2]
+        c = (H[2, 0] * x1 + H[2, 1] * y1) + H[2, 2]
+        dx, dy = a / c - x2, b / c - y2
+        hd = dx * dx + dy * dy
+        fx0 = (F[0, 0] * x1 + F[0, 1] * y1) + F[0, 2]
+        fx1 = (F[1, 0] * x1 + F[1, 1] * y1) + F[1, 2]
+        fx2 = (F[2, 0] * x1 + F[2, 1] * y1) + F[2, 2]
+        ft0 = (F[0, 0] * x2 + F[1, 0] * y2) + F[2, 0]
+        ft1 = (F[0, 1] * x2 + F[1, 1] * y2) + F[2, 1]
+        e = (x2 * fx0 + y2 * fx1) + fx2
+        den = ((fx0 * fx0 + fx1 * fx1) + ft0 * ft0) + ft1 * ft1
+        se = (e * e) / den
+    assert hd.dtype == f32 and se.dtype == f32
+    return hd, se
+
+
+def match_guided_numpy(desc1, desc2, kp1, kp2, config, F, H, max_error=4.0, rule="angular", max_ratio=0.8,
+                       max_distance=0.7, cross_check=True, return_filtered=False):
+    """Guided matching.  rule "angular": SiftGPUFeatureMatcher::MatchGuided (sift.cc:1308-1413) ->
+    SiftMatchGPU::GetGuidedSiftMatch (SiftMatch.cpp:676-689: the absent model becomes the identity with
+    bound 1e20) -> MultiplyDescriptorG_Kernel (ProgramCU.cu:1521-1663: candidate kept iff hd < hmax and
+    se < fmax, a dropped one ends <= 0 and never matches) -> GetBestMatch.  rule "l2":
+    SiftCPUFeatureMatcher::MatchGuided (sift.cc:1058-1157): one test by `config`, dropped iff residual >
+    max_error^2, dropped candidates take part with squared distance 512^2, FindBestMatchesIndex."""
+    n1, n2 = desc1.shape[0], desc2.shape[0]
+    empty = np.zeros((0, 2), np.uint32)
+    use_f = config in F_CONFIGS
+    if not use_f and config not in H_CONFIGS:
+        return (empty, None) if return_filtered else empty  # sift.cc:1122-1124 / :1385-1387
+    if n1 == 0 or n2 == 0:
+        return (empty, None) if return_filtered else empty
+    eye = np.eye(3, dtype=np.float32)
+    hd, se = guided_residuals(eye if use_f else H, F if use_f else eye, kp1[:n1, :2], kp2[:n2, :2])
+    if rule == "angular":
+        res = np.float32(max_error * max_error)  # sift.cc:1394: the double product, cast to float
+        hmax, fmax = (np.float32(1e20), res) if use_f else (res, np.float32(1e20))
+        filtered = ~((hd < hmax) & (se < fmax))
+        s, inv = _scores(desc1, desc2)
+        s = np.where(filtered, np.float32(0), s)
+        m12 = _one_way_numpy(s, inv, max_ratio, max_distance)
+        if cross_check:
+            m21 = _one_way_numpy(np.ascontiguousarray(s.T), inv, max_ratio, max_distance)
+            keep = [(i, j) for i, j in enumerate(m12) if j != -1 and m21[j] == i]
+        else:
+            keep = [(i, j) for i, j in enumerate(m12) if j != -1]
+        out = np.asarray(keep, dtype=np.uint32).reshape(-1, 2)
+    elif rule == "l2":
+        res = np.float32(max_error * max_error)  # sift.cc:1091
+        filtered = (se > res) if use_f else (hd > res)
+        out = match_l2_numpy(desc1, desc2, max_ratio, max_distance, cross_check, filtered=filtered)
+    else:
+        raise ValueError(rule)
+    return (out, filtered) if return_filtered else out
 
 
 def exhaustive_pairs(image_ids, block_size: int = 50):

@@ -60,15 +60,31 @@ def depth_of(sd) -> int:
     return 1 + max(int(k.split(".")[1]) for k in sd if k.startswith("blocks."))
 
 
-def interpolate_pos_embed(pos_embed: torch.Tensor, gh: int, gw: int) -> torch.Tensor:
-    """[1, 1+37*37, C] -> [1+gh*gw, C].  Bicubic, align_corners=False, size-based (the HF
-    transformers convention; identical to the hub model at 37x37 where nothing is interpolated)."""
+# torch.hub's dinov2_vit{s,b,l}14 are built with interpolate_offset=0.1, interpolate_antialias=False
+# (facebookresearch/dinov2 hub/backbones.py, restated from the public source; the reference does not pin
+# or vendor it, vit_extractor.py:95-98, so this stays "parity unpinned").
+HUB_INTERPOLATE_OFFSET = 0.1
+
+
+def interpolate_pos_embed(pos_embed: torch.Tensor, gh: int, gw: int,
+                          interpolate_offset: float = HUB_INTERPOLATE_OFFSET) -> torch.Tensor:
+    """[1, 1+37*37, C] -> [1+gh*gw, C], bicubic, align_corners=False, no antialias.
+    interpolate_offset > 0 (hub default 0.1): DINOv2's interpolate_pos_encoding passes
+    scale_factor = ((gh + 0.1) / 37, (gw + 0.1) / 37), so source coordinates are
+    (dst + 0.5) * 37 / (g + 0.1) - 0.5 -- slightly different samples from the size-based resize.
+    interpolate_offset == 0: size=(gh, gw) (the HF transformers convention, used to cross-check the
+    rest of the restatement against transformers.Dinov2Model).  Identical at 37x37 (no resize)."""
     pos = pos_embed[0].float()
     if gh == BASE_GRID and gw == BASE_GRID:
         return pos
     C = pos.shape[1]
     grid = pos[1:].reshape(1, BASE_GRID, BASE_GRID, C).permute(0, 3, 1, 2)
-    grid = F.interpolate(grid, size=(gh, gw), mode="bicubic", align_corners=False)
+    if interpolate_offset:
+        scale = (float(gh + interpolate_offset) / BASE_GRID, float(gw + interpolate_offset) / BASE_GRID)
+        grid = F.interpolate(grid, scale_factor=scale, mode="bicubic", align_corners=False)
+    else:
+        grid = F.interpolate(grid, size=(gh, gw), mode="bicubic", align_corners=False)
+    assert tuple(grid.shape[-2:]) == (gh, gw)
     return torch.cat([pos[:1], grid.permute(0, 2, 3, 1).reshape(gh * gw, C)], dim=0)
 
 
@@ -85,7 +101,8 @@ def _r(t: torch.Tensor, emulate: bool) -> torch.Tensor:
     return t.to(torch.bfloat16).float() if emulate else t
 
 
-def forward_features(sd: Dict[str, torch.Tensor], x: torch.Tensor, heads: int, emulate_bf16: bool = False):
+def forward_features(sd: Dict[str, torch.Tensor], x: torch.Tensor, heads: int, emulate_bf16: bool = False,
+                     interpolate_offset: float = HUB_INTERPOLATE_OFFSET):
     """x: normalised f32 [B,3,14*gh,14*gw].  emulate_bf16 rounds every GEMM / attention operand to
     bf16 at the points where the sm_100a kernels do (fp32 accumulation everywhere)."""
     e = emulate_bf16
@@ -97,7 +114,7 @@ def forward_features(sd: Dict[str, torch.Tensor], x: torch.Tensor, heads: int, e
     patches = F.unfold(x, kernel_size=PATCH, stride=PATCH).transpose(1, 2)          # [B, HW, 588]
     wpe = sd["patch_embed.proj.weight"].reshape(C, -1)
     tok = _r(patches, e) @ _r(wpe, e).t() + sd["patch_embed.proj.bias"]
-    pos = interpolate_pos_embed(sd["pos_embed"], gh, gw)
+    pos = interpolate_pos_embed(sd["pos_embed"], gh, gw, interpolate_offset)
     tok = tok + pos[1:]
     cls = (sd["cls_token"].reshape(1, 1, C) + pos[:1]).expand(B, 1, C)
     t = torch.cat([cls, tok], dim=1)                                                # [B, T, C]

@@ -388,3 +388,41 @@ def test_two_handles_on_two_devices():
                 got = m.match_pairs_host(desc, np.array(counts, np.int32), np.array([[0, 1]], np.int32))
             assert got[0].tolist() == ref.tolist(), (d, dev)
             m.close()
+
+
+@pytest.mark.parametrize("kind", ["H", "F"])
+@pytest.mark.parametrize("rule", ["angular", "l2"])
+def test_guided_matching_against_oracle(matcher, kind, rule):
+    """the geometric gate in the GEMM epilogue (vc_match_pairs_guided) against the numpy
+    restatement of MultiplyDescriptorG_Kernel + GetBestMatch (angular rule) resp. of
+    SiftCPUFeatureMatcher::MatchGuided (l2 rule): match lists bit-exact (every residual operation is a
+    separately rounded fp32 op on both sides), both pair orientations, cross check on and off; the gate
+    must actually bite (unguided matching returns a different list)."""
+    from _scenes import two_view_scene as _two_view_scene
+    from oracle import matching as om
+    from vit_colmap_b200.matching import PairGeometry
+    rng = np.random.default_rng(41 + (kind == "F") + 2 * (rule == "l2"))
+    n, kmax, d = 333, 400, 128
+    desc, kps, config, G = _two_view_scene(rng, n, kmax, d, kind)
+    counts = np.array([n, n], np.int32)
+    resident = matcher.upload(desc, counts, rule=rule)
+    F = G if kind == "F" else None
+    H = G if kind == "H" else None
+    H_inv = np.linalg.inv(G) if kind == "H" else None
+    geo_fwd = PairGeometry(config, F, H, 2.0)
+    geo_bwd = PairGeometry(config, None if F is None else F.T, H_inv, 2.0)
+    ratio, dist = (0.9, 1.0) if rule == "angular" else (0.9, 0.9)
+    for cross in (True, False):
+        got = matcher.match_guided(resident, kps, np.array([[0, 1], [1, 0]], np.int32), [geo_fwd, geo_bwd], ratio, dist,
+                                   cross)
+        ref_f, filt = om.match_guided_numpy(desc[0, :n], desc[1, :n], kps[0], kps[1], config, F, H, 2.0, rule, ratio,
+                                            dist, cross, return_filtered=True)
+        ref_b = om.match_guided_numpy(desc[1, :n], desc[0, :n], kps[1], kps[0], config, None if F is None else F.T,
+                                      H_inv, 2.0, rule, ratio, dist, cross)
+        assert got[0].tolist() == ref_f.tolist(), (cross, len(got[0]), len(ref_f))
+        assert got[1].tolist() == ref_b.tolist(), (cross, len(got[1]), len(ref_b))
+        plain = matcher.match_resident(resident, np.array([[0, 1]], np.int32), ratio, dist, cross)[0]
+        assert plain.tolist() != got[0].tolist()
+    assert 0.9 < filt.mean() < 1.0 and len(ref_f) > 100
+    with pytest.raises(ValueError):  # DEGENERATE / UNDEFINED carry no model (sift.cc:1122-1124)
+        matcher.match_guided(resident, kps, np.array([[0, 1]], np.int32), [PairGeometry(1)], ratio, dist, True)

@@ -284,3 +284,166 @@ def test_match_exhaustive_uploads_once_and_equals_oracle(tmp_path, rule):
     n_chunks = sum(-(-len(b) // 16) for b in ExhaustivePairGenerator(ids, 5).blocks())
     per_chunk = (launches_once - (2 if rule == "l2" else 1)) / n_chunks
     assert per_chunk == int(per_chunk) and 4 <= per_chunk <= 7, (launches_once, n_chunks)
+
+
+def test_guided_matching_updates_two_view_geometries(tmp_path):
+    """guided_matching over a database whose two_view_geometries rows were written by a verifier
+    (here: synthetic homographies): inlier matches are replaced by the guided result (equal to the
+    oracle), rows without a usable model are left alone, a pair left with fewer than min_num_inliers
+    becomes an empty TwoViewGeometry (feature_matching_utils.cc:490-493)."""
+    from oracle import matching as om
+    from _scenes import two_view_scene as _two_view_scene
+    from vit_colmap_b200.database import ColmapDatabase, Database, TwoViewGeometry
+    from vit_colmap_b200.matching import FeatureMatchingOptions, guided_matching
+    rng = np.random.default_rng(6)
+    n, d = 250, 128
+    desc, kps, config, G = _two_view_scene(rng, n, n, d, "H")
+    db = ColmapDatabase(str(tmp_path / "g.db"))
+    cam = db.add_pinhole_camera(640, 480, 500.0, 500.0, 320.0, 240.0)
+    ids = [db.add_image(f"im{i}.png", camera_id=cam) for i in range(3)]
+    for k, image_id in enumerate(ids):
+        src = min(k, 1)
+        kp6 = np.zeros((n, 6), np.float32)
+        kp6[:, :2] = kps[src, :n]
+        db.add_keypoints(image_id, kp6)                      # 6-column keypoints: only (x, y) is used
+        db.add_descriptors(image_id, desc[src, :n])
+    db.close()
+    with Database.open(str(tmp_path / "g.db")) as raw:
+        seed = np.array([[0, 0]], np.uint32)
+        raw.write_two_view_geometry(ids[0], ids[1], TwoViewGeometry(config, H=G, inlier_matches=seed))
+        raw.write_two_view_geometry(ids[0], ids[2], TwoViewGeometry(1, inlier_matches=seed))      # DEGENERATE: skipped
+        # image 2 == image 3 but the stored model is wrong for them: (almost) nothing survives the gate
+        raw.write_two_view_geometry(ids[1], ids[2], TwoViewGeometry(config, H=G, inlier_matches=seed))
+    opts = FeatureMatchingOptions(max_ratio=0.9, max_distance=1.0)
+    out = guided_matching(str(tmp_path / "g.db"), opts, max_error=2.0)
+    ref = om.match_guided_numpy(desc[0, :n], desc[1, :n], kps[0], kps[1], config, None, G, 2.0, "angular", 0.9, 1.0)
+    assert set(out) == {(ids[0], ids[1]), (ids[1], ids[2])}
+    assert out[(ids[0], ids[1])].tolist() == ref.tolist() and len(ref) > 100
+    assert len(out[(ids[1], ids[2])]) == 0
+    with Database.open(str(tmp_path / "g.db")) as raw:
+        g01 = raw.read_two_view_geometry(ids[0], ids[1])
+        assert g01.config == config and g01.inlier_matches.tolist() == ref.tolist() and np.allclose(g01.H, G)
+        assert raw.read_two_view_geometry(ids[1], ids[0]).inlier_matches.tolist() == ref[:, ::-1].tolist()
+        g12 = raw.read_two_view_geometry(ids[1], ids[2])
+        assert g12.config == 0 and len(g12.inlier_matches) == 0
+        assert raw.read_two_view_geometry(ids[0], ids[2]).inlier_matches.tolist() == seed.tolist()
+
+
+def _check_extraction_and_matches(ex, db_path, images, grid, num_keypoints, options, block_size=50):
+    """Shared by the C2 / C3 shaped tests: database rows of `ex.extract` against the oracle
+    post-processing of the extractor's own patch tokens, then match_exhaustive against the C oracle on
+    the descriptors that were written."""
+    import cv2
+    import torch
+    from oracle import extract_oracle as eo
+    from oracle import matching as om
+    from vit_colmap_b200.database import Database
+    from vit_colmap_b200.matching import match_exhaustive
+    gh, gw = grid
+    with Database.open(str(db_path)) as db:
+        ids = [im.image_id for im in db.read_all_images()]
+        assert len(ids) == len(images)
+        kps = [db.read_keypoints(i) for i in ids]
+        descs = [db.read_descriptors(i) for i in ids]
+    for k in (0, len(images) - 1):
+        img = cv2.imread(str(images[k]))
+        h, w = img.shape[:2]
+        res, orig_wh, resized_wh = ex._resize(img)
+        tok = ex.model.forward_patch_tokens(torch.from_numpy(res).cuda()[None], bgr=True)[0].cpu()
+        fm = tok.reshape(gh, gw, -1).permute(2, 0, 1).contiguous()
+        ref = eo.dense_to_sparse(fm, orig_wh, resized_wh, num_keypoints, ex.descriptor_dim, "harris",
+                                 projection=ex.descriptor_projection.cpu())
+        a = {tuple(p) for p in kps[k].tolist()}
+        b = {tuple(p) for p in ref["keypoints"].tolist()}
+        assert len(a ^ b) <= 0.02 * len(b), (k, len(a), len(b))    # score-map near-ties may flip a cell
+        pos = {tuple(p): i for i, p in enumerate(ref["keypoints"].tolist())}
+        common = [(i, pos[tuple(p)]) for i, p in enumerate(kps[k].tolist()) if tuple(p) in pos]
+        gi, ri = zip(*common)
+        assert np.abs(descs[k][list(gi)].astype(int) - ref["desc_u8"][list(ri)].astype(int)).max() <= 1
+        assert kps[k][:, 0].max() <= w and kps[k][:, 1].max() <= h
+
+    class Blocks:
+        pass
+    Blocks.block_size = block_size
+    res = match_exhaustive(str(db_path), options, Blocks())
+    for (a, b), m in res.items():
+        ref = om.match_c(descs[ids.index(a)], descs[ids.index(b)], options.max_ratio, options.max_distance,
+                         options.cross_check)
+        if len(ref) < options.min_num_matches:
+            ref = np.zeros((0, 2), np.uint32)
+        assert m.tolist() == ref.tolist(), (a, b)
+    # The reference's uint8 rows (negatives clipped, vit_extractor.py:250) have norm ~ 512 / sqrt(2), so even
+    # identical rows sit at acos(0.5) > max_distance = 0.7 and the default thresholds accept nothing -- as
+    # they would in COLMAP.  Looser thresholds exercise non-empty lists on the same descriptors.
+    from vit_colmap_b200.matching import FeatureMatchingOptions, match_descriptor_sets
+    loose = FeatureMatchingOptions(max_ratio=0.95, max_distance=1.3, cross_check=True)
+    pairs = [(i, j) for i in range(len(ids)) for j in range(i + 1, len(ids))]
+    got = match_descriptor_sets(descs, pairs, loose)
+    total = 0
+    for (i, j), m in zip(pairs, got):
+        assert m.tolist() == om.match_c(descs[i], descs[j], 0.95, 1.3, True).tolist(), (i, j)
+        total += len(m)
+    assert total > 20 * len(pairs)
+    return res, kps
+
+
+def test_c2_hpatches_shaped_sequence(tmp_path):
+    """BASELINE config C2 shape: one 6-image sequence (800x600 -> 798x588, grid 42 x 57), ViT-B/14 width,
+    2048 keypoints, PCA 768 -> 128 fitted on the first image, ratio-test matching of the 15 pairs; images
+    2..6 are homography warps of the first (corner jitter <= 15 %).  Depth-2 synthetic weights keep the
+    test short; every stage still runs at C2's sizes."""
+    import cv2
+    from oracle import vit_oracle as vo
+    from vit_colmap_b200.features.vit_extractor import ViTExtractor
+    from vit_colmap_b200.matching import FeatureMatchingOptions
+    rng = np.random.default_rng(116)
+    d = tmp_path / "seq"
+    d.mkdir()
+    base = cv2.GaussianBlur(rng.integers(0, 256, (600, 800, 3), dtype=np.uint8), (0, 0), 3.0)
+    base = cv2.normalize(base, None, 0, 255, cv2.NORM_MINMAX)
+    corners = np.float32([[0, 0], [800, 0], [800, 600], [0, 600]])
+    files = []
+    for i in range(6):
+        img = base
+        if i:
+            jitter = rng.uniform(-0.15, 0.15, (4, 2)).astype(np.float32) * np.float32([800, 600])
+            img = cv2.warpPerspective(base, cv2.getPerspectiveTransform(corners, corners + jitter), (800, 600))
+        files.append(d / f"{i + 1}.ppm")                      # HPatches sequences hold 1.ppm .. 6.ppm
+        cv2.imwrite(str(files[-1]), img)
+    sd = vo.synthetic_state_dict("dinov2_vitb14", seed=2, depth=2)
+    ex = ViTExtractor(model_name="dinov2_vitb14", num_keypoints=2048, descriptor_dim=128, state_dict=sd, batch_size=4)
+    ex.extract(d, tmp_path / "c2.db", "SIMPLE_PINHOLE")
+    opts = FeatureMatchingOptions(max_ratio=0.8, max_distance=0.7, cross_check=True, min_num_matches=15)
+    res, kps = _check_extraction_and_matches(ex, tmp_path / "c2.db", files, (42, 57), 2048, opts)
+    assert len(res) == 15 and all(150 < len(k) <= 2048 for k in kps)
+
+
+def test_c3_dtu_shaped_images_into_database(tmp_path):
+    """BASELINE config C3 shape: 1600x1200 images (resized to 1596x1190 on the host, grid 85 x 114,
+    T = 9691 tokens), ViT-B/14 width, num_keypoints 8192 (the reference's binning + greedy NMS yields
+    ~1.7k), exhaustive matching into the COLMAP database; 4 images, depth-2 synthetic weights."""
+    import cv2
+    from oracle import vit_oracle as vo
+    from vit_colmap_b200.features.vit_extractor import ViTExtractor
+    from vit_colmap_b200.matching import FeatureMatchingOptions
+    rng = np.random.default_rng(49)
+    d = tmp_path / "scan"
+    d.mkdir()
+    big = cv2.GaussianBlur(rng.integers(0, 256, (1300, 1800, 3), dtype=np.uint8), (0, 0), 2.5)
+    big = cv2.normalize(big, None, 0, 255, cv2.NORM_MINMAX)
+    yy, xx = np.mgrid[0:1300, 0:1800]
+    big = np.where((((yy // 64) + (xx // 64)) % 2 == 0)[..., None], big, 255 - big).astype(np.uint8)   # noise + checker
+    files = []
+    for i in range(4):
+        files.append(d / f"rect_{i + 1:03d}_3_r5000.png")     # DTU naming, scripts/run_DTU_vit.sh
+        cv2.imwrite(str(files[-1]), big[14 * i:14 * i + 1200, 28 * i:28 * i + 1600])
+    sd = vo.synthetic_state_dict("dinov2_vitb14", seed=3, depth=2)
+    ex = ViTExtractor(model_name="dinov2_vitb14", num_keypoints=8192, descriptor_dim=128, state_dict=sd, batch_size=2)
+    ex.extract(d, tmp_path / "c3.db", "SIMPLE_PINHOLE")
+    con = sqlite3.connect(str(tmp_path / "c3.db"))
+    model, w, h, params = con.execute("SELECT model, width, height, params FROM cameras").fetchone()
+    assert (model, w, h) == (0, 1600, 1200) and np.frombuffer(params, np.float64).tolist() == [1600.0, 800.0, 600.0]
+    opts = FeatureMatchingOptions(max_ratio=0.8, max_distance=0.7, cross_check=True, min_num_matches=15)
+    res, kps = _check_extraction_and_matches(ex, tmp_path / "c3.db", files, (85, 114), 8192, opts)
+    assert len(res) == 6 and all(1000 < len(k) <= 8192 for k in kps)
+    assert con.execute("SELECT COUNT(*) FROM matches").fetchone()[0] == 6

@@ -95,3 +95,39 @@ def test_pair_generator_matches_oracle_and_shards():
             assert sorted(x for a in assign for x in a) == list(range(len(blocks)))
             parts = [shard_pairs(flat, r, world) for r in range(world)]
             assert [p for part in parts for p in part] == flat
+
+
+def test_two_view_geometry_rows_follow_colmap_layout(tmp_path):
+    """two_view_geometries rows (database_sqlite.cc:1128-1190, :839-881): stored for the (smaller id,
+    larger id) order with the geometry inverted when written the other way round (F, E transposed,
+    H inverted, pose inverted, match columns swapped), matrices as row-major float64 blobs, no matrix
+    blobs without inlier matches."""
+    import sqlite3
+    import numpy as np
+    from vit_colmap_b200.database import Database, TwoViewGeometry, image_pair_to_pair_id
+    path = tmp_path / "t.db"
+    F = np.arange(9.0).reshape(3, 3)
+    H = np.array([[2.0, 0.0, 1.0], [0.0, 4.0, 0.0], [0.0, 0.0, 1.0]])
+    q = np.array([np.cos(0.3), np.sin(0.3), 0.0, 0.0])
+    g = TwoViewGeometry(3, F, F + 1, H, q, np.array([1.0, 2.0, 3.0]), np.array([[1, 2], [3, 4]], np.uint32))
+    with Database.open(str(path)) as db:
+        db.write_two_view_geometry(5, 2, g)
+        db.write_two_view_geometry(2, 7, TwoViewGeometry(1))
+        back = db.read_two_view_geometry(5, 2)
+        assert np.allclose(back.F, F) and np.allclose(back.H, H) and back.inlier_matches.tolist() == [[1, 2], [3, 4]]
+        assert np.allclose(back.qvec, q) and np.allclose(back.tvec, [1, 2, 3])
+        fwd = db.read_two_view_geometry(2, 5)
+        assert np.allclose(fwd.F, F.T) and np.allclose(fwd.H, np.linalg.inv(H)) and fwd.inlier_matches.tolist() == [[2, 1], [4, 3]]
+        assert db.num_verified_image_pairs() == 2 and db.exists_two_view_geometry(7, 2)
+        assert [pr for pr, _ in db.read_two_view_geometries()] == [(2, 5), (2, 7)]
+    con = sqlite3.connect(str(path))
+    rows, cols, data, config, fb, eb, hb, qb, tb = con.execute(
+        "SELECT rows, cols, data, config, F, E, H, qvec, tvec FROM two_view_geometries WHERE pair_id = ?",
+        (image_pair_to_pair_id(2, 5),)).fetchone()
+    assert (rows, cols, config) == (2, 2, 3)
+    assert np.frombuffer(data, np.uint32).tolist() == [2, 1, 4, 3]
+    assert np.frombuffer(fb, np.float64).tolist() == F.T.reshape(-1).tolist()      # row-major
+    assert len(hb) == 72 and len(qb) == 32 and len(tb) == 24 and len(eb) == 72
+    empty = con.execute("SELECT rows, F, H, qvec FROM two_view_geometries WHERE pair_id = ?",
+                        (image_pair_to_pair_id(2, 7),)).fetchone()
+    assert empty[0] == 0 and all(not b for b in empty[1:])

@@ -145,3 +145,42 @@ def test_l2_rule_known_answers():
     assert len(om.match_l2_numpy(a[:1], c.astype(np.uint8), 0.8, 1.0, False)) == 1
     # empty sides
     assert om.match_l2_numpy(a[:0], b).shape == (0, 2)
+
+
+def test_guided_oracle_structural_answers():
+    """Guided matching restatement (sift.cc:1058-1157 / ProgramCU.cu:1521-1663) on a scene whose answer
+    is structural: image 2 = permuted image 1 moved by a homography.  With the model every row matches
+    through the permutation; moving ten keypoints off the model removes exactly those; a configuration
+    without a model returns nothing; the GPU and CPU rules agree when no residual is near the bound."""
+    rng = np.random.default_rng(0)
+    n = 60
+    kp1 = rng.uniform(0, 640, (n, 2)).astype(np.float32)
+    H = np.array([[1.01, 0.02, 5.0], [-0.01, 0.99, -3.0], [1e-5, 2e-5, 1.0]])
+    p = np.c_[kp1, np.ones(n)] @ H.T
+    kp2 = (p[:, :2] / p[:, 2:]).astype(np.float32)
+    d1 = om.ten_hot_descriptors(n, rng)
+    perm = rng.permutation(n)
+    d2, kp2 = d1[perm], kp2[perm]
+    for rule in ("angular", "l2"):
+        m = om.match_guided_numpy(d1, d2, kp1, kp2, 4, None, H, 4.0, rule)
+        assert len(m) == n and all(perm[j] == i for i, j in m)
+        moved = kp2.copy()
+        moved[:10] += 50
+        m2 = om.match_guided_numpy(d1, d2, kp1, moved, 4, None, H, 4.0, rule)
+        assert sorted(m2[:, 1].tolist()) == list(range(10, n))
+        assert len(om.match_guided_numpy(d1, d2, kp1, kp2, 1, None, H, 4.0, rule)) == 0       # DEGENERATE
+        assert len(om.match_guided_numpy(d1[:0], d2, kp1[:0], kp2, 4, None, H, 4.0, rule)) == 0
+    # fundamental matrix of a pure x-translation: corresponding points share their y coordinate
+    F = np.array([[0.0, 0.0, 0.0], [0.0, 0.0, -1.0], [0.0, 1.0, 0.0]])
+    kp2f = kp1.copy()
+    kp2f[:, 0] += rng.uniform(-80, 80, n).astype(np.float32)
+    kp2f = kp2f[perm]
+    hd, se = om.guided_residuals(np.eye(3), F, kp1, kp2f)
+    assert se.dtype == np.float32 and np.allclose(se[np.arange(n), np.argsort(perm)], 0, atol=1e-6)
+    # Sampson-style residual of a point dy pixels off its epipolar line: dy^2 / 2
+    off = kp2f.copy()
+    off[:, 1] += 3.0
+    _, se3 = om.guided_residuals(np.eye(3), F, kp1, off)
+    assert np.allclose(se3[np.arange(n), np.argsort(perm)], 4.5, rtol=1e-4)
+    m = om.match_guided_numpy(d1, d2, kp1, kp2f, 3, F, None, 1.0, "angular")
+    assert len(m) == n

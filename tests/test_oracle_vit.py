@@ -48,7 +48,7 @@ def test_restatement_matches_transformers_dinov2(name, size):
     rng = np.random.default_rng(0)
     img = torch.from_numpy(rng.integers(0, 256, (1, size[0], size[1], 3), dtype=np.uint8))
     x = vo.preprocess(img)
-    ours = vo.forward_features(sd, x, vo.CONFIGS[name][2])
+    ours = vo.forward_features(sd, x, vo.CONFIGS[name][2], interpolate_offset=0.0)  # HF resizes the table by size
     with torch.no_grad():
         ref = _hf_model(sd, name, depth)(pixel_values=x, interpolate_pos_encoding=True).last_hidden_state
     assert np.abs(ours["x_norm_patchtokens"].numpy() - ref[:, 1:].numpy()).max() < 2e-4
@@ -68,3 +68,46 @@ def test_oracle_module_mirrors_hub_interface():
     m = vo.OracleDinoV2("dinov2_vits14", seed=0, state_dict=vo.synthetic_state_dict("dinov2_vits14", 0, depth=1))
     out = m.forward_features(torch.zeros(1, 3, 28, 42))
     assert m.embed_dim == 384 and out["x_norm_patchtokens"].shape == (1, 6, 384)
+
+
+def _bicubic_1d_weights(dst: int, src: int, scale: float):
+    """Index / weight table of one axis of ATen's upsample_bicubic2d (align_corners=False, A = -0.75):
+    source coordinate (o + 0.5) / scale - 0.5, four taps with clamped indices."""
+    A = -0.75
+    idx = np.zeros((dst, 4), np.int64)
+    w = np.zeros((dst, 4), np.float64)
+    for o in range(dst):
+        x = (o + 0.5) / scale - 0.5
+        x0 = int(np.floor(x))
+        t = x - x0
+        cc = [((A * (t + 1) - 5 * A) * (t + 1) + 8 * A) * (t + 1) - 4 * A,
+              ((A + 2) * t - (A + 3)) * t * t + 1,
+              ((A + 2) * (1 - t) - (A + 3)) * (1 - t) * (1 - t) + 1,
+              ((A * (2 - t) - 5 * A) * (2 - t) + 8 * A) * (2 - t) - 4 * A]
+        for k in range(4):
+            idx[o, k] = min(max(x0 - 1 + k, 0), src - 1)
+            w[o, k] = cc[k]
+    return idx, w
+
+
+@pytest.mark.parametrize("grid", [(10, 14), (42, 57), (85, 114)])
+def test_hub_position_table_resize(grid):
+    """The torch.hub DINOv2 models resize the 37x37 position table with scale_factor (g + 0.1) / 37
+    (interpolate_offset = 0.1), which samples other source coordinates than a size-based resize
+    (ADVICE r01).  Checked against a hand-written separable bicubic with exactly those coordinates;
+    the two variants agree at 37x37 (nothing is resized) and differ elsewhere."""
+    gh, gw = grid
+    g = torch.Generator().manual_seed(0)
+    pos = torch.randn(1, 1 + 37 * 37, 8, generator=g)
+    hub = vo.interpolate_pos_embed(pos, gh, gw).numpy()
+    size_based = vo.interpolate_pos_embed(pos, gh, gw, interpolate_offset=0.0).numpy()
+    iy, wy = _bicubic_1d_weights(gh, 37, (gh + 0.1) / 37)
+    ix, wx = _bicubic_1d_weights(gw, 37, (gw + 0.1) / 37)
+    table = pos[0, 1:].numpy().astype(np.float64).reshape(37, 37, 8)
+    rows = (table[iy] * wy[:, :, None, None]).sum(1)                  # [gh, 37, C]
+    want = (rows[:, ix] * wx[None, :, :, None]).sum(2).reshape(gh * gw, 8)
+    assert np.abs(hub[1:] - want).max() < 5e-5  # ATen evaluates the source coordinates in fp32
+    assert np.array_equal(hub[0], pos[0, 0].numpy())
+    assert np.abs(hub - size_based).max() > 1e-3
+    same = vo.interpolate_pos_embed(pos, 37, 37).numpy()
+    assert np.array_equal(same, vo.interpolate_pos_embed(pos, 37, 37, interpolate_offset=0.0).numpy())

@@ -24,6 +24,13 @@ class MatchOptions(ctypes.Structure):
                 ("inv_norm", c_float), ("rule", c_int32), ("l2_offset", c_float)]
 
 
+class PairGeometry(ctypes.Structure):
+    """vc_pair_geometry (include/vc_b200.h)."""
+    _fields_ = [("h", c_float * 9), ("f", c_float * 9), ("mode", c_int32), ("max_h", c_float), ("max_f", c_float)]
+
+
+GUIDED_SIFTGPU, GUIDED_F, GUIDED_H = 0, 1, 2
+
 # name -> (restype, argtypes); kept in one table so tests can check every exported symbol
 SIGNATURES = {
     "vc_last_error": (c_char_p, []),
@@ -44,6 +51,8 @@ SIGNATURES = {
                                     c_void_p, c_int, POINTER(MatchOptions), c_void_p, c_void_p]),
     "vc_match_pairs_resident": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_void_p, c_int,
                                         POINTER(MatchOptions), c_void_p, c_void_p]),
+    "vc_match_pairs_guided": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_void_p, c_void_p,
+                                      c_int, POINTER(MatchOptions), c_void_p, c_void_p, c_void_p, c_size_t, c_void_p]),
     "vc_l2_augment": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_void_p, POINTER(c_float), c_void_p]),
     "vc_convert_u8_to_bf16": (c_int, [c_void_p, c_void_p, c_size_t, c_void_p]),
     "vc_convert_f32_to_bf16": (c_int, [c_void_p, c_void_p, c_size_t, c_void_p]),

@@ -58,7 +58,7 @@ __device__ __forceinline__ Item decode_item(const MatchParams& p, int item) {
 
 }  // namespace
 
-template <bool kDebug>
+template <bool kDebug, bool kGuided>
 __global__ void __launch_bounds__(kThreads, 1)
 match_top2_kernel(const __grid_constant__ CUtensorMap tmap, const MatchParams p) {
   extern __shared__ uint8_t smem_raw[];
@@ -165,6 +165,22 @@ match_top2_kernel(const __grid_constant__ CUtensorMap tmap, const MatchParams p)
       const int row = it.rb * BM + q * 32 + lane;
       float best = 0.f, second = 0.f;  // sift.cc:742-743
       int bidx = -1;                   // sift.cc:741
+      // guided matching: this row's keypoint, the pair's geometry, the other image's keypoint rows
+      GuidedGeometry geom;
+      float rx = 0.f, ry = 0.f;
+      const float2* kp_n = nullptr;
+      if (kGuided) {
+        geom = p.geom[it.pair];
+        const int km = it.img_m >= p.kp_images ? it.img_m - p.kp_images : it.img_m;
+        const int kn = it.img_n >= p.kp_images ? it.img_n - p.kp_images : it.img_n;
+        const float2* kp_m = reinterpret_cast<const float2*>(p.kp) + (size_t)km * p.kmax;
+        kp_n = reinterpret_cast<const float2*>(p.kp) + (size_t)kn * p.kmax;
+        if (row < it.n_m) {
+          const float2 r = __ldg(kp_m + row);
+          rx = r.x;
+          ry = r.y;
+        }
+      }
       for (int ct = 0; ct < ntiles; ++ct, ++tile) {
         const uint32_t as = tile & 1, aph = (tile >> 1) & 1;
         mbar_wait(tfull_bar(as), aph);
@@ -184,6 +200,21 @@ match_top2_kernel(const __grid_constant__ CUtensorMap tmap, const MatchParams p)
 #pragma unroll
             for (int e = 0; e < 32; ++e)
               if (colbase + e >= it.n_n) v[e] = 0.f;
+          }
+          if (kGuided) {
+            // Candidates that violate the pair's geometry score `masked_score` (SIFTGPU/ProgramCU.cu:1573-1603
+            // drives them to <= 0, COLMAP/feature/sift.cc:945-951 to distance 512^2).  Direction 1 has the
+            // roles swapped: the row is the image-2 keypoint.  Lane e fetches column e's keypoint once.
+            const int cj = colbase + lane;
+            const float2 mine = cj < it.n_n ? __ldg(kp_n + cj) : make_float2(0.f, 0.f);
+#pragma unroll
+            for (int e = 0; e < 32; ++e) {
+              const float cx = __shfl_sync(0xffffffffu, mine.x, e), cy = __shfl_sync(0xffffffffu, mine.y, e);
+              if (colbase + e < it.n_n) {
+                const bool keep = it.dir == 0 ? guided_keep(geom, rx, ry, cx, cy) : guided_keep(geom, cx, cy, rx, ry);
+                if (!keep) v[e] = p.masked_score;
+              }
+            }
           }
           if (kDebug) {
             if (p.dbg_scores != nullptr && it.pair == 0 && it.dir == 0 && row < it.n_m) {
@@ -378,11 +409,22 @@ int match_smem_bytes() { return kSmemBytes; }
 cudaError_t launch_match_top2(const CUtensorMap& tmap, const MatchParams& p, int num_sms, bool debug,
                               cudaStream_t stream) {
   static SmemOptIn opt_in[2];
-  auto kern = debug ? match_top2_kernel<true> : match_top2_kernel<false>;
+  auto kern = debug ? match_top2_kernel<true, false> : match_top2_kernel<false, false>;
   if (cudaError_t e = ensure_dynamic_smem(kern, kSmemBytes, opt_in[debug]); e != cudaSuccess) return e;
   if (p.n_items <= 0) return cudaSuccess;
   const int grid = p.n_items < num_sms ? p.n_items : num_sms;
   kern<<<grid, kThreads, kSmemBytes, stream>>>(tmap, p);
+  return cudaGetLastError();
+}
+
+cudaError_t launch_match_top2_guided(const CUtensorMap& tmap, const MatchParams& p, int num_sms,
+                                     cudaStream_t stream) {
+  static SmemOptIn opt_in;
+  if (cudaError_t e = ensure_dynamic_smem(match_top2_kernel<false, true>, kSmemBytes, opt_in); e != cudaSuccess)
+    return e;
+  if (p.n_items <= 0) return cudaSuccess;
+  const int grid = p.n_items < num_sms ? p.n_items : num_sms;
+  match_top2_kernel<false, true><<<grid, kThreads, kSmemBytes, stream>>>(tmap, p);
   return cudaGetLastError();
 }
 

@@ -8,6 +8,14 @@
 
 namespace vc {
 
+// Two-view geometry of one pair for guided matching (device copy of vc_pair_geometry).
+struct GuidedGeometry {
+  float h[9];   // row-major homography, image 1 -> image 2
+  float f[9];   // row-major fundamental matrix, x2^T F x1
+  int mode;     // 0: SiftGPU rule (both tests, '<' keeps); 1: F only ('>' filters); 2: H only ('>' filters)
+  float max_h, max_f;  // squared residual bounds
+};
+
 struct MatchParams {
   const int32_t* counts;  // [n_images] valid descriptors per image
   const int32_t* pairs;   // [n_pairs, 2] image indices
@@ -36,7 +44,43 @@ struct MatchParams {
   float* part_best;       // [n_pairs, 2*cb_per_img, kmax] row partials, one per 128 columns
   float* part_second;
   int32_t* part_idx;
+  // guided matching (match_top2_kernel<.., true> only)
+  const float* kp;              // [kp_images, kmax, 2] keypoint (x, y) per descriptor row
+  int kp_images;                // image index modulo this = keypoint image (rule l2 doubles the image axis)
+  const GuidedGeometry* geom;   // [n_pairs]
+  float masked_score;           // score of a geometrically inconsistent candidate (0, or l2_offset - 512^2)
 };
+
+// Geometric consistency of a candidate (x1, y1) <-> (x2, y2).  Every operation is a separately rounded
+// fp32 multiply / add / divide (no FMA contraction), so that the numpy oracle reproduces it bit for bit.
+// mode 0: SIFTGPU/ProgramCU.cu:1573-1600 (homography test, then Sampson-style epipolar test, '<' keeps);
+// mode 1 / 2: COLMAP/feature/sift.cc:1099-1122 (one test, '>' filters).
+__device__ __forceinline__ bool guided_keep(const GuidedGeometry& g, float x1, float y1, float x2, float y2) {
+  bool keep = true;
+  if (g.mode != 1) {
+    const float* H = g.h;
+    const float a = __fadd_rn(__fadd_rn(__fmul_rn(H[0], x1), __fmul_rn(H[1], y1)), H[2]);
+    const float b = __fadd_rn(__fadd_rn(__fmul_rn(H[3], x1), __fmul_rn(H[4], y1)), H[5]);
+    const float c = __fadd_rn(__fadd_rn(__fmul_rn(H[6], x1), __fmul_rn(H[7], y1)), H[8]);
+    const float dx = __fsub_rn(__fdiv_rn(a, c), x2), dy = __fsub_rn(__fdiv_rn(b, c), y2);
+    const float hd = __fadd_rn(__fmul_rn(dx, dx), __fmul_rn(dy, dy));
+    keep = g.mode == 0 ? hd < g.max_h : !(hd > g.max_h);
+  }
+  if (g.mode != 2 && keep) {
+    const float* F = g.f;
+    const float fx0 = __fadd_rn(__fadd_rn(__fmul_rn(F[0], x1), __fmul_rn(F[1], y1)), F[2]);
+    const float fx1 = __fadd_rn(__fadd_rn(__fmul_rn(F[3], x1), __fmul_rn(F[4], y1)), F[5]);
+    const float fx2 = __fadd_rn(__fadd_rn(__fmul_rn(F[6], x1), __fmul_rn(F[7], y1)), F[8]);
+    const float ft0 = __fadd_rn(__fadd_rn(__fmul_rn(F[0], x2), __fmul_rn(F[3], y2)), F[6]);
+    const float ft1 = __fadd_rn(__fadd_rn(__fmul_rn(F[1], x2), __fmul_rn(F[4], y2)), F[7]);
+    const float e = __fadd_rn(__fadd_rn(__fmul_rn(x2, fx0), __fmul_rn(y2, fx1)), fx2);
+    const float den = __fadd_rn(__fadd_rn(__fadd_rn(__fmul_rn(fx0, fx0), __fmul_rn(fx1, fx1)), __fmul_rn(ft0, ft0)),
+                                __fmul_rn(ft1, ft1));
+    const float se = __fdiv_rn(__fmul_rn(e, e), den);
+    keep = g.mode == 0 ? se < g.max_f : !(se > g.max_f);
+  }
+  return keep;
+}
 
 // Acceptance tests on a row's (best, second) scores.  acos is evaluated in double and rounded once so
 // the float result agrees with a correctly rounded host acosf.
@@ -60,6 +104,9 @@ __device__ __forceinline__ int accept_scores(float best, float second, int idx, 
 int match_smem_bytes();
 cudaError_t launch_match_top2(const CUtensorMap& tmap, const MatchParams& p, int num_sms, bool debug,
                               cudaStream_t stream);
+// same kernel with the geometric gate of guided matching in the epilogue (p.kp, p.geom set)
+cudaError_t launch_match_top2_guided(const CUtensorMap& tmap, const MatchParams& p, int num_sms,
+                                     cudaStream_t stream);
 int match_fused_smem_bytes();
 // memset(rowthr) + fused kernel + row-partial merge; n_items must be n_pairs * cb_per_img
 cudaError_t launch_match_fused(const CUtensorMap& tmap, const MatchParams& p, int num_sms,

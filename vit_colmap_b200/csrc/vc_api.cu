@@ -282,6 +282,37 @@ int vc_match_pairs_top2(vc_handle* h, const void* desc, const int32_t* counts, i
                     second, index, workspace, workspace_bytes, stream);
 }
 
+int vc_match_pairs_guided(vc_handle* h, const void* desc, const float* keypoints, const int32_t* counts,
+                          int n_images, int kmax, int d, const int32_t* pairs, const vc_pair_geometry* geometry,
+                          int n_pairs, const vc_match_options* opt, uint32_t* matches, int32_t* n_matches,
+                          void* workspace, size_t workspace_bytes, void* stream) {
+  static_assert(sizeof(vc_pair_geometry) == sizeof(vc::GuidedGeometry), "vc_pair_geometry layout");
+  int rc = check_match_args(h, desc, counts, n_images, kmax, d, pairs, n_pairs, opt);
+  if (rc != VC_OK) return rc;
+  if (!keypoints || !matches || !n_matches || (n_pairs > 0 && !geometry))
+    return fail(VC_ERR_INVALID, "null pointer argument");
+  if (n_pairs == 0) return VC_OK;
+  if (!workspace || workspace_bytes < vc_match_workspace_bytes(n_pairs, kmax))
+    return fail(VC_ERR_WORKSPACE, "workspace %zu B < required %zu B", workspace_bytes,
+                vc_match_workspace_bytes(n_pairs, kmax));
+  VC_CUDA(cudaSetDevice(h->device));
+  rc = make_desc_map(h, desc, n_images, kmax, d);
+  if (rc != VC_OK) return rc;
+  cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
+  vc::MatchParams p = make_params(counts, pairs, n_pairs, kmax, d, opt, reinterpret_cast<int32_t*>(workspace));
+  p.kp = keypoints;
+  // rule l2 doubles the image axis (vc_l2_augment): copy n + j of the descriptors is image j's keypoints
+  p.kp_images = opt->rule == VC_RULE_L2 ? n_images / 2 : n_images;
+  p.geom = reinterpret_cast<const vc::GuidedGeometry*>(geometry);
+  // a gated candidate scores 0 under the angular rule (never a match: best starts at 0, strict '>') and
+  // squared distance 512^2 under the l2 rule (COLMAP/feature/sift.cc:945-946)
+  p.masked_score = opt->rule == VC_RULE_L2 ? opt->l2_offset - 262144.f : 0.f;
+  VC_CUDA(vc::launch_match_top2_guided(h->map, p, h->num_sms, s));
+  VC_CUDA(vc::launch_emit_matches(p, matches, n_matches, s));
+  g_launches += 2;
+  return VC_OK;
+}
+
 int vc_debug_scores(vc_handle* h, const void* desc, const int32_t* counts, int n_images, int kmax,
                     int d, int image1, int image2, float* scores, int ld, void* stream) {
   vc_match_options opt{0.8f, 0.7f, 1, 1.0f};

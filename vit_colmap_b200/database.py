@@ -131,6 +131,30 @@ class Image:
     image_id: int = -1
 
 
+@dataclass
+class TwoViewGeometry:
+    """COLMAP/scene/two_view_geometry.h:38-85 (the fields the database stores)."""
+    config: int = 0  # ConfigurationType: 0 UNDEFINED ... 2 CALIBRATED, 3 UNCALIBRATED, 4-6 homographies
+    F: np.ndarray = field(default_factory=lambda: np.zeros((3, 3)))
+    E: np.ndarray = field(default_factory=lambda: np.zeros((3, 3)))
+    H: np.ndarray = field(default_factory=lambda: np.zeros((3, 3)))
+    qvec: np.ndarray = field(default_factory=lambda: np.array([1.0, 0.0, 0.0, 0.0]))  # cam2_from_cam1, wxyz
+    tvec: np.ndarray = field(default_factory=lambda: np.zeros(3))
+    inlier_matches: np.ndarray = field(default_factory=lambda: np.zeros((0, 2), np.uint32))
+
+    def inverted(self) -> "TwoViewGeometry":
+        """TwoViewGeometry::Invert (scene/two_view_geometry.cc:34-42): the same geometry seen from image 2."""
+        w, x, y, z = (float(v) for v in self.qvec)
+        rot = np.array([[1 - 2 * (y * y + z * z), 2 * (x * y - z * w), 2 * (x * z + y * w)],
+                        [2 * (x * y + z * w), 1 - 2 * (x * x + z * z), 2 * (y * z - x * w)],
+                        [2 * (x * z - y * w), 2 * (y * z + x * w), 1 - 2 * (x * x + y * y)]])
+        H = np.asarray(self.H, dtype=np.float64)
+        H_inv = np.linalg.inv(H) if abs(np.linalg.det(H)) > 0 else np.zeros((3, 3))
+        return TwoViewGeometry(self.config, np.asarray(self.F).T.copy(), np.asarray(self.E).T.copy(), H_inv,
+                               np.array([w, -x, -y, -z]), -rot.T @ np.asarray(self.tvec, dtype=np.float64),
+                               np.asarray(self.inlier_matches, dtype=np.uint32).reshape(-1, 2)[:, ::-1].copy())
+
+
 class Database:
     """sqlite3-backed stand-in for pycolmap.Database (methods used on the hot path)."""
 
@@ -236,6 +260,24 @@ class Database:
     def clear_matches(self) -> None:
         self._conn.execute("DELETE FROM matches")
 
+    def write_two_view_geometry(self, image_id1: int, image_id2: int, geometry: TwoViewGeometry,
+                                replace: bool = False) -> None:
+        """database_sqlite.cc:1128-1190: stored for the (smaller id, larger id) order -- the geometry is
+        inverted when the pair comes the other way round -- matrices as row-major float64 blobs, and no
+        matrix blobs at all when there are no inlier matches."""
+        g = geometry.inverted() if image_id1 > image_id2 else geometry
+        m = np.ascontiguousarray(np.asarray(g.inlier_matches, dtype=np.uint32).reshape(-1, 2))
+        blobs = [np.ascontiguousarray(np.asarray(a, dtype=np.float64)).tobytes() if m.shape[0] else b""
+                 for a in (g.F, g.E, g.H, g.qvec, g.tvec)]
+        verb = "INSERT OR REPLACE" if replace else "INSERT"
+        self._conn.execute(f"{verb} INTO two_view_geometries(pair_id, rows, cols, data, config, F, E, H, qvec, tvec) "
+                           "VALUES(?, ?, ?, ?, ?, ?, ?, ?, ?, ?)",
+                           (image_pair_to_pair_id(image_id1, image_id2), int(m.shape[0]), 2, m.tobytes(),
+                            int(g.config), *blobs))
+
+    def clear_two_view_geometries(self) -> None:
+        self._conn.execute("DELETE FROM two_view_geometries")
+
     # ------------------------------------------------------------------ reads
     def _count(self, table: str) -> int:
         return int(self._conn.execute(f"SELECT COUNT(*) FROM {table}").fetchone()[0])
@@ -310,6 +352,37 @@ class Database:
         m = self._read_blob("matches", "pair_id", image_pair_to_pair_id(image_id1, image_id2), np.uint32)
         m = m.reshape(-1, 2)
         return m[:, ::-1].copy() if image_id1 > image_id2 else m
+
+    @staticmethod
+    def _geometry_from_row(rows, data, config, F, E, H, qvec, tvec) -> TwoViewGeometry:
+        def mat(blob, shape):
+            return np.frombuffer(blob, dtype=np.float64).reshape(shape).copy() if blob else np.zeros(shape)
+        m = np.frombuffer(data or b"", dtype=np.uint32).reshape(int(rows), 2).copy() if rows else np.zeros((0, 2), np.uint32)
+        q = mat(qvec, (4,)) if qvec else np.array([1.0, 0.0, 0.0, 0.0])
+        return TwoViewGeometry(int(config), mat(F, (3, 3)), mat(E, (3, 3)), mat(H, (3, 3)), q, mat(tvec, (3,)), m)
+
+    def exists_two_view_geometry(self, image_id1: int, image_id2: int) -> bool:
+        return self._exists("two_view_geometries", "pair_id", image_pair_to_pair_id(image_id1, image_id2))
+
+    def read_two_view_geometry(self, image_id1: int, image_id2: int) -> TwoViewGeometry:
+        """database_sqlite.cc:839-881 (inverted back when asked for as (larger id, smaller id))."""
+        r = self._conn.execute("SELECT rows, data, config, F, E, H, qvec, tvec FROM two_view_geometries "
+                               "WHERE pair_id = ?", (image_pair_to_pair_id(image_id1, image_id2),)).fetchone()
+        if r is None:
+            return TwoViewGeometry()
+        g = self._geometry_from_row(*r)
+        return g.inverted() if image_id1 > image_id2 else g
+
+    def read_two_view_geometries(self) -> List[Tuple[Tuple[int, int], TwoViewGeometry]]:
+        """Every row in its stored (smaller id, larger id) orientation (database_sqlite.cc:883-930)."""
+        out = []
+        for pid, *r in self._conn.execute("SELECT pair_id, rows, data, config, F, E, H, qvec, tvec FROM "
+                                          "two_view_geometries ORDER BY pair_id"):
+            out.append((pair_id_to_image_pair(int(pid)), self._geometry_from_row(*r)))
+        return out
+
+    def num_verified_image_pairs(self) -> int:
+        return self._count("two_view_geometries")
 
     def read_all_matches(self) -> List[Tuple[Tuple[int, int], np.ndarray]]:
         out = []

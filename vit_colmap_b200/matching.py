@@ -268,6 +268,91 @@ class Matcher:
         return out
 
 
+    # ------------------------------------------------------------------ guided matching
+    def match_guided(self, resident: "ResidentDescriptors", keypoints, pairs, geometries: Sequence["PairGeometry"],
+                     max_ratio=0.8, max_distance=0.7, cross_check=True) -> List[np.ndarray]:
+        """Guided matching of index pairs against resident descriptors.
+
+        keypoints: [n_images, kmax, 2] float32 (x, y) per descriptor row (host ndarray or device tensor);
+        geometries: one PairGeometry per pair.  Semantics: SiftGPUFeatureMatcher::MatchGuided
+        (COLMAP/feature/sift.cc:1308-1413) under the angular rule, SiftCPUFeatureMatcher::MatchGuided
+        (:1058-1157) under rule l2 -- see vc_match_pairs_guided in include/vc_b200.h."""
+        torch = self.torch
+        pairs = np.ascontiguousarray(pairs, dtype=np.int32).reshape(-1, 2)
+        n_pairs = pairs.shape[0]
+        if len(geometries) != n_pairs:
+            raise ValueError("one geometry per pair")
+        if n_pairs == 0:
+            return []
+        if pairs.min() < 0 or pairs.max() >= resident.n_images:
+            raise ValueError("pair index outside the uploaded image range")
+        desc = resident.desc
+        n_dev, kmax, d = (int(v) for v in desc.shape)
+        kp = keypoints if not isinstance(keypoints, np.ndarray) else torch.from_numpy(
+            np.ascontiguousarray(keypoints, dtype=np.float32))
+        kp = kp.to(device=desc.device, dtype=torch.float32).contiguous()
+        if tuple(kp.shape) != (resident.n_images, kmax, 2):
+            raise ValueError(f"keypoints must be [{resident.n_images}, {kmax}, 2]")
+        geo = (_lib.PairGeometry * n_pairs)()
+        for k, g in enumerate(geometries):
+            geo[k] = g.to_c(resident.rule)
+        geo_dev = torch.frombuffer(bytearray(bytes(geo)), dtype=torch.uint8).to(desc.device)
+        chunk = pairs.copy()
+        chunk[:, 1] += resident.second_offset
+        pairs_dev = torch.from_numpy(chunk).to(desc.device)
+        counts_dev = torch.from_numpy(resident.counts).to(desc.device)
+        matches = torch.empty((n_pairs, kmax, 2), dtype=torch.int32, device=desc.device)
+        n_matches = torch.empty((n_pairs,), dtype=torch.int32, device=desc.device)
+        ws, need = self._workspace(n_pairs, kmax)
+        opt = self._opts(max_ratio, max_distance, cross_check, resident.inv_norm, resident.rule, resident.l2_offset)
+        _lib.check(self.lib.vc_match_pairs_guided(self.handle, _ptr(desc), _ptr(kp), _ptr(counts_dev), n_dev, kmax, d,
+                                                  _ptr(pairs_dev), _ptr(geo_dev), n_pairs, ctypes.byref(opt),
+                                                  _ptr(matches), _ptr(n_matches), _ptr(ws), need, self._stream()))
+        n_h = n_matches.cpu().numpy()
+        out = []
+        for k in range(n_pairs):  # only the filled prefix of each pair's slot comes back
+            out.append(matches[k, : int(n_h[k])].cpu().numpy().view(np.uint32).reshape(-1, 2).copy())
+        return out
+
+
+# TwoViewGeometry::ConfigurationType (COLMAP/scene/two_view_geometry.h:40-61)
+CONFIG_UNDEFINED, CONFIG_DEGENERATE, CONFIG_CALIBRATED, CONFIG_UNCALIBRATED = 0, 1, 2, 3
+CONFIG_PLANAR, CONFIG_PANORAMIC, CONFIG_PLANAR_OR_PANORAMIC, CONFIG_CALIBRATED_RIG = 4, 5, 6, 9
+_F_CONFIGS = (CONFIG_CALIBRATED, CONFIG_CALIBRATED_RIG, CONFIG_UNCALIBRATED)
+_H_CONFIGS = (CONFIG_PLANAR, CONFIG_PANORAMIC, CONFIG_PLANAR_OR_PANORAMIC)
+
+
+@dataclass
+class PairGeometry:
+    """Two-view geometry of one image pair as guided matching consumes it
+    (TwoViewGeometry::{config, F, H}, COLMAP/scene/two_view_geometry.h:63-73).  F / H: 3x3, H maps
+    image 1 to image 2, F satisfies p2^T F p1 = 0; max_error in pixels (RANSAC max_error, default 4)."""
+    config: int
+    F: Optional[np.ndarray] = None
+    H: Optional[np.ndarray] = None
+    max_error: float = 4.0
+
+    def usable(self) -> bool:
+        return self.config in _F_CONFIGS or self.config in _H_CONFIGS
+
+    def to_c(self, rule: int) -> "_lib.PairGeometry":
+        if not self.usable():
+            raise ValueError(f"two-view configuration {self.config} has no geometry to guide with (sift.cc:1122-1124)")
+        use_f = self.config in _F_CONFIGS
+        eye = np.eye(3, dtype=np.float32)
+        big = 1.0e20  # SIFTGPU/SiftMatch.cpp:684: the absent model becomes identity with an unreachable bound
+        m = np.asarray(self.F if use_f else self.H, dtype=np.float64).astype(np.float32).reshape(3, 3)
+        res = np.float32(float(self.max_error) * float(self.max_error))  # sift.cc:1091,1394: double product -> float
+        g = _lib.PairGeometry()
+        g.h[:] = (eye if use_f else m).reshape(-1).tolist()
+        g.f[:] = (m if use_f else eye).reshape(-1).tolist()
+        if rule == 0:   # GPU path: both tests are evaluated
+            g.mode, g.max_h, g.max_f = _lib.GUIDED_SIFTGPU, (big if use_f else float(res)), (float(res) if use_f else big)
+        else:           # CPU path: one test, '>' filters
+            g.mode, g.max_h, g.max_f = (_lib.GUIDED_F if use_f else _lib.GUIDED_H), float(res), float(res)
+        return g
+
+
 @dataclass
 class ResidentDescriptors:
     """Descriptors of a set of images as the matcher reads them: bf16 [n_dev, kmax, d] in HBM."""
@@ -389,3 +474,59 @@ def match_exhaustive(database_path, matching_options: Optional[FeatureMatchingOp
                 for (a, b), m in results.items():
                     db.write_matches(a, b, m)
     return results
+
+
+def guided_matching(database_path, matching_options: Optional[FeatureMatchingOptions] = None, max_error: float = 4.0,
+                    min_num_inliers: int = 15, device=None, *, matcher: Optional[Matcher] = None,
+                    pairs_per_launch: int = 256):
+    """Second matching pass with ``guided_matching=True`` (COLMAP/feature/matcher.h:76-77,
+    controllers/feature_matching_utils.cc:129-146,300-330): every pair whose ``two_view_geometries`` row
+    holds a usable model (written by pycolmap's geometric verification) is matched again with the
+    model as a gate on the candidates, and the row's inlier matches are replaced by the result; a pair
+    left with fewer than ``min_num_inliers`` gets an empty TwoViewGeometry
+    (feature_matching_utils.cc:490-493).  Descriptors and keypoints are uploaded once.
+    ``max_error``: TwoViewGeometryOptions.ransac_options.max_error (pixels).
+    Returns {(image_id1, image_id2): inlier matches [n, 2] uint32}."""
+    from .database import Database, TwoViewGeometry
+    options = matching_options or FeatureMatchingOptions()
+    dev_index = device if isinstance(device, int) else 0
+    matcher = matcher or Matcher(dev_index)
+    rule = getattr(options, "rule", "angular")
+    out = {}
+    with Database.open(str(database_path)) as db:
+        todo = [(pr, g) for pr, g in db.read_two_view_geometries()
+                if PairGeometry(g.config).usable() and db.exists_descriptors(pr[0]) and db.exists_descriptors(pr[1])]
+        if not todo:
+            return out
+        ids = sorted({i for pr, _ in todo for i in pr})
+        index_of = {i: k for k, i in enumerate(ids)}
+        descs = [db.read_descriptors(i) for i in ids]
+        buf, counts = pad_descriptors(descs, options.max_num_matches)
+        kmax = int(buf.shape[1])
+        kps = np.zeros((len(ids), kmax, 2), np.float32)
+        for k, i in enumerate(ids):
+            kp = db.read_keypoints(i)
+            n = min(int(counts[k]), kp.shape[0])
+            if n != int(counts[k]):
+                raise ValueError(f"image {i}: {kp.shape[0]} keypoints for {counts[k]} descriptors (sift.cc:1069-1070)")
+            kps[k, :n] = kp[:n, :2]
+        resident = matcher.upload(buf, counts, rule=rule)
+        kps_dev = matcher.torch.from_numpy(kps).to(matcher._dev())
+        for s in range(0, len(todo), pairs_per_launch):
+            part = todo[s:s + pairs_per_launch]
+            idx = np.array([(index_of[a], index_of[b]) for (a, b), _ in part], dtype=np.int32)
+            geos = [PairGeometry(g.config, g.F, g.H, max_error) for _, g in part]
+            res = matcher.match_guided(resident, kps_dev, idx, geos, options.max_ratio, options.max_distance,
+                                       options.cross_check)
+            for (pr, g), m in zip(part, res):
+                out[pr] = m
+        with db.transaction():
+            for pr, g in todo:
+                m = out[pr]
+                if m.shape[0] < min_num_inliers:
+                    new = TwoViewGeometry()
+                    out[pr] = new.inlier_matches
+                else:
+                    new = TwoViewGeometry(g.config, g.F, g.E, g.H, g.qvec, g.tvec, m)
+                db.write_two_view_geometry(pr[0], pr[1], new, replace=True)
+    return out

@@ -31,12 +31,16 @@ class VitBackbone:
     """Weights resident on one GPU + the forward call.  ``state_dict`` uses the hub model's keys."""
 
     def __init__(self, state_dict: Dict[str, "torch.Tensor"], name: str = "dinov2_vitb14", device: int = 0,
-                 handle=None):
+                 handle=None, interpolate_offset: float = 0.1):
         import torch
         if not torch.cuda.is_available():
             raise _lib.VcError("no CUDA device: vit_colmap_b200 has no CPU fallback")
         self.torch = torch
         self.name = name
+        # 0.1 = the torch.hub dinov2_vit*14 models the reference loads (vit_extractor.py:95-98) are built
+        # with interpolate_offset=0.1 (position table resized by scale_factor (g + 0.1) / 37); 0 = the
+        # size-based resize of HF transformers.  Same table at 37x37.  See DESIGN.md section 4.
+        self.interpolate_offset = float(interpolate_offset)
         self.embed_dim, depth_default, self.num_heads = CONFIGS[name]
         self.depth = 1 + max(int(k.split(".")[1]) for k in state_dict if k.startswith("blocks."))
         self.device = int(device)
@@ -89,8 +93,10 @@ class VitBackbone:
 
     # ------------------------------------------------------------------ host-side one-offs
     def pos_embed(self, gh: int, gw: int):
-        """[1+gh*gw, C] f32 on the device; bicubic resize of the 37x37 table when the grid differs
-        (size-based, align_corners=False -- see oracle/vit_oracle.py).  Computed once per grid."""
+        """[1+gh*gw, C] f32 on the device; bicubic resize (align_corners=False, no antialias) of the 37x37
+        table when the grid differs: by scale_factor (g + interpolate_offset) / 37 as DINOv2's
+        interpolate_pos_encoding does for the hub models, or by size when the offset is 0.  A one-off
+        host-side step per grid (cached); the result is an input of vc_vit_forward."""
         key = (gh, gw)
         if key not in self._pos:
             torch = self.torch
@@ -98,7 +104,12 @@ class VitBackbone:
             if key != (BASE_GRID, BASE_GRID):
                 C = pos.shape[1]
                 grid = pos[1:].reshape(1, BASE_GRID, BASE_GRID, C).permute(0, 3, 1, 2)
-                grid = torch.nn.functional.interpolate(grid, size=key, mode="bicubic", align_corners=False)
+                if self.interpolate_offset:
+                    scale = (float(gh + self.interpolate_offset) / BASE_GRID, float(gw + self.interpolate_offset) / BASE_GRID)
+                    grid = torch.nn.functional.interpolate(grid, scale_factor=scale, mode="bicubic", align_corners=False)
+                else:
+                    grid = torch.nn.functional.interpolate(grid, size=key, mode="bicubic", align_corners=False)
+                assert tuple(grid.shape[-2:]) == key
                 pos = torch.cat([pos[:1], grid.permute(0, 2, 3, 1).reshape(gh * gw, C)], dim=0)
             self._pos[key] = pos.to(device=torch.device("cuda", self.device), dtype=torch.float32).contiguous()
         return self._pos[key]
