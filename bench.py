@@ -165,7 +165,7 @@ def run_reference(args):
     be built in this image).  Each step is a bounded sample; rank 0 only."""
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
-        return
+        return None
     # torchrun exports OMP_NUM_THREADS=1; the reference arm uses every host core the box has
     import torch
     torch.set_num_threads(_host_cores())
@@ -192,7 +192,7 @@ def run_reference(args):
                            "cpu_baseline": {"value": ev, "unit": "images/s", "cores": eth, "kind": "port",
                                             "sample": f"{en} images ({edt:.1f} s), fp32 PyTorch DINOv2 restatement + "
                                                       "reference post-processing restatement"}}
-    print(json.dumps(line))
+    return line
 
 
 # ------------------------------------------------------------------------------------------- GPU
@@ -396,9 +396,11 @@ def run_ours(args):
         if cpu_v is not None:
             line["cpu_baseline"] = {"value": cpu_v, "unit": UNIT, "cores": cpu_threads, "kind": "port",
                                     "sample": f"{cpu_rows} full 8192x8192 d=768 pairs ({cpu_dt:.1f} s), float32 SIMD dot, OpenMP"}
-        print(json.dumps(line))
+        if world == 1 and not args.skip_variants:
+            line["match_exhaustive_db"] = run_db_e2e(torch, local)
     if world > 1:
         dist.destroy_process_group()
+    return line if rank == 0 else None
 
 
 # ------------------------------------------------------------------------------------ extraction
@@ -589,6 +591,43 @@ def cpu_extract_sample(n_images=2):
     return n_images / dt, n_images, dt, torch.get_num_threads()
 
 
+def run_db_e2e(torch, local):
+    """Rank 0 of SURVEY 8(f): the callers either side of the matcher -- `match_exhaustive` over a COLMAP
+    database (sqlite3 reads of the descriptor blobs, ONE upload, pair chunks on the resident set, batched
+    write of the `matches` rows).  64 images x 2048 SIFT-like uint8 descriptors (d = 128), 2016 pairs."""
+    import tempfile
+    from oracle import matching as om  # quantiser only (to_uint8_colmap): building inputs, not measured
+    from vit_colmap_b200.database import ColmapDatabase
+    from vit_colmap_b200.matching import FeatureMatchingOptions, Matcher, match_exhaustive
+    n_images, k, d = 64, 2048, 128
+    rng = np.random.default_rng(5)
+    base = rng.standard_normal((4 * k, d)).astype(np.float32)
+    with tempfile.TemporaryDirectory() as tmp:
+        path = os.path.join(tmp, "bench.db")
+        db = ColmapDatabase(path)
+        cam = db.add_pinhole_camera(640, 480, 500.0, 500.0, 320.0, 240.0)
+        for i in range(n_images):
+            rows = np.abs(base[rng.permutation(4 * k)[:k]] + 0.15 * rng.standard_normal((k, d)).astype(np.float32))
+            image_id = db.add_image(f"im{i:03d}.png", camera_id=cam)
+            db.add_keypoints(image_id, rng.uniform(0, 480, (k, 2)).astype(np.float32))
+            db.add_descriptors(image_id, om.to_uint8_colmap(rows / np.linalg.norm(rows, axis=1, keepdims=True)))
+        db.close()
+        matcher = Matcher(local)
+        opts = FeatureMatchingOptions(max_ratio=0.85, max_distance=0.9)
+        warm = np.zeros((2, 256, d), np.uint8)
+        matcher.match_pairs_host(warm, np.array([256, 256], np.int32), np.array([[0, 1]], np.int32))
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        res = match_exhaustive(path, opts, matcher=matcher)
+        dt = time.perf_counter() - t0
+        n_rows = sum(len(m) for m in res.values())
+        matcher.close()
+    return {"metric": "matched_pairs_per_sec@match_exhaustive_db_2048kpts_d128", "value": len(res) / dt, "unit": "pairs/s",
+            "seconds": dt, "pairs": len(res), "match_rows_written": int(n_rows),
+            "h2d_bytes": n_images * k * d, "api": "vit_colmap_b200.matching.match_exhaustive(database_path) -- sqlite3 "
+            "reads, one upload, vc_match_pairs_resident per pair chunk, one write transaction"}
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -598,10 +637,15 @@ def main():
     ap.add_argument("--skip-extract", action="store_true", help="matcher half of the metric only")
     ap.add_argument("--skip-variants", action="store_true", help="skip the unpruned / non-negative-data matcher timings")
     args = ap.parse_args()
-    if args.impl == "reference":
-        run_reference(args)
-    else:
-        run_ours(args)
+    # stdout carries the ONE JSON line; the extractors' progress prints go to stderr
+    real_stdout = os.dup(1)
+    os.dup2(2, 1)
+    sys.stdout = os.fdopen(os.dup(2), "w")
+    out = os.fdopen(real_stdout, "w")
+    line = run_reference(args) if args.impl == "reference" else run_ours(args)
+    if line is not None:
+        out.write(json.dumps(line) + "\n")
+        out.flush()
 
 
 if __name__ == "__main__":

@@ -34,6 +34,7 @@ def main():
         base = cv2.GaussianBlur(rng.integers(0, 256, (700, 700, 3), dtype=np.uint8), (0, 0), 3)
         for i in range(n_images):
             cv2.imwrite(str(img_dir / f"im_{i:02d}.png"), base[14 * i:14 * i + 518, 14 * (i % 3):14 * (i % 3) + 518])  # patch-aligned shifts
+        (img_dir / "im_04_broken.png").write_bytes(b"not an image")  # skipped by both runs (vit_extractor.py:733-737)
         for p in (tmp / "dist.db", tmp / "single.db"):
             if p.exists():
                 p.unlink()
