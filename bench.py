@@ -618,12 +618,13 @@ def run_db_e2e(torch, local):
         matcher.match_pairs_host(warm, np.array([256, 256], np.int32), np.array([[0, 1]], np.int32))
         torch.cuda.synchronize()
         t0 = time.perf_counter()
-        res = match_exhaustive(path, opts, matcher=matcher)
+        stages = {}
+        res = match_exhaustive(path, opts, matcher=matcher, stats=stages)
         dt = time.perf_counter() - t0
         n_rows = sum(len(m) for m in res.values())
         matcher.close()
     return {"metric": "matched_pairs_per_sec@match_exhaustive_db_2048kpts_d128", "value": len(res) / dt, "unit": "pairs/s",
-            "seconds": dt, "pairs": len(res), "match_rows_written": int(n_rows),
+            "seconds": dt, "stage_seconds": {k: round(v, 4) for k, v in stages.items()}, "pairs": len(res), "match_rows_written": int(n_rows),
             "h2d_bytes": n_images * k * d, "api": "vit_colmap_b200.matching.match_exhaustive(database_path) -- sqlite3 "
             "reads, one upload, vc_match_pairs_resident per pair chunk, one write transaction"}
 

@@ -1,0 +1,66 @@
+"""Times guided matching (vc_match_pairs_guided: geometric gate in the GEMM epilogue) next to the
+unguided matcher on the same descriptors:  python tools/time_guided.py [n_images=8] [kpts=8192] [d=128]
+Rates are per pair (both directions, cross check, emit) with CUDA events on the launching stream."""
+import ctypes
+import sys
+from pathlib import Path
+
+import numpy as np
+import torch
+
+sys.path.insert(0, str(Path(__file__).resolve().parent.parent))
+from vit_colmap_b200 import _lib  # noqa: E402
+from vit_colmap_b200.matching import Matcher, PairGeometry  # noqa: E402
+
+n_img = int(sys.argv[1]) if len(sys.argv) > 1 else 8
+K = int(sys.argv[2]) if len(sys.argv) > 2 else 8192
+d = int(sys.argv[3]) if len(sys.argv) > 3 else 128
+m = Matcher(0)
+pairs_l = [(i, j) for i in range(n_img) for j in range(i + 1, n_img)]
+pairs = torch.tensor(pairs_l, dtype=torch.int32, device="cuda")
+counts = torch.full((n_img,), K, dtype=torch.int32, device="cuda")
+g = torch.Generator(device="cuda").manual_seed(1)
+x = torch.randn((n_img, K, d), device="cuda", generator=g).abs()
+x = (x / x.norm(dim=2, keepdim=True)).to(torch.bfloat16)
+kp = torch.rand((n_img, K, 2), device="cuda", generator=g) * torch.tensor([1600.0, 1200.0], device="cuda")
+H = np.array([[1.01, 0.02, 5.0], [-0.01, 0.99, -3.0], [1e-5, 2e-5, 1.0]])
+F = np.array([[0.0, 0.0, 0.0], [0.0, 0.0, -1.0], [0.0, 1.0, 0.0]])
+need = int(m.lib.vc_match_workspace_bytes(len(pairs_l), K))
+ws = torch.empty(need, dtype=torch.uint8, device="cuda")
+matches = torch.empty((len(pairs_l), K, 2), dtype=torch.int32, device="cuda")
+n_matches = torch.empty((len(pairs_l),), dtype=torch.int32, device="cuda")
+opt = m._opts(0.8, 0.7, True, 1.0)
+
+
+def timed(fn):
+    for _ in range(2):
+        fn()
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(True), torch.cuda.Event(True)
+    e0.record()
+    for _ in range(3):
+        fn()
+    e1.record()
+    torch.cuda.synchronize()
+    return e0.elapsed_time(e1) / 3
+
+
+def plain():
+    _lib.check(m.lib.vc_match_pairs(m.handle, x.data_ptr(), counts.data_ptr(), n_img, K, d, pairs.data_ptr(), len(pairs_l),
+                                    ctypes.byref(opt), matches.data_ptr(), n_matches.data_ptr(), ws.data_ptr(), need,
+                                    m._stream()))
+
+
+ms = timed(plain)
+print(f"unguided (fused single-pass kernel): {ms / len(pairs_l) * 1e3:8.1f} us/pair")
+for name, geo in (("H (SiftGPU rule: H and F tests)", PairGeometry(4, None, H, 4.0)), ("F (SiftGPU rule)", PairGeometry(3, F, None, 4.0))):
+    arr = (_lib.PairGeometry * len(pairs_l))(*[geo.to_c(0) for _ in pairs_l])
+    geo_dev = torch.frombuffer(bytearray(bytes(arr)), dtype=torch.uint8).cuda()
+
+    def guided():
+        _lib.check(m.lib.vc_match_pairs_guided(m.handle, x.data_ptr(), kp.data_ptr(), counts.data_ptr(), n_img, K, d,
+                                               pairs.data_ptr(), geo_dev.data_ptr(), len(pairs_l), ctypes.byref(opt),
+                                               matches.data_ptr(), n_matches.data_ptr(), ws.data_ptr(), need, m._stream()))
+    ms = timed(guided)
+    print(f"guided {name}: {ms / len(pairs_l) * 1e3:8.1f} us/pair, {2 * K * K * len(pairs_l) / ms / 1e9:6.2f} T gated candidates/s, "
+          f"mean matches {n_matches.float().mean().item():.1f}")

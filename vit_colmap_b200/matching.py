@@ -67,6 +67,7 @@ class Matcher:
         _lib.check(self.lib.vc_create(self.device, ctypes.byref(h)))
         self.handle = h
         self._ws = None
+        self._host_staging: list = []   # page-locked staging of pad_descriptors, reused across uploads
 
     def close(self):
         if getattr(self, "handle", None):
@@ -369,17 +370,28 @@ class ResidentDescriptors:
         return int(self.desc.numel()) * 2
 
 
-def pad_descriptors(descriptors: Sequence[np.ndarray], max_rows: int, pinned: bool = True):
+def pad_descriptors(descriptors: Sequence[np.ndarray], max_rows: int, pinned: bool = True, staging=None):
     """Ragged list of [n_i, d] uint8 / float32 arrays -> (padded [n, kmax, d] torch host tensor, counts).
-    The buffer is written once, directly in page-locked memory, so the upload is one DMA."""
+    The rows are written once, directly into page-locked memory, so the upload is one DMA.  `staging`
+    (a one-element list holding a flat page-locked uint8 tensor, grown on demand) lets a caller reuse
+    the allocation across calls: allocating and first-touching page-locked memory costs more than the
+    copy itself.  Only the padding rows are zeroed (the kernels ignore rows >= counts[i]; the l2
+    augmentation takes its largest norm over every row, so padding must not be garbage)."""
     import torch
     n_images = len(descriptors)
     d = max((int(x.shape[1]) for x in descriptors if x.ndim == 2 and x.shape[0] > 0), default=128)
     is_u8 = all(x.dtype == np.uint8 for x in descriptors)
     kmax = max(max((int(x.shape[0]) for x in descriptors if x.ndim == 2), default=0), 1)
     kmax = min(kmax, max_rows)  # SIFTGPU/SiftMatchCU.cpp:108 clamps inputs likewise
+    dtype = torch.uint8 if is_u8 else torch.float32
+    nbytes = n_images * kmax * d * (1 if is_u8 else 4)
     use_pin = pinned and torch.cuda.is_available()
-    buf = torch.zeros((n_images, kmax, d), dtype=torch.uint8 if is_u8 else torch.float32, pin_memory=use_pin)
+    if staging is not None:
+        if not staging or staging[0].numel() < nbytes:
+            staging[:] = [torch.empty((max(nbytes, 1 << 20),), dtype=torch.uint8, pin_memory=use_pin)]
+        buf = staging[0][:nbytes].view(dtype).view(n_images, kmax, d)
+    else:
+        buf = torch.empty((n_images, kmax, d), dtype=dtype, pin_memory=use_pin)
     view = buf.numpy()
     counts = np.zeros((n_images,), dtype=np.int32)
     for i, x in enumerate(descriptors):
@@ -387,6 +399,8 @@ def pad_descriptors(descriptors: Sequence[np.ndarray], max_rows: int, pinned: bo
         counts[i] = n
         if n:
             view[i, :n] = x[:n]
+        if n < kmax:
+            view[i, n:] = 0
     return buf, counts
 
 
@@ -396,7 +410,7 @@ def match_descriptor_sets(descriptors: Sequence[np.ndarray], pairs, options: Opt
     pairs: pad + upload ONCE, then match every pair on the resident set.  Returns list of [n,2] uint32."""
     options = options or FeatureMatchingOptions()
     matcher = matcher or Matcher(device)
-    buf, counts = pad_descriptors(descriptors, options.max_num_matches)
+    buf, counts = pad_descriptors(descriptors, options.max_num_matches, staging=matcher._host_staging)
     rule = getattr(options, "rule", "angular")
     resident = matcher.upload(buf, counts, rule=rule)
     return matcher.match_resident(resident, np.asarray(pairs, dtype=np.int32), options.max_ratio,
@@ -406,7 +420,8 @@ def match_descriptor_sets(descriptors: Sequence[np.ndarray], pairs, options: Opt
 def match_exhaustive(database_path, matching_options: Optional[FeatureMatchingOptions] = None,
                      pairing_options=None, verification_options=None, device=None, *,
                      matcher: Optional[Matcher] = None, rank: int = 0, world_size: int = 1,
-                     pairs_per_launch: int = 1024, max_resident_bytes: Optional[int] = None):
+                     pairs_per_launch: int = 1024, max_resident_bytes: Optional[int] = None,
+                     stats: Optional[dict] = None):
     """Drop-in for ``pycolmap.match_exhaustive(database_path, matching_options, ...)`` restricted to
     the matching half (PYCOLMAP/pipeline/match_features.cc:28-51; geometric verification stays with
     pycolmap and is invoked afterwards when pycolmap is importable).
@@ -420,9 +435,14 @@ def match_exhaustive(database_path, matching_options: Optional[FeatureMatchingOp
     memory) the upload happens per pairing block instead (the <= 2 x block_size images a block names),
     still once per block rather than once per pair chunk.  With world_size > 1 each rank matches its
     share of the pair blocks (no collective); only a single-process call writes.
+    ``stats`` (optional dict) receives the wall-clock seconds of the four stages: read_s (sqlite3 reads +
+    pair generation), upload_s (pad into page-locked memory, H2D, conversion), match_s, write_s.
     Returns {(image_id1, image_id2): matches[n,2] uint32}.
     """
+    import time
     from .database import Database
+    clock = {"read_s": 0.0, "upload_s": 0.0, "match_s": 0.0, "write_s": 0.0}
+    t_start = time.perf_counter()
     options = matching_options or FeatureMatchingOptions()
     block_size = int(getattr(pairing_options, "block_size", 50)) if pairing_options is not None else 50
     dev_index = device if isinstance(device, int) else 0
@@ -445,16 +465,23 @@ def match_exhaustive(database_path, matching_options: Optional[FeatureMatchingOp
             if part:
                 mine.append(part)
 
+        clock["read_s"] = time.perf_counter() - t_start
+
         def run(block_list, image_ids):
+            t0 = time.perf_counter()
             index_of = {i: k for k, i in enumerate(image_ids)}
-            buf, counts = pad_descriptors([desc[i] for i in image_ids], options.max_num_matches)
+            buf, counts = pad_descriptors([desc[i] for i in image_ids], options.max_num_matches,
+                                          staging=matcher._host_staging)
             resident = matcher.upload(buf, counts, rule=rule)
+            clock["upload_s"] += time.perf_counter() - t0
+            t0 = time.perf_counter()
             for blk in block_list:
                 idx = np.array([(index_of[a], index_of[b]) for a, b in blk], dtype=np.int32)
                 out = matcher.match_resident(resident, idx, options.max_ratio, options.max_distance,
                                              options.cross_check, pairs_per_launch)
                 for (a, b), m in zip(blk, out):
                     results[(a, b)] = m if m.shape[0] >= options.min_num_matches else np.zeros((0, 2), np.uint32)
+            clock["match_s"] += time.perf_counter() - t0
 
         if mine:
             kmax = min(max(max((int(v.shape[0]) for v in desc.values()), default=1), 1), options.max_num_matches)
@@ -469,10 +496,14 @@ def match_exhaustive(database_path, matching_options: Optional[FeatureMatchingOp
                 for blk in mine:
                     used = sorted({i for pr in blk for i in pr}, key=ids.index)
                     run([blk], used)
+        t0 = time.perf_counter()
         if rank == 0 and world_size == 1:
             with db.transaction():
                 for (a, b), m in results.items():
                     db.write_matches(a, b, m)
+        clock["write_s"] = time.perf_counter() - t0
+    if stats is not None:
+        stats.update(clock)
     return results
 
 
@@ -501,7 +532,7 @@ def guided_matching(database_path, matching_options: Optional[FeatureMatchingOpt
         ids = sorted({i for pr, _ in todo for i in pr})
         index_of = {i: k for k, i in enumerate(ids)}
         descs = [db.read_descriptors(i) for i in ids]
-        buf, counts = pad_descriptors(descs, options.max_num_matches)
+        buf, counts = pad_descriptors(descs, options.max_num_matches, staging=matcher._host_staging)
         kmax = int(buf.shape[1])
         kps = np.zeros((len(ids), kmax, 2), np.float32)
         for k, i in enumerate(ids):
