@@ -16,15 +16,36 @@ n_img = int(sys.argv[1]) if len(sys.argv) > 1 else 8
 K = int(sys.argv[2]) if len(sys.argv) > 2 else 8192
 d = int(sys.argv[3]) if len(sys.argv) > 3 else 128
 m = Matcher(0)
-pairs_l = [(i, j) for i in range(n_img) for j in range(i + 1, n_img)]
+# scene: image i > 0 shows image 0's points moved by a homography (H test) or along their epipolar
+# lines (F test), in permuted row order, descriptors perturbed; pairs (0, i) carry that model
+pairs_l = [(0, j) for j in range(1, n_img)]
 pairs = torch.tensor(pairs_l, dtype=torch.int32, device="cuda")
 counts = torch.full((n_img,), K, dtype=torch.int32, device="cuda")
 g = torch.Generator(device="cuda").manual_seed(1)
-x = torch.randn((n_img, K, d), device="cuda", generator=g).abs()
-x = (x / x.norm(dim=2, keepdim=True)).to(torch.bfloat16)
-kp = torch.rand((n_img, K, 2), device="cuda", generator=g) * torch.tensor([1600.0, 1200.0], device="cuda")
 H = np.array([[1.01, 0.02, 5.0], [-0.01, 0.99, -3.0], [1e-5, 2e-5, 1.0]])
 F = np.array([[0.0, 0.0, 0.0], [0.0, 0.0, -1.0], [0.0, 1.0, 0.0]])
+Ht = torch.tensor(H, dtype=torch.float64, device="cuda")
+
+
+def scene(kind):
+    base = torch.randn((K, d), device="cuda", generator=g).abs()
+    kp0 = torch.rand((K, 2), device="cuda", generator=g, dtype=torch.float64) * torch.tensor([1600.0, 1200.0], device="cuda")
+    xs, ks = [base], [kp0]
+    for _ in range(1, n_img):
+        perm = torch.randperm(K, device="cuda", generator=g)
+        xs.append((base + 0.15 * torch.randn((K, d), device="cuda", generator=g)).abs()[perm])
+        if kind == "H":
+            q = torch.cat([kp0, torch.ones((K, 1), device="cuda", dtype=torch.float64)], 1) @ Ht.T
+            moved = q[:, :2] / q[:, 2:]
+        else:
+            moved = kp0.clone()
+            moved[:, 0] += (torch.rand((K,), device="cuda", generator=g, dtype=torch.float64) - 0.5) * 100
+        ks.append((moved + 0.5 * torch.randn((K, 2), device="cuda", generator=g, dtype=torch.float64))[perm])
+    x = torch.stack(xs)
+    return (x / x.norm(dim=2, keepdim=True)).to(torch.bfloat16).contiguous(), torch.stack(ks).float().contiguous()
+
+
+x, kp = scene("H")
 need = int(m.lib.vc_match_workspace_bytes(len(pairs_l), K))
 ws = torch.empty(need, dtype=torch.uint8, device="cuda")
 matches = torch.empty((len(pairs_l), K, 2), dtype=torch.int32, device="cuda")
@@ -53,7 +74,8 @@ def plain():
 
 ms = timed(plain)
 print(f"unguided (fused single-pass kernel): {ms / len(pairs_l) * 1e3:8.1f} us/pair")
-for name, geo in (("H (SiftGPU rule: H and F tests)", PairGeometry(4, None, H, 4.0)), ("F (SiftGPU rule)", PairGeometry(3, F, None, 4.0))):
+for name, kind, geo in (("H (SiftGPU rule)", "H", PairGeometry(4, None, H, 4.0)), ("F (SiftGPU rule)", "F", PairGeometry(3, F, None, 4.0))):
+    x, kp = scene(kind)
     arr = (_lib.PairGeometry * len(pairs_l))(*[geo.to_c(0) for _ in pairs_l])
     geo_dev = torch.frombuffer(bytearray(bytes(arr)), dtype=torch.uint8).cuda()
 

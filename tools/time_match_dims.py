@@ -1,6 +1,8 @@
 """Times the fused matcher (top-2 stage only, CUDA events) over descriptor dimensions:
-python tools/time_match_dims.py [n_images=16] [kpts=8192]   (VC_MATCH_2CTA=1 selects the two-SM kernel)"""
+python tools/time_match_dims.py [n_images=16] [kpts=8192] [d ...]   (VC_MATCH_2CTA=1 selects the two-SM kernel;
+VC_MATCH_NO_PRUNE=1 switches the pruning bound off; VC_BENCH_NONNEG=1 uses |unit rows|, cosine ~0.64 between unrelated rows)"""
 import ctypes
+import os
 import sys
 from pathlib import Path
 
@@ -16,9 +18,12 @@ m = Matcher(0)
 pairs = torch.tensor([(i, j) for i in range(n_img) for j in range(i + 1, n_img)], dtype=torch.int32, device="cuda")
 counts = torch.full((n_img,), K, dtype=torch.int32, device="cuda")
 opt = m._opts(0.8, 0.7, True, 1.0)
-for d in (64, 128, 256, 384, 768, 1024):
+dims = [int(a) for a in sys.argv[3:]] or [64, 128, 256, 384, 768, 1024]
+for d in dims:
     g = torch.Generator(device="cuda").manual_seed(d)
     x = torch.randn((n_img, K, d), device="cuda", generator=g)
+    if os.environ.get("VC_BENCH_NONNEG"):
+        x = x.abs()
     x = (x / x.norm(dim=2, keepdim=True)).to(torch.bfloat16)
     need = int(m.lib.vc_match_workspace_bytes(len(pairs), K))
     ws = torch.empty(need, dtype=torch.uint8, device="cuda")

@@ -31,6 +31,7 @@
 
 #include "vc_ptx.cuh"
 #include "vc_launch.cuh"
+#include "match_epilogue.cuh"
 
 namespace vc {
 
@@ -272,101 +273,24 @@ match_fused2_kernel(const __grid_constant__ CUtensorMap tmap, const MatchParams 
         float thr = 0.f;
         if (row_ok) thr = fmaxf(p.prune, __uint_as_float(__ldcg(p.rowthr + pair_row0 + row)));
         const unsigned long long row_tag = 0xFFFFFFFFu - (unsigned)row;
-        float best = 0.f, second = 0.f;
-        int bidx = -1;
+        RowTop2 rs{0.f, 0.f, -1};
         const uint32_t as = tile & 1, aph = (tile >> 1) & 1;
         mbar_wait(tfull_bar(as), aph);
         tc_fence_after();
         const uint32_t t_addr = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + as * BN;
 #pragma unroll 1
-        for (int c = c_begin; c < c_end; ++c) {
-          uint32_t vr[32];
-          tmem_ld_32x32(t_addr + c * 32, vr);
-          tmem_wait_ld();
-          float v[32];
-#pragma unroll
-          for (int e = 0; e < 32; ++e) v[e] = __uint_as_float(vr[e]);
-          if (!row_ok) {  // padding rows of the last row tile must not reach the column state
-#pragma unroll
-            for (int e = 0; e < 32; ++e) v[e] = 0.f;
-          }
-          if (c * 32 + 32 > ncols) {
-#pragma unroll
-            for (int e = 0; e < 32; ++e)
-              if (c * 32 + e >= ncols) v[e] = 0.f;
-          }
-          // ---- columns: per-lane mask of scores that beat the column's current second-best
-          const uint4* thr4 = reinterpret_cast<const uint4*>(colsec + c * 32);
-          unsigned cm = 0;
-#pragma unroll
-          for (int g = 0; g < 8; ++g) {
-            const uint4 t4 = thr4[g];
-            cm |= (v[4 * g + 0] > __uint_as_float(t4.x)) ? (1u << (4 * g + 0)) : 0u;
-            cm |= (v[4 * g + 1] > __uint_as_float(t4.y)) ? (1u << (4 * g + 1)) : 0u;
-            cm |= (v[4 * g + 2] > __uint_as_float(t4.z)) ? (1u << (4 * g + 2)) : 0u;
-            cm |= (v[4 * g + 3] > __uint_as_float(t4.w)) ? (1u << (4 * g + 3)) : 0u;
-          }
-          // ---- rows: group maxima decide whether the running top-2 can change
-          float gm[4];
-#pragma unroll
-          for (int g = 0; g < 4; ++g) {
-            float m = v[8 * g];
-#pragma unroll
-            for (int e = 1; e < 8; ++e) m = fmaxf(m, v[8 * g + e]);
-            gm[g] = m;
-          }
-          const float cmax = fmaxf(fmaxf(gm[0], gm[1]), fmaxf(gm[2], gm[3]));
-          const unsigned any_col = __reduce_or_sync(0xffffffffu, cm);
-          const bool any_row = __any_sync(0xffffffffu, cmax > second && cmax >= thr);
-          if (any_col) {
-#pragma unroll
-            for (int g = 0; g < 8; ++g) {
-              if (any_col & (0xFu << (4 * g))) {  // warp-uniform
-#pragma unroll
-                for (int e = 0; e < 4; ++e) {
-                  if (cm & (1u << (4 * g + e))) {
-                    // every score above the threshold is merged: the key keeps the best score
-                    // and, on ties, the lowest row; each loser's score feeds the second-best
-                    const int jl = c * 32 + 4 * g + e;
-                    const unsigned xb = __float_as_uint(v[4 * g + e]);
-                    const unsigned long long key = ((unsigned long long)xb << 32) | row_tag;
-                    const unsigned long long old = atomicMax(colkey + jl, key);
-                    const unsigned cand = key > old ? (unsigned)(old >> 32) : xb;
-                    atomicMax(colsec + jl, cand);
-                  }
-                }
-              }
-            }
-          }
-          if (any_row) {
-            const int colbase = it.cb * BN + c * 32;
-#pragma unroll
-            for (int g = 0; g < 4; ++g) {
-              if (gm[g] > second && gm[g] >= thr) {
-#pragma unroll
-                for (int e = 0; e < 8; ++e) {
-                  const float sc = v[8 * g + e];
-                  if (sc > best) {
-                    second = best;
-                    best = sc;
-                    bidx = colbase + 8 * g + e;
-                  } else if (sc > second) {
-                    second = sc;
-                  }
-                }
-              }
-            }
-          }
-        }
+        for (int c = c_begin; c < c_end; ++c)
+          fused_epilogue_chunk(t_addr + c * 32, c, ncols, row_ok, row_tag, thr, it.cb * BN + c * 32, lane, p.dense_min,
+                               colkey, colsec, rs);
         tc_fence_before();
         __syncwarp();
         if (lane == 0) mbar_arrive_cluster(lead_tempty[as]);
         if (row_ok) {
           const size_t o = ((size_t)it.pair * p.cb_per_img * kEpiGroups + it.cb * kEpiGroups + h) * p.kmax + row;
-          p.part_best[o] = best;
-          p.part_second[o] = second;
-          p.part_idx[o] = bidx;
-          if (second > thr) atomicMax(p.rowthr + pair_row0 + row, __float_as_uint(second));
+          p.part_best[o] = rs.best;
+          p.part_second[o] = rs.second;
+          p.part_idx[o] = rs.idx;
+          if (rs.second > thr) atomicMax(p.rowthr + pair_row0 + row, __float_as_uint(rs.second));
         }
       }
       // ---- column block finished in this CTA (its half of the row tiles): state -> HBM, merged with

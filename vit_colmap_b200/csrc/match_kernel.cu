@@ -169,6 +169,9 @@ match_top2_kernel(const __grid_constant__ CUtensorMap tmap, const MatchParams p)
       GuidedGeometry geom;
       float rx = 0.f, ry = 0.f;
       const float2* kp_n = nullptr;
+      GuidedA row_a{}, col_a{};   // products with H / F of the image-1 point: this row's (direction 0) or
+      GuidedB row_b{}, col_b{};   // this lane's column's (direction 1); likewise for the image-2 point
+      bool skip_h = false;
       if (kGuided) {
         geom = p.geom[it.pair];
         const int km = it.img_m >= p.kp_images ? it.img_m - p.kp_images : it.img_m;
@@ -180,6 +183,9 @@ match_top2_kernel(const __grid_constant__ CUtensorMap tmap, const MatchParams p)
           rx = r.x;
           ry = r.y;
         }
+        skip_h = geom.mode == 0 && geom.max_h >= 1e19f;
+        if (it.dir == 0) row_a = guided_features_a(geom, rx, ry);
+        else row_b = guided_features_b(geom, rx, ry);
       }
       for (int ct = 0; ct < ntiles; ++ct, ++tile) {
         const uint32_t as = tile & 1, aph = (tile >> 1) & 1;
@@ -201,20 +207,14 @@ match_top2_kernel(const __grid_constant__ CUtensorMap tmap, const MatchParams p)
             for (int e = 0; e < 32; ++e)
               if (colbase + e >= it.n_n) v[e] = 0.f;
           }
+          // guided matching: lane e holds the keypoint of column colbase + e; the gate itself is evaluated
+          // lazily below, only for candidates that could still change this row's top-2
+          float2 mine = make_float2(0.f, 0.f);
           if (kGuided) {
-            // Candidates that violate the pair's geometry score `masked_score` (SIFTGPU/ProgramCU.cu:1573-1603
-            // drives them to <= 0, COLMAP/feature/sift.cc:945-951 to distance 512^2).  Direction 1 has the
-            // roles swapped: the row is the image-2 keypoint.  Lane e fetches column e's keypoint once.
             const int cj = colbase + lane;
-            const float2 mine = cj < it.n_n ? __ldg(kp_n + cj) : make_float2(0.f, 0.f);
-#pragma unroll
-            for (int e = 0; e < 32; ++e) {
-              const float cx = __shfl_sync(0xffffffffu, mine.x, e), cy = __shfl_sync(0xffffffffu, mine.y, e);
-              if (colbase + e < it.n_n) {
-                const bool keep = it.dir == 0 ? guided_keep(geom, rx, ry, cx, cy) : guided_keep(geom, cx, cy, rx, ry);
-                if (!keep) v[e] = p.masked_score;
-              }
-            }
+            if (cj < it.n_n) mine = __ldg(kp_n + cj);
+            if (it.dir == 0) col_b = guided_features_b(geom, mine.x, mine.y);
+            else col_a = guided_features_a(geom, mine.x, mine.y);
           }
           if (kDebug) {
             if (p.dbg_scores != nullptr && it.pair == 0 && it.dir == 0 && row < it.n_m) {
@@ -229,11 +229,49 @@ match_top2_kernel(const __grid_constant__ CUtensorMap tmap, const MatchParams p)
             float m = v[8 * g];
 #pragma unroll
             for (int e = 1; e < 8; ++e) m = fmaxf(m, v[8 * g + e]);
+            // a gated candidate scores masked_score, which under rule l2 may exceed its own score
+            if (kGuided) m = fmaxf(m, p.masked_score);
             // Nothing in this group can change (best, second, idx) unless it beats `second`.
             if (__any_sync(0xffffffffu, m > second)) {
 #pragma unroll
               for (int e = 0; e < 8; ++e) {
-                const float s = v[8 * g + e];
+                float s = v[8 * g + e];
+                if (kGuided) {
+                  // Candidates that violate the pair's geometry score `masked_score` (SIFTGPU/ProgramCU.cu:1573-1603
+                  // drives them to <= 0, COLMAP/feature/sift.cc:945-951 to distance 512^2).  Only a candidate whose
+                  // gated or ungated score beats `second` can matter, so the residuals are evaluated for those
+                  // alone.  Direction 1 has the roles swapped: the row is the image-2 keypoint.
+                  // the other point's products come from the lane that holds column 8g+e (warp-uniform shuffles)
+                  constexpr unsigned kAll = 0xffffffffu;
+                  const int src = 8 * g + e;
+                  const float cx = __shfl_sync(kAll, mine.x, src), cy = __shfl_sync(kAll, mine.y, src);
+                  GuidedA A = row_a;
+                  GuidedB B = row_b;
+                  if (it.dir == 0) {
+                    B.x = cx;
+                    B.y = cy;
+                    B.n2 = __shfl_sync(kAll, col_b.n2, src);
+                  } else {
+                    if (geom.mode != 1 && !skip_h) {
+                      A.a = __shfl_sync(kAll, col_a.a, src);
+                      A.b = __shfl_sync(kAll, col_a.b, src);
+                      A.c = __shfl_sync(kAll, col_a.c, src);
+                      A.hb = __shfl_sync(kAll, col_a.hb, src);
+                    }
+                    if (geom.mode != 2) {
+                      A.f0 = __shfl_sync(kAll, col_a.f0, src);
+                      A.f1 = __shfl_sync(kAll, col_a.f1, src);
+                      A.f2 = __shfl_sync(kAll, col_a.f2, src);
+                      A.n1 = __shfl_sync(kAll, col_a.n1, src);
+                    }
+                  }
+                  if (fmaxf(s, p.masked_score) > second && colbase + src < it.n_n) {
+                    int keep = guided_fast(geom.mode, skip_h, geom.max_f, A, B);
+                    if (keep < 0)  // residual within rounding of the bound: the exactly specified form decides
+                      keep = it.dir == 0 ? guided_keep(geom, rx, ry, cx, cy) : guided_keep(geom, cx, cy, rx, ry);
+                    if (!keep) s = p.masked_score;
+                  }
+                }
                 if (s > best) {  // strict '>' keeps the lowest index on ties (sift.cc:747-751)
                   second = best;
                   best = s;

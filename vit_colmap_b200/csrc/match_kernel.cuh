@@ -39,6 +39,7 @@ struct MatchParams {
   unsigned long long* col_key;  // two-SM kernel: [n_pairs, 2 (cta rank), kmax] column states
   unsigned int* col_sec;
   float prune;            // raw-score bound below which a score can change no accept / reject decision (0 = off)
+  int dense_min;          // hit columns per 32x32 chunk from which the column merge takes the warp-reduction path
   int stagger;            // row-tile offset per column block (0 = every CTA of a pair sweeps in the same order)
   unsigned int* rowthr;   // [n_pairs, kmax] float bits: lower bound of each row's final second-best
   float* part_best;       // [n_pairs, 2*cb_per_img, kmax] row partials, one per 128 columns
@@ -99,6 +100,63 @@ __device__ __forceinline__ int accept_scores(float best, float second, int idx, 
   const float t2 = (float)acos((double)fminf(p.inv_norm * second, 1.0f));
   if (t1 >= p.max_ratio * t2) return -1;
   return idx;
+}
+
+// Fast form of the same decision.  Per point, the products with H and F are formed once
+// (image-1 point: H p1 and the bound max_h * c^2, F p1 and |F p1|_xy^2; image-2 point: |F^T p2|_xy^2), so a
+// candidate costs a handful of FMAs and no division:
+//   homography : (a - x2 c)^2 + (b - y2 c)^2   against  max_h * c^2
+//   epipolar   : (x2 fx0 + y2 fx1 + fx2)^2     against  max_f * (|F p1|_xy^2 + |F^T p2|_xy^2)
+// These differ from guided_keep's separately rounded operations by rounding only, so the fast form
+// decides just the candidates whose residual is outside a +-1/64 band around the bound (far more than the
+// rounding differences for pixel coordinates and max_error >= 0.25 px); it returns -1 inside the band
+// (and for degenerate denominators) and the caller falls back to guided_keep.  Decisions are therefore
+// those of guided_keep, at a fraction of the cost.
+struct GuidedA {  // image-1 point
+  float a, b, c, hb, f0, f1, f2, n1;
+};
+struct GuidedB {  // image-2 point
+  float x, y, n2;
+};
+__device__ __forceinline__ GuidedA guided_features_a(const GuidedGeometry& g, float x1, float y1) {
+  GuidedA A;
+  A.a = fmaf(g.h[0], x1, fmaf(g.h[1], y1, g.h[2]));
+  A.b = fmaf(g.h[3], x1, fmaf(g.h[4], y1, g.h[5]));
+  A.c = fmaf(g.h[6], x1, fmaf(g.h[7], y1, g.h[8]));
+  A.hb = g.max_h * A.c * A.c;
+  A.f0 = fmaf(g.f[0], x1, fmaf(g.f[1], y1, g.f[2]));
+  A.f1 = fmaf(g.f[3], x1, fmaf(g.f[4], y1, g.f[5]));
+  A.f2 = fmaf(g.f[6], x1, fmaf(g.f[7], y1, g.f[8]));
+  A.n1 = fmaf(A.f0, A.f0, A.f1 * A.f1);
+  return A;
+}
+__device__ __forceinline__ GuidedB guided_features_b(const GuidedGeometry& g, float x2, float y2) {
+  GuidedB B;
+  B.x = x2;
+  B.y = y2;
+  const float t0 = fmaf(g.f[0], x2, fmaf(g.f[3], y2, g.f[6]));
+  const float t1 = fmaf(g.f[1], x2, fmaf(g.f[4], y2, g.f[7]));
+  B.n2 = fmaf(t0, t0, t1 * t1);
+  return B;
+}
+// 1 keep, 0 drop, -1 undecided.  skip_h: mode 0 with the homography absent (identity, bound 1e20:
+// SIFTGPU/SiftMatch.cpp:684) -- that test passes for every finite keypoint pair.
+__device__ __forceinline__ int guided_fast(int mode, bool skip_h, float max_f, const GuidedA& A, const GuidedB& B) {
+  constexpr float kLo = 1.f - 1.f / 64.f, kHi = 1.f + 1.f / 64.f;
+  int h = 1, f = 1;  // 1 below the bound, 0 above, -1 in the band
+  if (mode != 1 && !skip_h) {
+    const float u = fmaf(-B.x, A.c, A.a), w = fmaf(-B.y, A.c, A.b);
+    const float r = fmaf(u, u, w * w);
+    h = r < A.hb * kLo ? 1 : (r > A.hb * kHi ? 0 : -1);
+  }
+  if (mode != 2) {
+    const float e = fmaf(B.x, A.f0, fmaf(B.y, A.f1, A.f2));
+    const float r = e * e, bound = max_f * (A.n1 + B.n2);
+    f = r < bound * kLo ? 1 : (r > bound * kHi ? 0 : -1);
+  }
+  if (h == 0 || f == 0) return 0;   // one test certainly fails: dropped under every mode
+  if (h < 0 || f < 0) return -1;
+  return 1;
 }
 
 int match_smem_bytes();
