@@ -1,5 +1,5 @@
 """Times guided matching (vc_match_pairs_guided: geometric gate in the GEMM epilogue) next to the
-unguided matcher on the same descriptors:  python tools/time_guided.py [n_images=8] [kpts=8192] [d=128]
+unguided matcher on the same descriptors:  python tools/time_guided.py [n_images=8] [kpts=8192] [d=128] [signed]
 Rates are per pair (both directions, cross check, emit) with CUDA events on the launching stream."""
 import ctypes
 import sys
@@ -15,6 +15,7 @@ from vit_colmap_b200.matching import Matcher, PairGeometry  # noqa: E402
 n_img = int(sys.argv[1]) if len(sys.argv) > 1 else 8
 K = int(sys.argv[2]) if len(sys.argv) > 2 else 8192
 d = int(sys.argv[3]) if len(sys.argv) > 3 else 128
+signed = len(sys.argv) > 4 and sys.argv[4] == "signed"   # default: non-negative rows (uint8-descriptor-like, cosine ~0.64)
 m = Matcher(0)
 # scene: image i > 0 shows image 0's points moved by a homography (H test) or along their epipolar
 # lines (F test), in permuted row order, descriptors perturbed; pairs (0, i) carry that model
@@ -28,12 +29,13 @@ Ht = torch.tensor(H, dtype=torch.float64, device="cuda")
 
 
 def scene(kind):
-    base = torch.randn((K, d), device="cuda", generator=g).abs()
+    fold = (lambda t: t) if signed else torch.abs
+    base = fold(torch.randn((K, d), device="cuda", generator=g))
     kp0 = torch.rand((K, 2), device="cuda", generator=g, dtype=torch.float64) * torch.tensor([1600.0, 1200.0], device="cuda")
     xs, ks = [base], [kp0]
     for _ in range(1, n_img):
         perm = torch.randperm(K, device="cuda", generator=g)
-        xs.append((base + 0.15 * torch.randn((K, d), device="cuda", generator=g)).abs()[perm])
+        xs.append(fold(base + 0.15 * torch.randn((K, d), device="cuda", generator=g))[perm])
         if kind == "H":
             q = torch.cat([kp0, torch.ones((K, 1), device="cuda", dtype=torch.float64)], 1) @ Ht.T
             moved = q[:, :2] / q[:, 2:]

@@ -33,7 +33,8 @@ constexpr int kBBytes = BN * BK * 2;
 constexpr int kStageBytes = kABytes + kBBytes;
 constexpr int kThreads = 256;      // warp0 TMA, warp1 MMA, warp2 TMEM alloc, warps4-7 epilogue
 constexpr int kTmemCols = 512;     // 2 accumulator stages x 256 fp32 columns
-constexpr int kSmemBytes = kStages * kStageBytes + 1024 /*align slack*/ + 256 /*barriers*/;
+constexpr int kGuidedFeatBytes = 4 * 32 * 2 * 16;  // guided matching: per epilogue warp, 32 columns x 2 float4
+constexpr int kSmemBytes = kStages * kStageBytes + 1024 /*align slack*/ + 256 /*barriers*/ + kGuidedFeatBytes;
 
 struct Item {
   int pair, dir, rb, img_m, img_n, n_m, n_n;
@@ -74,6 +75,8 @@ match_top2_kernel(const __grid_constant__ CUtensorMap tmap, const MatchParams p)
   auto tfull_bar = [&](int s) { return bar0 + 8u * (2 * kStages + s); };
   auto tempty_bar = [&](int s) { return bar0 + 8u * (2 * kStages + 2 + s); };
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * kStages + 4);
+  float4* feat_all = reinterpret_cast<float4*>(smem + kStages * kStageBytes + 256);
+  (void)feat_all;
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
@@ -163,15 +166,19 @@ match_top2_kernel(const __grid_constant__ CUtensorMap tmap, const MatchParams p)
       if (!it.valid) continue;
       const int ntiles = (it.n_n + BN - 1) / BN;
       const int row = it.rb * BM + q * 32 + lane;
-      float best = 0.f, second = 0.f;  // sift.cc:742-743
-      int bidx = -1;                   // sift.cc:741
+      // sift.cc:741-743 start best = second = 0, idx = -1.  p.prune (guided match lists only, 0 otherwise) is the
+      // bound below which a score can change no accept / reject decision (vc_api.cu, match_impl): starting
+      // there instead of at 0 gives the same match list and spares the geometric gate for every such score.
+      float best = kGuided ? p.prune : 0.f, second = best;
+      int bidx = -1;
       // guided matching: this row's keypoint, the pair's geometry, the other image's keypoint rows
       GuidedGeometry geom;
       float rx = 0.f, ry = 0.f;
       const float2* kp_n = nullptr;
-      GuidedA row_a{}, col_a{};   // products with H / F of the image-1 point: this row's (direction 0) or
-      GuidedB row_b{}, col_b{};   // this lane's column's (direction 1); likewise for the image-2 point
+      GuidedA row_a{};   // this row's keypoint as image-1 point (direction 0) ...
+      GuidedB row_b{};   // ... or as image-2 point (direction 1): its products with H / F
       bool skip_h = false;
+      float4* feat = feat_all + (warp - 4) * 64;  // this warp's staging: 32 columns x 2 float4
       if (kGuided) {
         geom = p.geom[it.pair];
         const int km = it.img_m >= p.kp_images ? it.img_m - p.kp_images : it.img_m;
@@ -207,14 +214,66 @@ match_top2_kernel(const __grid_constant__ CUtensorMap tmap, const MatchParams p)
             for (int e = 0; e < 32; ++e)
               if (colbase + e >= it.n_n) v[e] = 0.f;
           }
-          // guided matching: lane e holds the keypoint of column colbase + e; the gate itself is evaluated
-          // lazily below, only for candidates that could still change this row's top-2
-          float2 mine = make_float2(0.f, 0.f);
           if (kGuided) {
-            const int cj = colbase + lane;
-            if (cj < it.n_n) mine = __ldg(kp_n + cj);
-            if (it.dir == 0) col_b = guided_features_b(geom, mine.x, mine.y);
-            else col_a = guided_features_a(geom, mine.x, mine.y);
+            // Geometric gate of guided matching.  Candidates that violate the pair's geometry score
+            // `masked_score` (SIFTGPU/ProgramCU.cu:1573-1603 drives them to <= 0, COLMAP/feature/sift.cc:945-951
+            // to distance 512^2).  Lane e holds the keypoint of column colbase + e and stages that point's
+            // products with H / F in shared memory; every lane then reads entry e as a broadcast load and
+            // decides all 32 candidates of its row branch-free (guided_fast); the few candidates whose
+            // residual lies within rounding of the bound are re-decided by the exactly specified form.
+            // Skipped for a chunk in which no score, gated or not, can enter any row's top-2.
+            // Direction 1 has the roles swapped: the row is the image-2 keypoint.
+            float cmx = v[0];
+#pragma unroll
+            for (int e = 1; e < 32; ++e) cmx = fmaxf(cmx, v[e]);
+            if (__any_sync(0xffffffffu, fmaxf(cmx, p.masked_score) > second)) {
+              const int cj = colbase + lane;
+              const float2 mine = cj < it.n_n ? __ldg(kp_n + cj) : make_float2(0.f, 0.f);
+              float4* slot = feat + 2 * lane;
+              if (it.dir == 0) {
+                const GuidedB cb = guided_features_b(geom, mine.x, mine.y);
+                slot[0] = make_float4(cb.x, cb.y, cb.n2, 0.f);
+              } else {
+                const GuidedA ca = guided_features_a(geom, mine.x, mine.y);
+                slot[0] = make_float4(ca.a, ca.b, ca.c, ca.hb);
+                slot[1] = make_float4(ca.f0, ca.f1, ca.f2, ca.n1);
+              }
+              __syncwarp();
+              unsigned undecided = 0u;
+#pragma unroll
+              for (int e = 0; e < 32; ++e) {
+                GuidedA A = row_a;
+                GuidedB B = row_b;
+                const float4 lo = feat[2 * e];
+                if (it.dir == 0) {
+                  B.x = lo.x;
+                  B.y = lo.y;
+                  B.n2 = lo.z;
+                } else {
+                  const float4 hi = feat[2 * e + 1];
+                  A.a = lo.x; A.b = lo.y; A.c = lo.z; A.hb = lo.w;
+                  A.f0 = hi.x; A.f1 = hi.y; A.f2 = hi.z; A.n1 = hi.w;
+                }
+                const int keep = guided_fast(geom.mode, skip_h, geom.max_f, A, B);
+                const bool live = colbase + e < it.n_n;  // padding columns keep their score of 0
+                if (live && keep == 0) v[e] = p.masked_score;
+                if (live && keep < 0) undecided |= 1u << e;
+              }
+              const unsigned any_und = __reduce_or_sync(0xffffffffu, undecided);
+              if (any_und) {
+#pragma unroll
+                for (int e = 0; e < 32; ++e) {
+                  if (any_und & (1u << e)) {  // warp-uniform
+                    const float cx = __shfl_sync(0xffffffffu, mine.x, e), cy = __shfl_sync(0xffffffffu, mine.y, e);
+                    if (undecided & (1u << e)) {
+                      const bool keep = it.dir == 0 ? guided_keep(geom, rx, ry, cx, cy) : guided_keep(geom, cx, cy, rx, ry);
+                      if (!keep) v[e] = p.masked_score;
+                    }
+                  }
+                }
+              }
+              __syncwarp();  // the staging slots are rewritten by the next chunk
+            }
           }
           if (kDebug) {
             if (p.dbg_scores != nullptr && it.pair == 0 && it.dir == 0 && row < it.n_m) {
@@ -229,49 +288,11 @@ match_top2_kernel(const __grid_constant__ CUtensorMap tmap, const MatchParams p)
             float m = v[8 * g];
 #pragma unroll
             for (int e = 1; e < 8; ++e) m = fmaxf(m, v[8 * g + e]);
-            // a gated candidate scores masked_score, which under rule l2 may exceed its own score
-            if (kGuided) m = fmaxf(m, p.masked_score);
             // Nothing in this group can change (best, second, idx) unless it beats `second`.
             if (__any_sync(0xffffffffu, m > second)) {
 #pragma unroll
               for (int e = 0; e < 8; ++e) {
-                float s = v[8 * g + e];
-                if (kGuided) {
-                  // Candidates that violate the pair's geometry score `masked_score` (SIFTGPU/ProgramCU.cu:1573-1603
-                  // drives them to <= 0, COLMAP/feature/sift.cc:945-951 to distance 512^2).  Only a candidate whose
-                  // gated or ungated score beats `second` can matter, so the residuals are evaluated for those
-                  // alone.  Direction 1 has the roles swapped: the row is the image-2 keypoint.
-                  // the other point's products come from the lane that holds column 8g+e (warp-uniform shuffles)
-                  constexpr unsigned kAll = 0xffffffffu;
-                  const int src = 8 * g + e;
-                  const float cx = __shfl_sync(kAll, mine.x, src), cy = __shfl_sync(kAll, mine.y, src);
-                  GuidedA A = row_a;
-                  GuidedB B = row_b;
-                  if (it.dir == 0) {
-                    B.x = cx;
-                    B.y = cy;
-                    B.n2 = __shfl_sync(kAll, col_b.n2, src);
-                  } else {
-                    if (geom.mode != 1 && !skip_h) {
-                      A.a = __shfl_sync(kAll, col_a.a, src);
-                      A.b = __shfl_sync(kAll, col_a.b, src);
-                      A.c = __shfl_sync(kAll, col_a.c, src);
-                      A.hb = __shfl_sync(kAll, col_a.hb, src);
-                    }
-                    if (geom.mode != 2) {
-                      A.f0 = __shfl_sync(kAll, col_a.f0, src);
-                      A.f1 = __shfl_sync(kAll, col_a.f1, src);
-                      A.f2 = __shfl_sync(kAll, col_a.f2, src);
-                      A.n1 = __shfl_sync(kAll, col_a.n1, src);
-                    }
-                  }
-                  if (fmaxf(s, p.masked_score) > second && colbase + src < it.n_n) {
-                    int keep = guided_fast(geom.mode, skip_h, geom.max_f, A, B);
-                    if (keep < 0)  // residual within rounding of the bound: the exactly specified form decides
-                      keep = it.dir == 0 ? guided_keep(geom, rx, ry, cx, cy) : guided_keep(geom, cx, cy, rx, ry);
-                    if (!keep) s = p.masked_score;
-                  }
-                }
+                const float s = v[8 * g + e];
                 if (s > best) {  // strict '>' keeps the lowest index on ties (sift.cc:747-751)
                   second = best;
                   best = s;

@@ -104,6 +104,15 @@ int check_match_args(vc_handle* h, const void* desc, const int32_t* counts, int 
   return VC_OK;
 }
 
+// Exact pruning bound (angular rule, match lists only), as a raw score; 0 = no bound.
+float prune_bound(const vc_match_options* opt) {
+  if (opt->rule != 0 || !(opt->max_ratio > 0.f) || !(opt->inv_norm > 0.f) || getenv("VC_MATCH_NO_PRUNE")) return 0.f;
+  const double a = std::max((double)opt->max_distance / (double)opt->max_ratio, (double)opt->max_distance);
+  if (a >= 1.5707) return 0.f;
+  const double c = cos(a) - 1e-3;
+  return c > 0.0 ? (float)(c / (double)opt->inv_norm) : 0.f;
+}
+
 vc::MatchParams make_params(const int32_t* counts, const int32_t* pairs, int n_pairs, int kmax, int d,
                             const vc_match_options* opt, int32_t* m_out) {
   vc::MatchParams p{};
@@ -220,14 +229,7 @@ static int match_impl(vc_handle* h, const void* desc, const int32_t* counts, int
     // sift.cc:765-771) nor, as second-best, make the ratio test fail for one (t1 <= max_distance <
     // max_ratio * t2, sift.cc:773-780), so the epilogue never has to track it.  The diagnostics entry
     // (vc_match_pairs_top2) keeps the bound at 0 and returns exact top-2 values for every row.
-    p.prune = 0.f;
-    if (opt->rule == 0 && best == nullptr && opt->max_ratio > 0.f && opt->inv_norm > 0.f && !getenv("VC_MATCH_NO_PRUNE")) {
-      const double a = std::max((double)opt->max_distance / (double)opt->max_ratio, (double)opt->max_distance);
-      if (a < 1.5707) {
-        const double c = cos(a) - 1e-3;
-        if (c > 0.0) p.prune = (float)(c / (double)opt->inv_norm);
-      }
-    }
+    p.prune = best == nullptr ? prune_bound(opt) : 0.f;
     static const int stagger = [] {
       const char* e = getenv("VC_MATCH_STAGGER");
       return e ? atoi(e) : 2;
@@ -313,6 +315,7 @@ int vc_match_pairs_guided(vc_handle* h, const void* desc, const float* keypoints
   // a gated candidate scores 0 under the angular rule (never a match: best starts at 0, strict '>') and
   // squared distance 512^2 under the l2 rule (COLMAP/feature/sift.cc:945-946)
   p.masked_score = opt->rule == VC_RULE_L2 ? opt->l2_offset - 262144.f : 0.f;
+  p.prune = prune_bound(opt);
   VC_CUDA(vc::launch_match_top2_guided(h->map, p, h->num_sms, s));
   VC_CUDA(vc::launch_emit_matches(p, matches, n_matches, s));
   g_launches += 2;
