@@ -603,22 +603,24 @@ def run_db_e2e(torch, local):
     rng = np.random.default_rng(5)
     base = rng.standard_normal((4 * k, d)).astype(np.float32)
     with tempfile.TemporaryDirectory() as tmp:
-        path = os.path.join(tmp, "bench.db")
-        db = ColmapDatabase(path)
-        cam = db.add_pinhole_camera(640, 480, 500.0, 500.0, 320.0, 240.0)
-        for i in range(n_images):
-            rows = np.abs(base[rng.permutation(4 * k)[:k]] + 0.15 * rng.standard_normal((k, d)).astype(np.float32))
-            image_id = db.add_image(f"im{i:03d}.png", camera_id=cam)
-            db.add_keypoints(image_id, rng.uniform(0, 480, (k, 2)).astype(np.float32))
-            db.add_descriptors(image_id, om.to_uint8_colmap(rows / np.linalg.norm(rows, axis=1, keepdims=True)))
-        db.close()
+        def make_db(path):
+            db = ColmapDatabase(path)
+            cam = db.add_pinhole_camera(640, 480, 500.0, 500.0, 320.0, 240.0)
+            for i in range(n_images):
+                rows = np.abs(base[rng.permutation(4 * k)[:k]] + 0.15 * rng.standard_normal((k, d)).astype(np.float32))
+                image_id = db.add_image(f"im{i:03d}.png", camera_id=cam)
+                db.add_keypoints(image_id, rng.uniform(0, 480, (k, 2)).astype(np.float32))
+                db.add_descriptors(image_id, om.to_uint8_colmap(rows / np.linalg.norm(rows, axis=1, keepdims=True)))
+            db.close()
+            return path
         matcher = Matcher(local)
         opts = FeatureMatchingOptions(max_ratio=0.85, max_distance=0.9)
-        warm = np.zeros((2, 256, d), np.uint8)
-        matcher.match_pairs_host(warm, np.array([256, 256], np.int32), np.array([[0, 1]], np.int32))
+        # first database: warm-up (device staging, page-locked result buffers are allocated once per Matcher)
+        match_exhaustive(make_db(os.path.join(tmp, "warm.db")), opts, matcher=matcher)
+        path = make_db(os.path.join(tmp, "bench.db"))
         torch.cuda.synchronize()
-        t0 = time.perf_counter()
         stages = {}
+        t0 = time.perf_counter()
         res = match_exhaustive(path, opts, matcher=matcher, stats=stages)
         dt = time.perf_counter() - t0
         n_rows = sum(len(m) for m in res.values())

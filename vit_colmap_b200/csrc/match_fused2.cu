@@ -42,7 +42,7 @@ constexpr int kABytes = BM * BK * 2, kBBytes = (BN / 2) * BK * 2, kStageBytes = 
 constexpr int kEpiGroups = 3;   // epilogue warps per TMEM lane quarter: 3 / 3 / 2 of the eight 32-column chunks
 constexpr int kEpiWarps = 4 * kEpiGroups;
 constexpr int kEpiThreads = 32 * kEpiWarps;
-constexpr int kThreads = 128 + 32 * 12;  // warp0 TMA, warp1 MMA, warp2 TMEM alloc, warps 4-15 epilogue
+constexpr int kThreads = 128 + kEpiThreads;  // warp0 TMA, warp1 MMA, warp2 TMEM alloc, warps 4-15 epilogue
 constexpr int kTmemCols = 512;
 constexpr int kColStateBytes = BN * 8 + BN * 4;
 constexpr int kSmemBytes = kStages * kStageBytes + 1024 + 256 + kColStateBytes;
@@ -67,7 +67,7 @@ __device__ __forceinline__ FItem decode_fitem(const MatchParams& p, int item) {
   return it;
 }
 
-__device__ __forceinline__ void epi_bar_sync() { asm volatile("bar.sync 1, 384;" ::: "memory"); }
+__device__ __forceinline__ void epi_bar_sync() { asm volatile("bar.sync 1, %0;" ::"n"(kEpiThreads) : "memory"); }
 
 // ---- cluster / two-SM PTX (cta_group::2)
 __device__ __forceinline__ uint32_t cluster_rank() {
@@ -88,20 +88,6 @@ __device__ __forceinline__ void mbar_arrive_cluster(uint32_t cluster_addr) {
   // default semantics (.release.cta): no cluster-scope fence, which would wait for this warp's
   // outstanding global stores.  TMEM hand-over is ordered by the tcgen05 fences on either side.
   asm volatile("mbarrier.arrive.shared::cluster.b64 _, [%0];" ::"r"(cluster_addr) : "memory");
-}
-__device__ __forceinline__ void mbar_wait_cluster(uint32_t bar, uint32_t parity) {
-  uint32_t ok = 0;
-  while (!ok) {
-    asm volatile(
-        "{\n\t"
-        ".reg .pred p;\n\t"
-        "mbarrier.try_wait.parity.acquire.cluster.shared::cta.b64 p, [%1], %2;\n\t"
-        "selp.u32 %0, 1, 0, p;\n\t"
-        "}"
-        : "=r"(ok)
-        : "r"(bar), "r"(parity)
-        : "memory");
-  }
 }
 // TMA load whose completion bytes are counted on the LEADER CTA's mbarrier (bar_leader is a
 // shared::cluster address of rank 0); the data lands in this CTA's shared memory.

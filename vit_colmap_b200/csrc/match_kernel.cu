@@ -239,26 +239,16 @@ match_top2_kernel(const __grid_constant__ CUtensorMap tmap, const MatchParams p)
                 slot[1] = make_float4(ca.f0, ca.f1, ca.f2, ca.n1);
               }
               __syncwarp();
-              unsigned undecided = 0u;
-#pragma unroll
-              for (int e = 0; e < 32; ++e) {
-                GuidedA A = row_a;
-                GuidedB B = row_b;
-                const float4 lo = feat[2 * e];
-                if (it.dir == 0) {
-                  B.x = lo.x;
-                  B.y = lo.y;
-                  B.n2 = lo.z;
-                } else {
-                  const float4 hi = feat[2 * e + 1];
-                  A.a = lo.x; A.b = lo.y; A.c = lo.z; A.hb = lo.w;
-                  A.f0 = hi.x; A.f1 = hi.y; A.f2 = hi.z; A.n1 = hi.w;
-                }
-                const int keep = guided_fast(geom.mode, skip_h, geom.max_f, A, B);
-                const bool live = colbase + e < it.n_n;  // padding columns keep their score of 0
-                if (live && keep == 0) v[e] = p.masked_score;
-                if (live && keep < 0) undecided |= 1u << e;
-              }
+              // which tests the pair's mode asks for (warp-uniform): 2 directions x {H, F, H and F}
+              const bool do_h = geom.mode != 1 && !skip_h, do_f = geom.mode != 2;
+              const int n_live = it.n_n - colbase;
+              unsigned undecided;
+#define VC_GATE(D, H, F) guided_gate_chunk<D, H, F>(feat, row_a, row_b, geom.max_f, p.masked_score, n_live, v)
+              if (it.dir == 0)
+                undecided = do_h ? (do_f ? VC_GATE(false, true, true) : VC_GATE(false, true, false)) : VC_GATE(false, false, true);
+              else
+                undecided = do_h ? (do_f ? VC_GATE(true, true, true) : VC_GATE(true, true, false)) : VC_GATE(true, false, true);
+#undef VC_GATE
               const unsigned any_und = __reduce_or_sync(0xffffffffu, undecided);
               if (any_und) {
 #pragma unroll

@@ -139,24 +139,68 @@ __device__ __forceinline__ GuidedB guided_features_b(const GuidedGeometry& g, fl
   B.n2 = fmaf(t0, t0, t1 * t1);
   return B;
 }
-// 1 keep, 0 drop, -1 undecided.  skip_h: mode 0 with the homography absent (identity, bound 1e20:
-// SIFTGPU/SiftMatch.cpp:684) -- that test passes for every finite keypoint pair.
-__device__ __forceinline__ int guided_fast(int mode, bool skip_h, float max_f, const GuidedA& A, const GuidedB& B) {
+// One candidate, branch-free: `drop` = one test certainly fails (dropped under every mode), `undecided` =
+// no test certainly fails but one is inside the band.  kH / kF: which tests the pair's mode asks for
+// (mode 0 with the homography absent -- identity, bound 1e20, SIFTGPU/SiftMatch.cpp:684 -- needs no H test:
+// it passes for every finite keypoint pair).
+template <bool kH, bool kF>
+__device__ __forceinline__ void guided_fast(float max_f, const GuidedA& A, const GuidedB& B, bool& drop, bool& undecided) {
   constexpr float kLo = 1.f - 1.f / 64.f, kHi = 1.f + 1.f / 64.f;
-  int h = 1, f = 1;  // 1 below the bound, 0 above, -1 in the band
-  if (mode != 1 && !skip_h) {
+  bool below = true, above = false;
+  if (kH) {
     const float u = fmaf(-B.x, A.c, A.a), w = fmaf(-B.y, A.c, A.b);
     const float r = fmaf(u, u, w * w);
-    h = r < A.hb * kLo ? 1 : (r > A.hb * kHi ? 0 : -1);
+    below = r < A.hb * kLo;
+    above = r > A.hb * kHi;
   }
-  if (mode != 2) {
+  if (kF) {
     const float e = fmaf(B.x, A.f0, fmaf(B.y, A.f1, A.f2));
     const float r = e * e, bound = max_f * (A.n1 + B.n2);
-    f = r < bound * kLo ? 1 : (r > bound * kHi ? 0 : -1);
+    below = below & (r < bound * kLo);
+    above = above | (r > bound * kHi);
   }
-  if (h == 0 || f == 0) return 0;   // one test certainly fails: dropped under every mode
-  if (h < 0 || f < 0) return -1;
-  return 1;
+  drop = above;
+  undecided = !above & !below;
+}
+
+// The gate over one 32-column chunk of a row: entry e of `feat` holds the staged products of column e's
+// keypoint (direction 0: image-2 point {x, y, n2, -}; direction 1: image-1 point {a, b, c, hb}, {f0, f1, f2, n1}).
+// Dropped candidates get `masked`; returns the bit mask of candidates the exact form has to decide.
+template <bool kDir1, bool kH, bool kF>
+__device__ __forceinline__ unsigned guided_gate_chunk(const float4* feat, const GuidedA& row_a, const GuidedB& row_b,
+                                                      float max_f, float masked, int n_live, float (&v)[32]) {
+  unsigned undecided = 0u;
+#pragma unroll
+  for (int e = 0; e < 32; ++e) {
+    GuidedA A = row_a;
+    GuidedB B = row_b;
+    const float4 lo = feat[2 * e];
+    if (!kDir1) {
+      B.x = lo.x;
+      B.y = lo.y;
+      B.n2 = lo.z;
+    } else {
+      if (kH) {
+        A.a = lo.x;
+        A.b = lo.y;
+        A.c = lo.z;
+        A.hb = lo.w;
+      }
+      if (kF) {
+        const float4 hi = feat[2 * e + 1];
+        A.f0 = hi.x;
+        A.f1 = hi.y;
+        A.f2 = hi.z;
+        A.n1 = hi.w;
+      }
+    }
+    bool drop, und;
+    guided_fast<kH, kF>(max_f, A, B, drop, und);
+    const bool live = e < n_live;  // padding columns keep their score of 0
+    v[e] = (live & drop) ? masked : v[e];
+    undecided |= (live & und) ? (1u << e) : 0u;
+  }
+  return undecided;
 }
 
 int match_smem_bytes();

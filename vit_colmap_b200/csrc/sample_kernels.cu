@@ -15,7 +15,6 @@ namespace vc {
 
 namespace {
 
-constexpr int kVec = kMaxChannels / 128;
 
 template <typename T>
 __device__ __forceinline__ float4 ld4(const T* row, int v);

@@ -15,7 +15,6 @@ namespace vc {
 
 namespace {
 
-constexpr int kVec = kMaxChannels / 128;  // float4 per lane for C = 1024
 constexpr int kStrip = 8;
 
 template <typename T>

@@ -68,6 +68,7 @@ class Matcher:
         self.handle = h
         self._ws = None
         self._host_staging: list = []   # page-locked staging of pad_descriptors, reused across uploads
+        self._out_cache = None          # host result slots of match_resident, reused across calls
 
     def close(self):
         if getattr(self, "handle", None):
@@ -260,7 +261,9 @@ class Matcher:
             chunk = pairs[s:s + pairs_per_call].copy()
             chunk[:, 1] += resident.second_offset
             n = chunk.shape[0]
-            matches = np.empty((n, kmax, 2), dtype=np.uint32)
+            if self._out_cache is None or self._out_cache.size < n * kmax * 2:
+                self._out_cache = np.empty((n * kmax * 2,), dtype=np.uint32)  # reused: fresh pages fault on first touch
+            matches = self._out_cache[: n * kmax * 2].reshape(n, kmax, 2)
             n_matches = np.zeros((n,), dtype=np.int32)
             _lib.check(self.lib.vc_match_pairs_resident(self.handle, _ptr(desc), resident.counts.ctypes.data, n_dev,
                                                         kmax, d, chunk.ctypes.data, n, ctypes.byref(opt),
