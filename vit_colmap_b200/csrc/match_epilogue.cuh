@@ -118,19 +118,20 @@ __device__ __forceinline__ void fused_epilogue_chunk(uint32_t taddr, int c, int 
     }
   }
   if (any_row) {
+    // A group of 8 is folded in when ANY lane's group maximum can enter its top-2 (warp-uniform test), and
+    // then with selects only: a per-lane branchy update (if / else if per score) cost 30 % of the kernel at
+    // d = 128 on data the pruning bound does not remove (profiles/r02_match_d128_noprune_hot_lines.txt).
+    // A lane whose state cannot change is unaffected by the selects (sc <= second leaves all three as is).
 #pragma unroll
     for (int g = 0; g < 4; ++g) {
-      if (gm[g] > rs.second && gm[g] >= thr) {
+      if (__any_sync(0xffffffffu, gm[g] > rs.second && gm[g] >= thr)) {
 #pragma unroll
         for (int e = 0; e < 8; ++e) {
           const float sc = v[8 * g + e];
-          if (sc > rs.best) {
-            rs.second = rs.best;
-            rs.best = sc;
-            rs.idx = colbase + 8 * g + e;
-          } else if (sc > rs.second) {
-            rs.second = sc;
-          }
+          const bool gt = sc > rs.best;  // strict: the lowest column keeps a tie (sift.cc:747-751)
+          rs.second = gt ? rs.best : fmaxf(rs.second, sc);
+          rs.idx = gt ? colbase + 8 * g + e : rs.idx;
+          rs.best = fmaxf(rs.best, sc);
         }
       }
     }
