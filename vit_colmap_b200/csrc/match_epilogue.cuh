@@ -3,8 +3,12 @@
 //   * the thread's running row state (best, second, index) -- COLMAP/feature/sift.cc:745-757, and
 //   * the CTA-wide column state in shared memory: a 64-bit key (score bits << 32 | ~row: the larger key
 //     is the better score, the lower row on ties) plus a 32-bit second-best per column.
-// A score takes part in the column state only if it beats the column's current second-best (one compare
-// per score against a broadcast shared-memory load).  Two merge paths:
+// A score takes part in the column state only if it beats the column's current second-best.  That test is
+// two-level: the maximum of each group of 8 scores (needed for the rows anyway) is first compared with the
+// smallest threshold of the group's 8 columns (colmin8, refreshed by the epilogue warps at every row tile;
+// a stale value is merely less selective), and only groups that pass for some lane compare score by score
+// against the per-column thresholds.  Once the thresholds have risen -- or start at the pruning bound --
+// most groups stop there.  Two merge paths:
 //   sparse : few columns of the chunk are hit -- every hit lane merges its own score with two shared-
 //            memory atomics (the usual case once the thresholds have risen);
 //   dense  : many columns are hit at once (the first row tiles of a work item, when the thresholds are
@@ -21,6 +25,21 @@
 
 namespace vc {
 
+// Refresh of colmin8 for the groups [g_begin, g_end) of 8 columns (lane l takes group g_begin + l).  Called by
+// every epilogue warp for its own chunks at each row tile; concurrent writers store lower bounds that
+// were valid when read, and the thresholds only rise.
+__device__ __forceinline__ void refresh_colmin8(const unsigned int* colsec, unsigned int* colmin8, int g_begin,
+                                                int g_end, int lane) {
+  const int g = g_begin + lane;
+  if (g < g_end) {
+    const uint4 a = *reinterpret_cast<const uint4*>(colsec + 8 * g);
+    const uint4 b = *reinterpret_cast<const uint4*>(colsec + 8 * g + 4);
+    // thresholds are non-negative floats: their bit patterns order like unsigned integers
+    colmin8[g] = min(min(min(a.x, a.y), min(a.z, a.w)), min(min(b.x, b.y), min(b.z, b.w)));
+  }
+  __syncwarp();
+}
+
 struct RowTop2 {
   float best, second;
   int idx;
@@ -30,7 +49,7 @@ struct RowTop2 {
 __device__ __forceinline__ void fused_epilogue_chunk(uint32_t taddr, int c, int ncols, bool row_ok,
                                                      unsigned long long row_tag, float thr, int colbase, int lane,
                                                      int dense_min, unsigned long long* colkey, unsigned int* colsec,
-                                                     RowTop2& rs) {
+                                                     const unsigned int* colmin8, RowTop2& rs) {
   uint32_t vr[32];
   tmem_ld_32x32(taddr, vr);
   tmem_wait_ld();
@@ -46,18 +65,7 @@ __device__ __forceinline__ void fused_epilogue_chunk(uint32_t taddr, int c, int 
     for (int e = 0; e < 32; ++e)
       if (c * 32 + e >= ncols) v[e] = 0.f;
   }
-  // ---- columns: per-lane mask of scores that beat the column's current second-best
-  const uint4* thr4 = reinterpret_cast<const uint4*>(colsec + c * 32);
-  unsigned cm = 0;
-#pragma unroll
-  for (int g = 0; g < 8; ++g) {
-    const uint4 t4 = thr4[g];
-    cm |= (v[4 * g + 0] > __uint_as_float(t4.x)) ? (1u << (4 * g + 0)) : 0u;
-    cm |= (v[4 * g + 1] > __uint_as_float(t4.y)) ? (1u << (4 * g + 1)) : 0u;
-    cm |= (v[4 * g + 2] > __uint_as_float(t4.z)) ? (1u << (4 * g + 2)) : 0u;
-    cm |= (v[4 * g + 3] > __uint_as_float(t4.w)) ? (1u << (4 * g + 3)) : 0u;
-  }
-  // ---- rows: group maxima decide whether the running top-2 can change
+  // ---- group maxima: they decide whether the row's running top-2 can change, and pre-filter the columns
   float gm[4];
 #pragma unroll
   for (int g = 0; g < 4; ++g) {
@@ -66,8 +74,29 @@ __device__ __forceinline__ void fused_epilogue_chunk(uint32_t taddr, int c, int 
     for (int e = 1; e < 8; ++e) m = fmaxf(m, v[8 * g + e]);
     gm[g] = m;
   }
+  // ---- columns: per-lane mask of scores that beat the column's current second-best
+  const uint4 tm = *reinterpret_cast<const uint4*>(colmin8 + c * 4);
+  unsigned gpass = (gm[0] > __uint_as_float(tm.x) ? 1u : 0u) | (gm[1] > __uint_as_float(tm.y) ? 2u : 0u) |
+                   (gm[2] > __uint_as_float(tm.z) ? 4u : 0u) | (gm[3] > __uint_as_float(tm.w) ? 8u : 0u);
+  gpass = __reduce_or_sync(0xffffffffu, gpass);
+  const uint4* thr4 = reinterpret_cast<const uint4*>(colsec + c * 32);
+  unsigned cm = 0;
+#pragma unroll
+  for (int g2 = 0; g2 < 4; ++g2) {
+    if (gpass & (1u << g2)) {  // warp-uniform
+#pragma unroll
+      for (int k = 0; k < 2; ++k) {
+        const int g = 2 * g2 + k;
+        const uint4 t4 = thr4[g];
+        cm |= (v[4 * g + 0] > __uint_as_float(t4.x)) ? (1u << (4 * g + 0)) : 0u;
+        cm |= (v[4 * g + 1] > __uint_as_float(t4.y)) ? (1u << (4 * g + 1)) : 0u;
+        cm |= (v[4 * g + 2] > __uint_as_float(t4.z)) ? (1u << (4 * g + 2)) : 0u;
+        cm |= (v[4 * g + 3] > __uint_as_float(t4.w)) ? (1u << (4 * g + 3)) : 0u;
+      }
+    }
+  }
   const float cmax = fmaxf(fmaxf(gm[0], gm[1]), fmaxf(gm[2], gm[3]));
-  const unsigned any_col = __reduce_or_sync(0xffffffffu, cm);
+  const unsigned any_col = gpass ? __reduce_or_sync(0xffffffffu, cm) : 0u;
   const bool any_row = __any_sync(0xffffffffu, cmax > rs.second && cmax >= thr);
   if (any_col) {
     if (__popc(any_col) >= dense_min) {

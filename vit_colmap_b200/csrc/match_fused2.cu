@@ -44,7 +44,7 @@ constexpr int kEpiWarps = 4 * kEpiGroups;
 constexpr int kEpiThreads = 32 * kEpiWarps;
 constexpr int kThreads = 128 + kEpiThreads;  // warp0 TMA, warp1 MMA, warp2 TMEM alloc, warps 4-15 epilogue
 constexpr int kTmemCols = 512;
-constexpr int kColStateBytes = BN * 8 + BN * 4;
+constexpr int kColStateBytes = BN * 8 + BN * 4 + (BN / 8) * 4;  // keys, seconds, per-8-column minima
 constexpr int kSmemBytes = kStages * kStageBytes + 1024 + 256 + kColStateBytes;
 
 struct FItem {
@@ -147,6 +147,7 @@ match_fused2_kernel(const __grid_constant__ CUtensorMap tmap, const MatchParams 
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * kStages + 4);
   unsigned long long* colkey = reinterpret_cast<unsigned long long*>(smem + kStages * kStageBytes + 256);
   unsigned int* colsec = reinterpret_cast<unsigned int*>(colkey + BN);
+  unsigned int* colmin8 = colsec + BN;
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
@@ -242,6 +243,7 @@ match_fused2_kernel(const __grid_constant__ CUtensorMap tmap, const MatchParams 
       if (et < BN) {
         colkey[et] = 0ull;
         colsec[et] = __float_as_uint(p.prune);  // scores at or below the bound never reach the column state
+        if (et < BN / 8) colmin8[et] = __float_as_uint(p.prune);
       }
       epi_bar_sync();
       const int ncols = min(BN, it.n2 - it.cb * BN);  // valid columns of this block
@@ -249,25 +251,32 @@ match_fused2_kernel(const __grid_constant__ CUtensorMap tmap, const MatchParams 
       const int c_begin = h * 3;
       const int c_end = min(min(c_begin + 3, BN / 32), (ncols + 31) >> 5);
       const size_t pair_row0 = (size_t)it.pair * p.kmax;
-      for (int s = 0; s < it.npt; ++s, ++tile) {
+      // hint: lower bound of a row's final second-best (L2 load, may be stale).  The load for the NEXT row
+      // tile is issued before this tile's chunks are processed, so its latency is off the critical path.
+      auto row_of = [&](int s) {
         int rtp = it.start + s;
         if (rtp >= it.npt) rtp -= it.npt;
-        const int rt = 2 * rtp + (int)rank;
-        const int row = rt * BM + q * 32 + lane;
+        return (2 * rtp + (int)rank) * BM + q * 32 + lane;
+      };
+      unsigned hint_next = 0u;
+      if (it.npt > 0 && row_of(0) < it.n1) hint_next = __ldcg(p.rowthr + pair_row0 + row_of(0));
+      for (int s = 0; s < it.npt; ++s, ++tile) {
+        const int row = row_of(s);
         const bool row_ok = row < it.n1;
-        // hint: lower bound of this row's final second-best (L2 load, may be stale)
         float thr = 0.f;
-        if (row_ok) thr = fmaxf(p.prune, __uint_as_float(__ldcg(p.rowthr + pair_row0 + row)));
+        if (row_ok) thr = fmaxf(p.prune, __uint_as_float(hint_next));
+        if (s + 1 < it.npt && row_of(s + 1) < it.n1) hint_next = __ldcg(p.rowthr + pair_row0 + row_of(s + 1));
         const unsigned long long row_tag = 0xFFFFFFFFu - (unsigned)row;
         RowTop2 rs{0.f, 0.f, -1};
         const uint32_t as = tile & 1, aph = (tile >> 1) & 1;
+        if (s > 0) refresh_colmin8(colsec, colmin8, 4 * c_begin, 4 * c_end, lane);
         mbar_wait(tfull_bar(as), aph);
         tc_fence_after();
         const uint32_t t_addr = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + as * BN;
 #pragma unroll 1
         for (int c = c_begin; c < c_end; ++c)
           fused_epilogue_chunk(t_addr + c * 32, c, ncols, row_ok, row_tag, thr, it.cb * BN + c * 32, lane, p.dense_min,
-                               colkey, colsec, rs);
+                               colkey, colsec, colmin8, rs);
         tc_fence_before();
         __syncwarp();
         if (lane == 0) mbar_arrive_cluster(lead_tempty[as]);
