@@ -426,3 +426,46 @@ def test_guided_matching_against_oracle(matcher, kind, rule):
     assert 0.9 < filt.mean() < 1.0 and len(ref_f) > 100
     with pytest.raises(ValueError):  # DEGENERATE / UNDEFINED carry no model (sift.cc:1122-1124)
         matcher.match_guided(resident, kps, np.array([[0, 1]], np.int32), [PairGeometry(1)], ratio, dist, True)
+
+
+def test_column_merge_paths_agree(matcher, monkeypatch):
+    """The fused epilogue merges column hits either lane by lane (two shared-memory atomics per hit) or,
+    when many columns of a chunk are hit at once, through warp-wide maxima with one merging lane per
+    column.  Forcing each path for every chunk (VC_MATCH_DENSE_MIN = 33 / 1) and the default must give
+    the same top-2 values, indices and match lists -- with the pruning bound off and exact duplicates
+    in both images, so that ties and second-best updates go through both paths -- and equal the oracle."""
+    import torch
+    from oracle import matching as om
+    rng = np.random.default_rng(17)
+    kmax, counts = 900, [900, 777, 640]
+    monkeypatch.setenv("VC_MATCH_NO_PRUNE", "1")
+    for d in (128, 768):                                  # single-CTA and two-SM kernels
+        desc = np.abs(_make_set(rng, 3, kmax, d, counts))  # non-negative: every score is a candidate
+        desc /= np.maximum(np.linalg.norm(desc, axis=2, keepdims=True), 1e-12)
+        desc[0, 300:310] = desc[0, 20:30]                 # duplicate rows: column ties, lowest row must win
+        desc[1, 400:405] = desc[1, 7:12]                  # duplicate columns: row ties, lowest column must win
+        desc = _bf16_round(desc)
+        t = torch.from_numpy(desc).cuda().to(torch.bfloat16)
+        c = torch.tensor(counts, dtype=torch.int32, device="cuda")
+        pairs = [(0, 1), (1, 2), (2, 0)]
+        p = torch.tensor(pairs, dtype=torch.int32, device="cuda")
+        outs = []
+        for dense_min in ("33", "1", None):
+            if dense_min is None:
+                monkeypatch.delenv("VC_MATCH_DENSE_MIN", raising=False)
+            else:
+                monkeypatch.setenv("VC_MATCH_DENSE_MIN", dense_min)
+            m, n = matcher.match_pairs(t, c, p, 1.05, 3.2, True, 1.0)   # mutual nearest neighbours: indices matter on ties
+            top = matcher.top2(t, c, p, 1.05, 3.2, True, 1.0)
+            torch.cuda.synchronize()
+            outs.append(([m[k, : int(n[k])].cpu().numpy().tolist() for k in range(len(pairs))],
+                         [x.cpu().numpy() for x in top]))
+        for lists, top in outs[1:]:
+            assert lists == outs[0][0]
+            for a, b in zip(top, outs[0][1]):
+                assert np.array_equal(a, b)
+        for k, (i1, i2) in enumerate(pairs):
+            ref = om.match_c(desc[i1, : counts[i1]], desc[i2, : counts[i2]], 1.05, 3.2, True)
+            got = np.array(outs[0][0][k], np.uint32).reshape(-1, 2)
+            differ = set(map(tuple, got.tolist())) ^ set(map(tuple, ref.tolist()))
+            assert len(differ) <= 0.01 * len(ref) and len(ref) > 300   # fp32 near-ties only (accumulation order)

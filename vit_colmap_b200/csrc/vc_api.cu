@@ -235,12 +235,12 @@ static int match_impl(vc_handle* h, const void* desc, const int32_t* counts, int
       return e ? atoi(e) : 2;
     }();
     p.stagger = stagger;
-    // column merge: warp-reduction path from this many hit columns per chunk (33 = never); tools/time_match_dims.py
-    static const int dense_min = [] {
+    // column merge: warp-reduction path from this many hit columns per 32x32 chunk (1 = always, 33 = never;
+    // measured best at 6, tools/time_match_dims.py).  Read per call so that tests can force either path.
+    {
       const char* e = getenv("VC_MATCH_DENSE_MIN");
-      return e ? atoi(e) : 6;
-    }();
-    p.dense_min = dense_min;
+      p.dense_min = e ? std::max(1, atoi(e)) : 6;
+    }
     w += part_bytes(n_pairs, kmax);
     p.col_key = reinterpret_cast<unsigned long long*>(w);
     p.col_sec = reinterpret_cast<unsigned int*>(w + align_up((size_t)n_pairs * 2 * kmax * 8, 256));
