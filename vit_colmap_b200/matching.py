@@ -313,10 +313,10 @@ class Matcher:
                                                   _ptr(pairs_dev), _ptr(geo_dev), n_pairs, ctypes.byref(opt),
                                                   _ptr(matches), _ptr(n_matches), _ptr(ws), need, self._stream()))
         n_h = n_matches.cpu().numpy()
-        out = []
-        for k in range(n_pairs):  # only the filled prefix of each pair's slot comes back
-            out.append(matches[k, : int(n_h[k])].cpu().numpy().view(np.uint32).reshape(-1, 2).copy())
-        return out
+        top = int(n_h.max()) if n_pairs else 0
+        # one strided device-to-host copy of the filled prefixes [n_pairs, max count, 2] instead of one per pair
+        m_h = matches[:, :top].cpu().numpy().view(np.uint32) if top else np.zeros((n_pairs, 0, 2), np.uint32)
+        return [m_h[k, : int(n_h[k])].copy() for k in range(n_pairs)]
 
 
 # TwoViewGeometry::ConfigurationType (COLMAP/scene/two_view_geometry.h:40-61)
