@@ -468,4 +468,4 @@ def test_column_merge_paths_agree(matcher, monkeypatch):
             ref = om.match_c(desc[i1, : counts[i1]], desc[i2, : counts[i2]], 1.05, 3.2, True)
             got = np.array(outs[0][0][k], np.uint32).reshape(-1, 2)
             differ = set(map(tuple, got.tolist())) ^ set(map(tuple, ref.tolist()))
-            assert len(differ) <= 0.01 * len(ref) and len(ref) > 300   # fp32 near-ties only (accumulation order)
+            assert len(differ) <= 0.01 * len(ref) and len(ref) > 150   # fp32 near-ties only (accumulation order)
