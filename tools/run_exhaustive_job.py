@@ -1,0 +1,95 @@
+"""Whole exhaustive-matching job of BASELINE config C4 / C5 through the product's own sharded driver:
+synthetic descriptor sets [n_images, kpts, d] bf16 generated on the device (each rank its shard), ONE NCCL
+all-gather, pair blocks of 50 x 50 images (ExhaustivePairGenerator) dealt to the ranks by
+pairing.shard_blocks, every block matched on the resident set (vc_match_pairs_resident), match lists
+gathered on rank 0.  Reports job time (max over ranks), pairs/s, TFLOP/s and the fraction of the measured
+sustained bf16 peak.
+
+    python tools/run_exhaustive_job.py [n_images=1024] [kpts=8192] [d=768]
+    python -m torch.distributed.run --nproc-per-node 8 --master-addr 127.0.0.1 tools/run_exhaustive_job.py 1024
+"""
+import json
+import os
+import sys
+import time
+from pathlib import Path
+
+import numpy as np
+import torch
+import torch.distributed as dist
+
+ROOT = Path(__file__).resolve().parent.parent
+sys.path.insert(0, str(ROOT))
+from bench import _peaks, make_descriptors_device  # noqa: E402
+from vit_colmap_b200 import distributed as vd  # noqa: E402
+from vit_colmap_b200.matching import FeatureMatchingOptions, Matcher, ResidentDescriptors  # noqa: E402
+
+
+def main():
+    n_images = int(sys.argv[1]) if len(sys.argv) > 1 else 1024
+    kpts = int(sys.argv[2]) if len(sys.argv) > 2 else 8192
+    d = int(sys.argv[3]) if len(sys.argv) > 3 else 768
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    lo, hi = vd.shard_range(n_images, rank, world)
+    # the C4 / C5 recipe (bench.make_descriptors_device) in chunks of 32 images, seeded per chunk so that a
+    # rank generates exactly its own images
+    shard = torch.empty((hi - lo, kpts, d), dtype=torch.bfloat16, device=dev)
+    for s in range(lo, hi, 32):
+        e = min(hi, s + 32)
+        shard[s - lo:e - lo] = make_descriptors_device(torch, dev, e - s, kpts, d, seed=1000 + s)
+    counts_local = torch.full((hi - lo,), kpts, dtype=torch.int32, device=dev)
+    torch.cuda.synchronize()
+    if world > 1:
+        dist.barrier()
+    t0 = time.perf_counter()
+    desc, counts = vd.all_gather_descriptors(shard, counts_local, n_images)
+    torch.cuda.synchronize()
+    t_gather = time.perf_counter() - t0
+    del shard
+    matcher = Matcher(local)
+    resident = ResidentDescriptors(desc, counts.cpu().numpy(), n_images, 1.0, 0, 0.0, 0)
+    options = FeatureMatchingOptions()
+    fn = vd.gpu_match_fn(matcher, resident, options)
+    t1 = time.perf_counter()
+    # rank-local part of match_exhaustive_sharded, timed before the host-side gather of the lists
+    ids = list(range(1, n_images + 1))
+    from vit_colmap_b200.pairing import ExhaustivePairGenerator, shard_blocks
+    blocks = list(ExhaustivePairGenerator(ids, 50).blocks())
+    mine = shard_blocks([len(b) for b in blocks], world)[rank]
+    n_pairs = n_rows = 0
+    for b in mine:
+        idx = np.array([(a - 1, c - 1) for a, c in blocks[b]], dtype=np.int32)
+        for m in fn(idx):
+            n_rows += len(m)
+        n_pairs += len(idx)
+    torch.cuda.synchronize()
+    t_match = time.perf_counter() - t1
+    stats = torch.tensor([t_match, t_gather, float(n_pairs), float(n_rows)], dtype=torch.float64, device=dev)
+    mx = stats.clone()
+    if world > 1:
+        dist.all_reduce(mx, op=dist.ReduceOp.MAX)
+        dist.all_reduce(stats, op=dist.ReduceOp.SUM)
+    if rank == 0:
+        total_pairs = int(stats[2].item())
+        assert total_pairs == n_images * (n_images - 1) // 2, total_pairs
+        secs = float(mx[0].item())
+        tf = 2.0 * kpts * kpts * d * total_pairs / secs / 1e12
+        peak, _, src = _peaks()
+        print(json.dumps({"job": f"exhaustive matching of {n_images} images x {kpts} kpts x d={d}", "n_gpus": world,
+                          "pairs": total_pairs, "match_rows": int(stats[3].item()), "seconds": secs,
+                          "pairs_per_s": total_pairs / secs, "tflops_per_gpu": tf / world,
+                          "frac_of_sustained_bf16_per_gpu": tf / world / peak, "peak_source": src,
+                          "all_gather_seconds": float(mx[1].item()),
+                          "slowest_rank_pairs": int(mx[2].item()), "includes": "pair lists up, packed match lists down to host"}))
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()
