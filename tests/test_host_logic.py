@@ -131,3 +131,33 @@ def test_two_view_geometry_rows_follow_colmap_layout(tmp_path):
     empty = con.execute("SELECT rows, F, H, qvec FROM two_view_geometries WHERE pair_id = ?",
                         (image_pair_to_pair_id(2, 7),)).fetchone()
     assert empty[0] == 0 and all(not b for b in empty[1:])
+
+
+def test_decode_ahead_keeps_order_and_passes_failures_through():
+    """features/_pipelined.decode_ahead: results come back in input order (the single database writer
+    hands out image ids in sorted file order), a failing prepare() is returned in place of its result,
+    None (unreadable file) passes through, and no more than `lookahead` files are prepared ahead."""
+    import threading
+    import time
+    from vit_colmap_b200.features._pipelined import decode_ahead
+    started, lock = [], threading.Lock()
+
+    def prepare(i):
+        with lock:
+            started.append(i)
+        time.sleep(0.002 * ((i * 7) % 5))      # out-of-order completion
+        if i == 3:
+            raise ValueError("too small")
+        return None if i == 5 else i * i
+
+    ahead = []
+    out = []
+    for k, item, got in decode_ahead(range(30), prepare, workers=4, lookahead=6):
+        with lock:
+            ahead.append(max(started) - k)
+        out.append((k, item, got))
+    assert [k for k, _, _ in out] == list(range(30)) and [i for _, i, _ in out] == list(range(30))
+    assert isinstance(out[3][2], ValueError) and out[5][2] is None
+    assert [g for k, _, g in out if k not in (3, 5)] == [i * i for i in range(30) if i not in (3, 5)]
+    assert max(ahead) <= 6
+    assert list(decode_ahead([], prepare)) == []

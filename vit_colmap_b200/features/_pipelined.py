@@ -17,6 +17,34 @@ import numpy as np
 Batch = Tuple[List[np.ndarray], Tuple[int, int], Tuple[int, int], object]  # images, orig_wh, resized_wh, extra
 
 
+def decode_ahead(files, prepare, workers: int = 8, lookahead: int = 0):
+    """Ordered iterator of ``(index, path, prepare(path))`` with the ``prepare`` calls (cv2.imread, the
+    resize to a multiple of 14, a host-side detector: all release the GIL) running on a thread pool up
+    to ``lookahead`` files ahead of the consumer (default 2 x workers).  A 1600 x 1200 PNG takes 30-40 ms to
+    decode, an order of magnitude more than its share of the GPU batch, so a serial ``for f in files:
+    cv2.imread(f)`` loop -- the reference's, vit_extractor.py:729-739 -- would leave the device idle.  An
+    exception inside ``prepare`` is returned in place of the result; the order, and with it the image ids the
+    single database writer hands out, is the sorted file order."""
+    files = list(files)
+    lookahead = lookahead or 2 * workers
+
+    def run(path):
+        try:
+            return prepare(path)
+        except Exception as e:  # noqa: BLE001
+            return e
+
+    with ThreadPoolExecutor(max_workers=workers, thread_name_prefix="vc-decode") as pool:
+        jobs = []
+        nxt = 0
+        for k, path in enumerate(files):
+            while nxt < len(files) and nxt < k + lookahead:
+                jobs.append(pool.submit(run, files[nxt]))
+                nxt += 1
+            yield k, path, jobs[k].result()
+            jobs[k] = None
+
+
 class BatchPipeline:
     """Mixin.  The extractor provides ``self.device`` and
     ``_device_stage(batch_u8, orig_wh, resized_wh, extra) -> (keypoints, desc_u8, counts, keep)``

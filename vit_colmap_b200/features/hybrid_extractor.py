@@ -14,6 +14,7 @@ from typing import List, Optional, Tuple
 
 import numpy as np
 
+from ._pipelined import decode_ahead
 from .base_extractor import default_camera_params, list_images
 from .vit_extractor import PATCH, ViTExtractor as _GridViTExtractor
 
@@ -46,17 +47,30 @@ class HybridViTExtractor(_GridViTExtractor):
             return cv2.goodFeaturesToTrack
         return cv2.ORB_create(nfeatures=self.num_keypoints)
 
+    def _thread_detector(self):
+        """cv2 Feature2D objects are not documented as re-entrant; extract() detects on decode worker
+        threads (decode_ahead), so every thread gets its own detector (same parameters, same results)."""
+        import threading
+        if getattr(self, "_tls", None) is None:
+            self._tls = threading.local()
+        if threading.current_thread() is threading.main_thread():
+            return self.detector
+        if getattr(self._tls, "detector", None) is None:
+            self._tls.detector = self._create_detector()
+        return self._tls.detector
+
     def _detect_keypoints(self, image_bgr: np.ndarray) -> np.ndarray:
         """hybrid_extractor.py:131-180: [n, 2] float32 (x, y) pixels of the ORIGINAL image."""
         import cv2
         gray = cv2.cvtColor(image_bgr, cv2.COLOR_BGR2GRAY)
+        detector = self._thread_detector()
         if self.detector_type == "gftt":
-            corners = self.detector(gray, maxCorners=self.num_keypoints, qualityLevel=0.01, minDistance=7,
+            corners = detector(gray, maxCorners=self.num_keypoints, qualityLevel=0.01, minDistance=7,
                                     blockSize=7)
             if corners is None:
                 return np.zeros((0, 2), np.float32)
             return corners.reshape(-1, 2).astype(np.float32)
-        kpts = self.detector.detect(gray, None)
+        kpts = detector.detect(gray, None)
         keypoints = np.array([[kp.pt[0], kp.pt[1]] for kp in kpts], dtype=np.float32).reshape(-1, 2)
         if self.detector_type == "fast" and len(keypoints) > self.num_keypoints:
             responses = np.array([kp.response for kp in kpts])
@@ -160,19 +174,23 @@ class HybridViTExtractor(_GridViTExtractor):
         camera_id = db.db.write_camera(make_camera(camera_model, width, height, camera_params))
         print(f"Camera ID: {camera_id}\n")
 
+        def prepare(path):  # worker threads: decode, host-side detector, resize (None: unreadable file)
+            img = cv2.imread(str(path))
+            if img is None:
+                return None
+            kps = self._detect_keypoints(img)
+            return kps, self._resize(img)
+
         def items():
-            for idx, f in enumerate(files, start=1):
-                img = cv2.imread(str(f))
-                if img is None:
-                    print(f"[{idx}/{len(files)}] {f.name}: ⚠ Warning: Failed to read image, skipping")
+            for k, f, got in decode_ahead(files, prepare):
+                if got is None:
+                    print(f"[{k + 1}/{len(files)}] {f.name}: ⚠ Warning: Failed to read image, skipping")
                     continue
                 image_id = db.add_image(f.name, camera_id=camera_id)
-                try:
-                    kps = self._detect_keypoints(img)
-                    img, orig_wh, resized_wh = self._resize(img)
-                except Exception as e:  # noqa: BLE001
-                    print(f"  ✗ Error: {e}")
+                if isinstance(got, Exception):
+                    print(f"  ✗ Error: {got}")
                     continue
+                kps, (img, orig_wh, resized_wh) = got
                 yield image_id, img, orig_wh, resized_wh, kps
 
         def write(image_id, kps, desc):

@@ -17,7 +17,7 @@ from typing import List, Optional, Tuple
 
 import numpy as np
 
-from ._pipelined import BatchPipeline
+from ._pipelined import BatchPipeline, decode_ahead
 from .base_extractor import BaseExtractor
 
 PATCH = 14
@@ -184,18 +184,22 @@ class TrainableViTExtractor(BatchPipeline, BaseExtractor):
         camera_id = db.db.write_camera(make_camera(camera_model, width, height, camera_params))
         print(f"Camera ID: {camera_id}\n")
 
+        def prepare(path):  # worker threads: decode + resize (None: unreadable file)
+            img = cv2.imread(str(path))
+            return None if img is None else (img, self._resize(img))
+
         def items():
-            for idx, f in enumerate(files, start=1):
-                img = cv2.imread(str(f))
-                if img is None:
-                    print(f"[{idx}/{len(files)}] {f.name}: Warning: Failed to read image, skipping")
+            for k, f, got in decode_ahead(files, prepare):
+                if got is None:
+                    print(f"[{k + 1}/{len(files)}] {f.name}: Warning: Failed to read image, skipping")
                     continue
+                if isinstance(got, Exception) and not isinstance(got, ValueError):
+                    raise got
                 image_id = db.add_image(f.name, camera_id=camera_id)
-                try:
-                    img, orig_wh, resized_wh = self._resize(img)
-                except Exception as e:  # noqa: BLE001
-                    print(f"  Error during feature extraction: {e}")
+                if isinstance(got, Exception):
+                    print(f"  Error during feature extraction: {got}")
                     continue
+                _, (img, orig_wh, resized_wh) = got
                 yield (image_id, f.name), img, orig_wh, resized_wh, None
 
         def write(meta, kps, desc):

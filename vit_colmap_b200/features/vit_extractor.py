@@ -14,7 +14,7 @@ from typing import List, Optional, Tuple
 
 import numpy as np
 
-from ._pipelined import BatchPipeline
+from ._pipelined import BatchPipeline, decode_ahead
 from .base_extractor import BaseExtractor, default_camera_params, list_images
 
 PATCH = 14
@@ -158,18 +158,22 @@ class ViTExtractor(BatchPipeline, BaseExtractor):
         # image ids follow the sorted file order (single writer); features are computed in batches
         # through BatchPipeline.extract_stream: decoding / staging of the next batch and the database
         # writes of the previous one run under the current batch's kernels
+        def prepare(path):  # worker threads: decode + resize (None: unreadable file)
+            img = cv2.imread(str(path))
+            return None if img is None else (img, self._resize(img))
+
         def items():
-            for idx, f in enumerate(files, start=1):
-                img = cv2.imread(str(f))
-                if img is None:
-                    print(f"[{idx}/{len(files)}] {f.name}: ⚠ Warning: Failed to read image, skipping")
+            for k, f, got in decode_ahead(files, prepare):
+                if got is None:
+                    print(f"[{k + 1}/{len(files)}] {f.name}: ⚠ Warning: Failed to read image, skipping")
                     continue
-                image_id = db.add_image(f.name, camera_id=camera_id)
-                try:
-                    img, orig_wh, resized_wh = self._resize(img)
-                except Exception as e:  # noqa: BLE001
-                    print(f"  ✗ Error during feature extraction: {e}")
+                if isinstance(got, Exception) and not isinstance(got, ValueError):
+                    raise got
+                image_id = db.add_image(f.name, camera_id=camera_id)   # the image row exists even if extraction fails
+                if isinstance(got, Exception):                          # _resize refused the image (vit_extractor.py:757-762)
+                    print(f"  ✗ Error during feature extraction: {got}")
                     continue
+                _, (img, orig_wh, resized_wh) = got
                 yield image_id, img, orig_wh, resized_wh, None
 
         def write(image_id, kps, desc):
