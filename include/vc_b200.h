@@ -310,6 +310,13 @@ int vc_vit_forward(vc_handle* h, const vc_vit_weights* w, const uint8_t* images,
  * 1: bf16 GELU(erf) out, 2: f32 out += gamma * (.).  K % 64 == 0, N % 32 == 0. */
 int vc_vit_linear(vc_handle* h, const void* a, const void* w, const float* bias, const float* gamma,
                   int m, int n, int k, int epilogue, void* out, void* stream);
+/* vc_vit_linear with the residual epilogue (x += gamma * (A W^T + bias), fp32, [m, n]) followed IN THE SAME
+ * KERNEL by LayerNorm(x; ln_w, ln_b, eps 1e-6) -> ln_out bf16 [m, n]: the CTA that stores the last column
+ * tile of a 128-row block normalises that block out of L2.  n is the full row (<= 1024); ln_out must not
+ * alias a.  This is how vc_vit_forward runs every LayerNorm but the first and the final one. */
+int vc_vit_linear_ln(vc_handle* h, const void* a, const void* w, const float* bias, const float* gamma,
+                     const float* ln_w, const float* ln_b, int m, int n, int k, float* x, void* ln_out_bf16,
+                     void* stream);
 /* vc_vit_attention: qkv bf16 [n_images, tokens, 3*heads*64] -> out bf16 [n_images, tokens, heads*64] */
 int vc_vit_attention(vc_handle* h, const void* qkv, int n_images, int tokens, int heads, void* out,
                      void* stream);

@@ -153,3 +153,63 @@ def test_forward_dtu_grid_85x114():
     # north-star tolerance for one block (1e-3) on all but a 1e-5 fraction of the 7.4 M values; the
     # extreme tail is a bf16 rounding flip of an intermediate (1 ulp = 3.9e-3 of that value)
     assert torch.quantile(err[::7], 0.9999).item() < 1e-3 and err.max().item() < 2.5e-3, err.max().item()
+
+
+@pytest.mark.parametrize("shape", [(1370, 768, 768), (43840 // 8, 768, 3072), (300, 384, 384), (129, 1024, 1024),
+                                   (5000, 384, 1536)])
+def test_linear_with_fused_layernorm(lib_handle, shape):
+    """vc_vit_linear_ln: the residual GEMM whose epilogue also normalises every 128-row block it has
+    completed (per-block counter, the completing CTA reads the rows back from L2).  The fp32 stream must
+    equal the plain residual epilogue bit for bit, and the bf16 LayerNorm rows must equal the stand-alone
+    LayerNorm kernel applied to that stream bit for bit (same arithmetic), for row counts that leave a
+    partial last block, several column tiles per row (C = 768 / 1024: 3 / 4 tiles whose completion order is
+    not fixed) and a single one (C = 384 / 256-wide tile); twice in a row (the counters must be left zero)."""
+    import torch
+    from vit_colmap_b200 import _lib
+    lib, h = lib_handle
+    m, n, k = shape
+    g = torch.Generator(device="cuda").manual_seed(m + n + k)
+    a = torch.randn((m, k), generator=g, device="cuda").to(torch.bfloat16)
+    w = (torch.randn((n, k), generator=g, device="cuda") * 0.05).to(torch.bfloat16)
+    bias = torch.randn((n,), generator=g, device="cuda")
+    gamma = torch.randn((n,), generator=g, device="cuda")
+    ln_w = torch.randn((n,), generator=g, device="cuda")
+    ln_b = torch.randn((n,), generator=g, device="cuda")
+    x0 = torch.randn((m, n), generator=g, device="cuda") * 2 + 0.3
+    for _ in range(2):
+        x_ref = x0.clone()
+        _lib.check(lib.vc_vit_linear(h, a.data_ptr(), w.data_ptr(), bias.data_ptr(), gamma.data_ptr(), m, n, k, 2,
+                                     x_ref.data_ptr(), _stream()))
+        ln_ref = torch.zeros((m, n), dtype=torch.bfloat16, device="cuda")
+        _lib.check(lib.vc_vit_layernorm(h, x_ref.data_ptr(), ln_w.data_ptr(), ln_b.data_ptr(), m, n, ln_ref.data_ptr(),
+                                        _stream()))
+        x = x0.clone()
+        ln = torch.full((m, n), float("nan"), dtype=torch.bfloat16, device="cuda")
+        _lib.check(lib.vc_vit_linear_ln(h, a.data_ptr(), w.data_ptr(), bias.data_ptr(), gamma.data_ptr(),
+                                        ln_w.data_ptr(), ln_b.data_ptr(), m, n, k, x.data_ptr(), ln.data_ptr(), _stream()))
+        torch.cuda.synchronize()
+        assert torch.equal(x, x_ref)
+        assert torch.equal(ln.view(torch.int16), ln_ref.view(torch.int16))
+    ref = torch.nn.functional.layer_norm(x0 + gamma * (a.float() @ w.float().t() + bias), (n,), ln_w, ln_b, eps=1e-6)
+    assert (ln.float() - ref).abs().max().item() <= 2 ** -7 * ref.abs().max().item()
+    with pytest.raises(Exception):   # the normalised rows may not overwrite the operand other CTAs still read
+        _lib.check(lib.vc_vit_linear_ln(h, a.data_ptr(), w.data_ptr(), bias.data_ptr(), gamma.data_ptr(),
+                                        ln_w.data_ptr(), ln_b.data_ptr(), m, n, k, x.data_ptr(), a.data_ptr(), _stream()))
+
+
+def test_forward_fused_layernorm_equals_separate_launches(monkeypatch):
+    """vc_vit_forward with the LayerNorms in the GEMM epilogues (default) and with one launch per LayerNorm
+    (VC_VIT_FUSED_LN=0): identical tokens, bit for bit, at a grid with a partial last row block."""
+    import torch
+    from oracle import vit_oracle as vo
+    from vit_colmap_b200.vit import VitBackbone
+    sd = vo.synthetic_state_dict("dinov2_vitb14", seed=5, depth=3)
+    rng = np.random.default_rng(5)
+    img = torch.from_numpy(rng.integers(0, 256, (3, 518, 518, 3), dtype=np.uint8)).cuda()
+    net = VitBackbone(sd, "dinov2_vitb14", 0)
+    fused = net.forward_patch_tokens(img).clone()
+    monkeypatch.setenv("VC_VIT_FUSED_LN", "0")
+    separate = net.forward_patch_tokens(img).clone()
+    torch.cuda.synchronize()
+    net.close()
+    assert torch.equal(fused, separate) and torch.isfinite(fused).all()

@@ -180,6 +180,7 @@ int vc_destroy(vc_handle* h) {
   cudaDeviceSynchronize();
   if (h->stage) cudaFree(h->stage);
   if (h->pin) cudaFreeHost(h->pin);
+  if (h->ln_counters) cudaFree(h->ln_counters);
   for (auto st : h->host_streams)
     if (st) cudaStreamDestroy(st);
   for (auto ev : h->host_events)
@@ -465,6 +466,7 @@ static int match_host_impl(vc_handle* h, const void* desc, int dtype, bool resid
   if (h->pin_bytes < pin_total) {
     VC_CUDA(cudaDeviceSynchronize());
     if (h->pin) cudaFreeHost(h->pin);
+  if (h->ln_counters) cudaFree(h->ln_counters);
     h->pin = nullptr;
     h->pin_bytes = 0;
     VC_CUDA(cudaHostAlloc(&h->pin, pin_total, cudaHostAllocDefault));

@@ -3,6 +3,8 @@
 #include "vc_internal.cuh"
 #include "vit_kernels.cuh"
 
+#include <cstdlib>
+
 using vc::fail;
 
 namespace {
@@ -54,21 +56,26 @@ int run_linear(vc_handle* h, const void* a, const void* w, int m, int n, int k, 
 
 struct VitWs {
   float* x;                // [B*T, C] residual stream
-  __nv_bfloat16* y;        // [B*T, C] LayerNorm output / attention output
+  __nv_bfloat16* y;        // [B*T, C] LayerNorm-1 output / attention output
+  __nv_bfloat16* y2;       // [B*T, C] LayerNorm-2 output (written by the proj GEMM while it still reads y)
   __nv_bfloat16* wide;     // [B*T, 4C] qkv (3C) / MLP hidden (4C) / patch rows (kpad)
+  int* counters;           // [ceil(B*T / 128)] row-block counters of the fused LayerNorm epilogue
 };
 
 size_t ws_bytes(int B, int T, int C, VitWs* out, void* base) {
   const size_t rows = (size_t)B * T;
   const size_t bx = vc::align_up(rows * C * 4, 1024), by = vc::align_up(rows * C * 2, 1024);
   const size_t bw = vc::align_up(rows * (size_t)(4 * C > 640 ? 4 * C : 640) * 2, 1024);
+  const size_t bc = vc::align_up(((rows + 127) / 128) * sizeof(int), 1024);
   if (out) {
     uint8_t* p = static_cast<uint8_t*>(base);
     out->x = reinterpret_cast<float*>(p);
     out->y = reinterpret_cast<__nv_bfloat16*>(p + bx);
-    out->wide = reinterpret_cast<__nv_bfloat16*>(p + bx + by);
+    out->y2 = reinterpret_cast<__nv_bfloat16*>(p + bx + by);
+    out->wide = reinterpret_cast<__nv_bfloat16*>(p + bx + 2 * by);
+    out->counters = reinterpret_cast<int*>(p + bx + 2 * by + bw);
   }
-  return bx + by + bw;
+  return bx + 2 * by + bw + bc;
 }
 
 }  // namespace
@@ -96,6 +103,39 @@ int vc_vit_linear(vc_handle* h, const void* a, const void* w, const float* bias,
   p.out = out;
   p.ldo = n;
   return run_linear(h, a, w, m, n, k, p, reinterpret_cast<cudaStream_t>(stream));
+}
+
+int vc_vit_linear_ln(vc_handle* h, const void* a, const void* w, const float* bias, const float* gamma,
+                     const float* ln_w, const float* ln_b, int m, int n, int k, float* x, void* ln_out_bf16,
+                     void* stream) {
+  if (!h) return fail(VC_ERR_INVALID, "null handle");
+  if (!a || !w || !bias || !gamma || !ln_w || !ln_b || !x || !ln_out_bf16)
+    return fail(VC_ERR_INVALID, "null pointer argument");
+  if (m <= 0 || n <= 0 || k <= 0 || k % 64 != 0 || n % 32 != 0 || n > 1024)
+    return fail(VC_ERR_INVALID, "bad GEMM shape m=%d n=%d k=%d (k %% 64, n %% 32, n <= 1024)", m, n, k);
+  if (ln_out_bf16 == a) return fail(VC_ERR_INVALID, "the LayerNorm output must not alias the A operand");
+  VC_CUDA(cudaSetDevice(h->device));
+  cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
+  const size_t blocks = ((size_t)m + 127) / 128;
+  if (h->ln_counters_len < blocks) {
+    if (h->ln_counters) cudaFree(h->ln_counters);
+    h->ln_counters = nullptr;
+    h->ln_counters_len = 0;
+    VC_CUDA(cudaMalloc(&h->ln_counters, blocks * sizeof(int)));
+    h->ln_counters_len = blocks;
+  }
+  VC_CUDA(cudaMemsetAsync(h->ln_counters, 0, blocks * sizeof(int), s));
+  vc::GemmParams p{};
+  p.epilogue = vc::kEpiResidualLnF32;
+  p.bias = bias;
+  p.gamma = gamma;
+  p.out = x;
+  p.ldo = n;
+  p.ln_w = ln_w;
+  p.ln_b = ln_b;
+  p.ln_out = static_cast<__nv_bfloat16*>(ln_out_bf16);
+  p.tile_counters = h->ln_counters;
+  return run_linear(h, a, w, m, n, k, p, s);
 }
 
 int vc_vit_attention(vc_handle* h, const void* qkv, int n_images, int tokens, int heads, void* out,
@@ -169,9 +209,18 @@ int vc_vit_forward(vc_handle* h, const vc_vit_weights* w, const uint8_t* images,
   CUtensorMap map_qkv;
   int rc = make_map_qkv(h, &map_qkv, ws.wide, n_images, T, 3 * C);
   if (rc != VC_OK) return rc;
+  // LayerNorm placement: only the first one is its own launch.  LN2 of a block runs in the epilogue of its
+  // proj GEMM (into y2: the GEMM still reads its A operand from y), LN1 of block l + 1 in the epilogue of
+  // block l's fc2 GEMM (into y); the final norm (fp32, cls row dropped) stays a kernel.  VC_VIT_FUSED_LN=0
+  // falls back to one launch per LayerNorm (comparison runs).
+  const char* fused_env = getenv("VC_VIT_FUSED_LN");
+  const bool fused_ln = !(fused_env && fused_env[0] == '0');
+  VC_CUDA(cudaMemsetAsync(ws.counters, 0, ((size_t)rows + 127) / 128 * sizeof(int), s));
+  VC_CUDA(vc::launch_layernorm_bf16(ws.x, w->blocks[0].ln1_w, w->blocks[0].ln1_b, ws.y, rows, C, s));
+  vc::add_launches(1);
   for (int l = 0; l < w->depth; ++l) {
     const vc_vit_block& b = w->blocks[l];
-    VC_CUDA(vc::launch_layernorm_bf16(ws.x, b.ln1_w, b.ln1_b, ws.y, rows, C, s));
+    const bool last = l + 1 == w->depth;
     vc::GemmParams p{};
     p.epilogue = vc::kEpiBiasBf16;
     p.bias = b.qkv_b;
@@ -186,31 +235,48 @@ int vc_vit_forward(vc_handle* h, const vc_vit_weights* w, const uint8_t* images,
     ap.scale = 0.125f;
     ap.out = ws.y;
     VC_CUDA(vc::launch_attention(map_qkv, ap, s));
+    vc::add_launches(1);
     p = vc::GemmParams{};
-    p.epilogue = vc::kEpiResidualF32;
+    p.epilogue = fused_ln ? vc::kEpiResidualLnF32 : vc::kEpiResidualF32;
     p.bias = b.proj_b;
     p.gamma = b.ls1;
     p.out = ws.x;
     p.ldo = C;
+    p.ln_w = b.ln2_w;
+    p.ln_b = b.ln2_b;
+    p.ln_out = ws.y2;
+    p.tile_counters = ws.counters;
     rc = run_linear(h, ws.y, b.proj_w, rows, C, C, p, s);
     if (rc != VC_OK) return rc;
-    VC_CUDA(vc::launch_layernorm_bf16(ws.x, b.ln2_w, b.ln2_b, ws.y, rows, C, s));
+    if (!fused_ln) {
+      VC_CUDA(vc::launch_layernorm_bf16(ws.x, b.ln2_w, b.ln2_b, ws.y2, rows, C, s));
+      vc::add_launches(1);
+    }
     p = vc::GemmParams{};
     p.epilogue = vc::kEpiBiasGeluBf16;
     p.bias = b.fc1_b;
     p.out = ws.wide;
     p.ldo = 4 * C;
-    rc = run_linear(h, ws.y, b.fc1_w, rows, 4 * C, C, p, s);
+    rc = run_linear(h, ws.y2, b.fc1_w, rows, 4 * C, C, p, s);
     if (rc != VC_OK) return rc;
     p = vc::GemmParams{};
-    p.epilogue = vc::kEpiResidualF32;
+    p.epilogue = (fused_ln && !last) ? vc::kEpiResidualLnF32 : vc::kEpiResidualF32;
     p.bias = b.fc2_b;
     p.gamma = b.ls2;
     p.out = ws.x;
     p.ldo = C;
+    if (!last) {
+      p.ln_w = w->blocks[l + 1].ln1_w;
+      p.ln_b = w->blocks[l + 1].ln1_b;
+      p.ln_out = ws.y;
+      p.tile_counters = ws.counters;
+    }
     rc = run_linear(h, ws.wide, b.fc2_w, rows, C, 4 * C, p, s);
     if (rc != VC_OK) return rc;
-    vc::add_launches(3);
+    if (!fused_ln && !last) {
+      VC_CUDA(vc::launch_layernorm_bf16(ws.x, w->blocks[l + 1].ln1_w, w->blocks[l + 1].ln1_b, ws.y, rows, C, s));
+      vc::add_launches(1);
+    }
   }
   VC_CUDA(vc::launch_layernorm_final(ws.x, w->norm_w, w->norm_b, tokens, n_images, T, C, s));
   vc::add_launches(1);

@@ -47,4 +47,7 @@ struct vc_handle {
   cudaEvent_t host_events[16] = {};                           // [0..7] chunk uploaded, [8..15] group matched
   void* pin = nullptr;
   size_t pin_bytes = 0;
+  // row-block counters of vc_vit_linear_ln (the forward keeps its own in the caller's workspace)
+  int* ln_counters = nullptr;
+  size_t ln_counters_len = 0;
 };

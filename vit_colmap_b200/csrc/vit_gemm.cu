@@ -10,6 +10,12 @@
 //     transposed through a swizzled shared-memory buffer so that every global access of a warp
 //     covers 4 whole 128-byte lines (8 lanes x 16 B per row) instead of 32 different lines with
 //     16 B each -- the L1/LSU line rate, not HBM, bounded the K = 768 GEMMs before
+//   - kEpiResidualLnF32: the LayerNorm that follows a residual update runs in this kernel.  Every tile bumps
+//     the counter of its 128-row block after its stores are visible device-wide; the CTA that brings it to
+//     the number of column tiles owns the block: its 8 epilogue warps read the 128 complete rows back
+//     from L2 (just written: no HBM read), compute mean / variance exactly as the stand-alone kernel does
+//     (row in registers, two passes) and store the bf16 rows the next GEMM loads.  The MMA warp keeps
+//     filling the other TMEM buffer meanwhile.  Saves one launch and one pass over the fp32 stream per LN.
 // Activations are bf16, accumulation and the residual stream are fp32.
 #include "vit_kernels.cuh"
 
@@ -29,6 +35,54 @@ constexpr int kThreads = 384;
 constexpr int kTmemCols = 512;
 constexpr int kStageOutBytes = 32 * 128;  // per epilogue warp: 32 rows x 128 B transposition buffer
 constexpr int kSmemBytes = kStages * kStageBytes + 1024 + 256 + 8 * kStageOutBytes;
+constexpr bool is_residual(int epi) { return epi == kEpiResidualF32 || epi == kEpiResidualLnF32; }
+
+__device__ __forceinline__ float warp_sum(float v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  return v;
+}
+
+// LayerNorm (eps 1e-6, biased variance around the mean: torch.nn.LayerNorm) of one fp32 row by one warp,
+// the row read through L2 (ld.global.cg: other SMs wrote most of it), bf16 out.  Same arithmetic as
+// layernorm_kernel in vit_pointwise.cu.
+__device__ __forceinline__ void ln_row_bf16(const float* __restrict__ xrow, const float* __restrict__ w,
+                                            const float* __restrict__ b, __nv_bfloat16* __restrict__ orow, int C,
+                                            int lane) {
+  constexpr int kVec = 8;  // float4 per lane, C <= 1024
+  const int nvec = C >> 2;
+  float4 v[kVec];
+  float s = 0.f;
+#pragma unroll
+  for (int k = 0; k < kVec; ++k) {
+    const int i = lane + 32 * k;
+    v[k] = i < nvec ? __ldcg(reinterpret_cast<const float4*>(xrow) + i) : make_float4(0, 0, 0, 0);
+    s += v[k].x + v[k].y + v[k].z + v[k].w;
+  }
+  const float mean = warp_sum(s) / (float)C;
+  float ss = 0.f;
+#pragma unroll
+  for (int k = 0; k < kVec; ++k) {
+    const int i = lane + 32 * k;
+    if (i < nvec) {
+      const float a = v[k].x - mean, c = v[k].y - mean, d = v[k].z - mean, e = v[k].w - mean;
+      ss += a * a + c * c + d * d + e * e;
+    }
+  }
+  const float rstd = rsqrtf(warp_sum(ss) / (float)C + 1e-6f);
+#pragma unroll
+  for (int k = 0; k < kVec; ++k) {
+    const int i = lane + 32 * k;
+    if (i < nvec) {
+      const float4 g = __ldg(reinterpret_cast<const float4*>(w) + i);
+      const float4 be = __ldg(reinterpret_cast<const float4*>(b) + i);
+      uint2 pk;
+      pk.x = pack_bf16((v[k].x - mean) * rstd * g.x + be.x, (v[k].y - mean) * rstd * g.y + be.y);
+      pk.y = pack_bf16((v[k].z - mean) * rstd * g.z + be.z, (v[k].w - mean) * rstd * g.w + be.w);
+      reinterpret_cast<uint2*>(orow)[i] = pk;
+    }
+  }
+}
 
 template <int EPI>
 __global__ void __launch_bounds__(kThreads, 1)
@@ -47,6 +101,7 @@ vit_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant
   auto tfull_bar = [&](int s) { return bar0 + 8u * (2 * kStages + s); };
   auto tempty_bar = [&](int s) { return bar0 + 8u * (2 * kStages + 2 + s); };
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * kStages + 4);
+  int* ln_owner = reinterpret_cast<int*>(tmem_slot + 1);  // kEpiResidualLnF32: does this CTA own the row block?
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int nkb = p.K / BK;
@@ -210,7 +265,7 @@ vit_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant
           // residual rows are requested first, so their HBM latency overlaps the TMEM read and the
           // transposition (loads and stores are kept in separate loops: no load waits on a store)
           float4 x[8];
-          if (EPI == kEpiResidualF32) {
+          if (is_residual(EPI)) {
 #pragma unroll
             for (int i = 0; i < 8; ++i) {
               const int m = row0 + tr + 4 * i;
@@ -232,13 +287,13 @@ vit_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant
           __syncwarp();
           const float4 b = __ldg(reinterpret_cast<const float4*>(p.bias + col));
           float4 ga = make_float4(1.f, 1.f, 1.f, 1.f);
-          if (EPI == kEpiResidualF32) ga = __ldg(reinterpret_cast<const float4*>(p.gamma + col));
+          if (is_residual(EPI)) ga = __ldg(reinterpret_cast<const float4*>(p.gamma + col));
 #pragma unroll
           for (int i = 0; i < 8; ++i) {
             const int r = tr + 4 * i, m = row0 + r;
             if (m < p.M) {
               const float4 a = *reinterpret_cast<const float4*>(stg + r * 128 + ((tc ^ (r & 7)) << 4));
-              if (EPI == kEpiResidualF32) {
+              if (is_residual(EPI)) {
                 float4 y = x[i];
                 y.x = fmaf(ga.x, a.x + b.x, y.x);
                 y.y = fmaf(ga.y, a.y + b.y, y.y);
@@ -260,6 +315,26 @@ vit_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant
       if (!released) {  // this warp's columns lie entirely beyond N
         tc_fence_before();
         mbar_arrive(tempty_bar(as));
+      }
+      if (EPI == kEpiResidualLnF32) {
+        // tile stored: publish it, and normalise the 128-row block if this tile completed it
+        __threadfence();                                          // this thread's stores, device-wide
+        asm volatile("bar.sync 1, 256;" ::: "memory");            // all 8 epilogue warps have stored
+        if (threadIdx.x == 128) {
+          const int done = atomicAdd(p.tile_counters + tm, 1) + 1;
+          *ln_owner = done == tiles_n;
+          if (done == tiles_n) p.tile_counters[tm] = 0;           // left zero for the next launch
+        }
+        asm volatile("bar.sync 1, 256;" ::: "memory");
+        if (*ln_owner) {                                          // CTA-uniform
+          __threadfence();                                        // order the reads after the counter
+          const int r_end = min(BM, p.M - tm * BM);
+          for (int r = warp - 4; r < r_end; r += 8) {
+            const size_t m = (size_t)tm * BM + r;
+            ln_row_bf16(static_cast<const float*>(p.out) + m * p.ldo, p.ln_w, p.ln_b, p.ln_out + m * p.N, p.N, lane);
+          }
+        }
+        asm volatile("bar.sync 1, 256;" ::: "memory");            // ln_owner is rewritten by the next tile
       }
     }
   }
@@ -293,6 +368,10 @@ cudaError_t launch_gemm(const CUtensorMap& map_a, const CUtensorMap& map_w, cons
     case kEpiBiasGeluBf16: return launch_one<kEpiBiasGeluBf16>(map_a, map_w, p, grid, stream);
     case kEpiResidualF32: return launch_one<kEpiResidualF32>(map_a, map_w, p, grid, stream);
     case kEpiPatchEmbed: return launch_one<kEpiPatchEmbed>(map_a, map_w, p, grid, stream);
+    case kEpiResidualLnF32:
+      if (!p.ln_w || !p.ln_b || !p.ln_out || !p.tile_counters || p.N != p.ldo || p.N > 1024 || p.N % 4 != 0)
+        return cudaErrorInvalidValue;
+      return launch_one<kEpiResidualLnF32>(map_a, map_w, p, grid, stream);
     default: return cudaErrorInvalidValue;
   }
 }

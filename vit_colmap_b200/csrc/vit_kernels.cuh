@@ -14,7 +14,11 @@ enum GemmEpilogue {
   kEpiBiasBf16 = 0,      // out_bf16 = acc + bias                       (QKV)
   kEpiBiasGeluBf16 = 1,  // out_bf16 = gelu_erf(acc + bias)             (fc1)
   kEpiResidualF32 = 2,   // out_f32 += gamma * (acc + bias)             (proj / fc2 + LayerScale + residual)
-  kEpiPatchEmbed = 3     // out_f32[b*T + 1 + t] = acc + bias + pos[1+t] (patch embedding)
+  kEpiPatchEmbed = 3,    // out_f32[b*T + 1 + t] = acc + bias + pos[1+t] (patch embedding)
+  // kEpiResidualF32 followed, in the same kernel, by the LayerNorm of the rows it has completed: the CTA
+  // that stores the LAST column tile of a 128-row block (per-block counter) normalises those rows straight
+  // out of L2 and writes the bf16 operand of the next GEMM.  N must be the full row (N == ldo <= 1024).
+  kEpiResidualLnF32 = 4
 };
 
 struct GemmParams {
@@ -26,6 +30,11 @@ struct GemmParams {
   int tokens_per_image;   // HW (kEpiPatchEmbed): row m -> image m / HW, token 1 + m % HW
   void* out;              // bf16 [M, ldo] or f32 [rows, ldo]
   int ldo;
+  // kEpiResidualLnF32 only
+  const float* ln_w;      // [N] LayerNorm weight / bias applied to the updated rows
+  const float* ln_b;
+  __nv_bfloat16* ln_out;  // bf16 [M, N]; must not alias the A operand
+  int* tile_counters;     // [ceil(M / 128)] zero before the launch; the kernel leaves them zero
 };
 int gemm_smem_bytes();
 cudaError_t launch_gemm(const CUtensorMap& map_a, const CUtensorMap& map_w, const GemmParams& p,
