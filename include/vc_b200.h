@@ -313,7 +313,8 @@ int vc_vit_linear(vc_handle* h, const void* a, const void* w, const float* bias,
 /* vc_vit_linear with the residual epilogue (x += gamma * (A W^T + bias), fp32, [m, n]) followed IN THE SAME
  * KERNEL by LayerNorm(x; ln_w, ln_b, eps 1e-6) -> ln_out bf16 [m, n]: the CTA that stores the last column
  * tile of a 128-row block normalises that block out of L2.  n is the full row (<= 1024); ln_out must not
- * alias a.  This is how vc_vit_forward runs every LayerNorm but the first and the final one. */
+ * alias a.  Bit-identical to vc_vit_linear(epilogue 2) + vc_vit_layernorm; vc_vit_forward uses it only with
+ * VC_VIT_FUSED_LN=1 (measured slower than the stand-alone LayerNorm launches). */
 int vc_vit_linear_ln(vc_handle* h, const void* a, const void* w, const float* bias, const float* gamma,
                      const float* ln_w, const float* ln_b, int m, int n, int k, float* x, void* ln_out_bf16,
                      void* stream);

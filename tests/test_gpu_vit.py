@@ -198,8 +198,9 @@ def test_linear_with_fused_layernorm(lib_handle, shape):
 
 
 def test_forward_fused_layernorm_equals_separate_launches(monkeypatch):
-    """vc_vit_forward with the LayerNorms in the GEMM epilogues (default) and with one launch per LayerNorm
-    (VC_VIT_FUSED_LN=0): identical tokens, bit for bit, at a grid with a partial last row block."""
+    """vc_vit_forward with one launch per LayerNorm (default) and with the LayerNorms in the GEMM epilogues
+    (VC_VIT_FUSED_LN=1, kept as an option: measured slower): identical tokens, bit for bit, at a grid with a
+    partial last row block."""
     import torch
     from oracle import vit_oracle as vo
     from vit_colmap_b200.vit import VitBackbone
@@ -207,9 +208,9 @@ def test_forward_fused_layernorm_equals_separate_launches(monkeypatch):
     rng = np.random.default_rng(5)
     img = torch.from_numpy(rng.integers(0, 256, (3, 518, 518, 3), dtype=np.uint8)).cuda()
     net = VitBackbone(sd, "dinov2_vitb14", 0)
-    fused = net.forward_patch_tokens(img).clone()
-    monkeypatch.setenv("VC_VIT_FUSED_LN", "0")
     separate = net.forward_patch_tokens(img).clone()
+    monkeypatch.setenv("VC_VIT_FUSED_LN", "1")
+    fused = net.forward_patch_tokens(img).clone()
     torch.cuda.synchronize()
     net.close()
     assert torch.equal(fused, separate) and torch.isfinite(fused).all()

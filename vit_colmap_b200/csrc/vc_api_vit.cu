@@ -209,12 +209,12 @@ int vc_vit_forward(vc_handle* h, const vc_vit_weights* w, const uint8_t* images,
   CUtensorMap map_qkv;
   int rc = make_map_qkv(h, &map_qkv, ws.wide, n_images, T, 3 * C);
   if (rc != VC_OK) return rc;
-  // LayerNorm placement: only the first one is its own launch.  LN2 of a block runs in the epilogue of its
-  // proj GEMM (into y2: the GEMM still reads its A operand from y), LN1 of block l + 1 in the epilogue of
-  // block l's fc2 GEMM (into y); the final norm (fp32, cls row dropped) stays a kernel.  VC_VIT_FUSED_LN=0
-  // falls back to one launch per LayerNorm (comparison runs).
+  // LayerNorm placement.  Default: one launch per LayerNorm.  VC_VIT_FUSED_LN=1 runs LN2 of a block in the
+  // epilogue of its proj GEMM (into y2: the GEMM still reads its A operand from y) and LN1 of block l + 1 in
+  // the epilogue of block l's fc2 GEMM (into y) -- bit-identical tokens, but measured SLOWER (13.95 vs
+  // 11.96 ms per 32 images, see vit_gemm.cu), so it is not the default.
   const char* fused_env = getenv("VC_VIT_FUSED_LN");
-  const bool fused_ln = !(fused_env && fused_env[0] == '0');
+  const bool fused_ln = fused_env && fused_env[0] == '1';
   VC_CUDA(cudaMemsetAsync(ws.counters, 0, ((size_t)rows + 127) / 128 * sizeof(int), s));
   VC_CUDA(vc::launch_layernorm_bf16(ws.x, w->blocks[0].ln1_w, w->blocks[0].ln1_b, ws.y, rows, C, s));
   vc::add_launches(1);
@@ -270,7 +270,7 @@ int vc_vit_forward(vc_handle* h, const vc_vit_weights* w, const uint8_t* images,
       p.ln_b = w->blocks[l + 1].ln1_b;
       p.ln_out = ws.y;
       p.tile_counters = ws.counters;
-    }
+      }
     rc = run_linear(h, ws.wide, b.fc2_w, rows, C, 4 * C, p, s);
     if (rc != VC_OK) return rc;
     if (!fused_ln && !last) {

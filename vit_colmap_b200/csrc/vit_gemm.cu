@@ -11,11 +11,19 @@
 //     covers 4 whole 128-byte lines (8 lanes x 16 B per row) instead of 32 different lines with
 //     16 B each -- the L1/LSU line rate, not HBM, bounded the K = 768 GEMMs before
 //   - kEpiResidualLnF32: the LayerNorm that follows a residual update runs in this kernel.  Every tile bumps
-//     the counter of its 128-row block after its stores are visible device-wide; the CTA that brings it to
-//     the number of column tiles owns the block: its 8 epilogue warps read the 128 complete rows back
-//     from L2 (just written: no HBM read), compute mean / variance exactly as the stand-alone kernel does
-//     (row in registers, two passes) and store the bf16 rows the next GEMM loads.  The MMA warp keeps
-//     filling the other TMEM buffer meanwhile.  Saves one launch and one pass over the fp32 stream per LN.
+//     the counter of its 128-row block after its stores are visible device-wide.  The CTA that processes
+//     the block's LAST column tile owns the block: it waits until the other column tiles have been counted
+//     (they have lower tile indices, so they run in the same round or earlier and nobody waits in a cycle),
+//     then its 8 epilogue warps read the 128 complete rows back from L2 (just written: no HBM read), compute
+//     mean / variance exactly as the stand-alone kernel does (row in registers, two passes) and store the
+//     bf16 rows the next GEMM loads.  A fixed owner keeps the work balanced: giving the block to whichever
+//     CTA finishes last (first version) fed back on itself -- a CTA that had normalised one block was late
+//     for all its later tiles, collected their blocks too and the GEMM waited for it (+ 170 us per GEMM).
+//     MEASURED (ViT-B/14, 32 x 518^2, tools/time_vit.py): 13.95 ms per forward against 11.96 ms with one
+//     launch per LayerNorm -- the 128 rows x 3 KB a block owner reads sit on its epilogue's critical path
+//     (8 warps per SM cover far less L2 latency than the stand-alone kernel's 64) and owners wait on their
+//     neighbours' tiles, so delays chain through a round.  vc_vit_forward therefore keeps the stand-alone
+//     LayerNorm launches; this epilogue stays available (vc_vit_linear_ln, VC_VIT_FUSED_LN=1), bit-identical.
 // Activations are bf16, accumulation and the residual stream are fp32.
 #include "vit_kernels.cuh"
 
@@ -43,43 +51,57 @@ __device__ __forceinline__ float warp_sum(float v) {
   return v;
 }
 
-// LayerNorm (eps 1e-6, biased variance around the mean: torch.nn.LayerNorm) of one fp32 row by one warp,
-// the row read through L2 (ld.global.cg: other SMs wrote most of it), bf16 out.  Same arithmetic as
-// layernorm_kernel in vit_pointwise.cu.
-__device__ __forceinline__ void ln_row_bf16(const float* __restrict__ xrow, const float* __restrict__ w,
-                                            const float* __restrict__ b, __nv_bfloat16* __restrict__ orow, int C,
-                                            int lane) {
-  constexpr int kVec = 8;  // float4 per lane, C <= 1024
+// LayerNorm (eps 1e-6, biased variance around the mean: torch.nn.LayerNorm) of RIF fp32 rows at a time by one
+// warp, the rows read through L2 (ld.global.cg: other SMs wrote most of them), bf16 out.  Same arithmetic
+// per row as layernorm_kernel in vit_pointwise.cu (bit-identical results); RIF rows are loaded before the
+// first reduction so that the L2 latency is paid once per batch of rows, not once per row.
+// KV = float4 per lane (C <= 128 * KV).
+template <int KV, int RIF>
+__device__ __forceinline__ void ln_rows_bf16(const float* __restrict__ x, size_t ldx, const float* __restrict__ w,
+                                             const float* __restrict__ b, __nv_bfloat16* __restrict__ out, int C,
+                                             int row_first, int row_step, int n_rows, int lane) {
   const int nvec = C >> 2;
-  float4 v[kVec];
-  float s = 0.f;
+  for (int r0 = row_first; r0 < n_rows; r0 += RIF * row_step) {
+    float4 v[RIF][KV];
 #pragma unroll
-  for (int k = 0; k < kVec; ++k) {
-    const int i = lane + 32 * k;
-    v[k] = i < nvec ? __ldcg(reinterpret_cast<const float4*>(xrow) + i) : make_float4(0, 0, 0, 0);
-    s += v[k].x + v[k].y + v[k].z + v[k].w;
-  }
-  const float mean = warp_sum(s) / (float)C;
-  float ss = 0.f;
+    for (int j = 0; j < RIF; ++j) {
+      const int r = r0 + j * row_step;
 #pragma unroll
-  for (int k = 0; k < kVec; ++k) {
-    const int i = lane + 32 * k;
-    if (i < nvec) {
-      const float a = v[k].x - mean, c = v[k].y - mean, d = v[k].z - mean, e = v[k].w - mean;
-      ss += a * a + c * c + d * d + e * e;
+      for (int k = 0; k < KV; ++k) {
+        const int i = lane + 32 * k;
+        v[j][k] = (r < n_rows && i < nvec) ? __ldcg(reinterpret_cast<const float4*>(x + (size_t)r * ldx) + i)
+                                           : make_float4(0, 0, 0, 0);
+      }
     }
-  }
-  const float rstd = rsqrtf(warp_sum(ss) / (float)C + 1e-6f);
 #pragma unroll
-  for (int k = 0; k < kVec; ++k) {
-    const int i = lane + 32 * k;
-    if (i < nvec) {
-      const float4 g = __ldg(reinterpret_cast<const float4*>(w) + i);
-      const float4 be = __ldg(reinterpret_cast<const float4*>(b) + i);
-      uint2 pk;
-      pk.x = pack_bf16((v[k].x - mean) * rstd * g.x + be.x, (v[k].y - mean) * rstd * g.y + be.y);
-      pk.y = pack_bf16((v[k].z - mean) * rstd * g.z + be.z, (v[k].w - mean) * rstd * g.w + be.w);
-      reinterpret_cast<uint2*>(orow)[i] = pk;
+    for (int j = 0; j < RIF; ++j) {
+      const int r = r0 + j * row_step;
+      if (r >= n_rows) break;  // warp-uniform
+      float s = 0.f;
+#pragma unroll
+      for (int k = 0; k < KV; ++k) s += v[j][k].x + v[j][k].y + v[j][k].z + v[j][k].w;
+      const float mean = warp_sum(s) / (float)C;
+      float ss = 0.f;
+#pragma unroll
+      for (int k = 0; k < KV; ++k) {
+        if (lane + 32 * k < nvec) {
+          const float a = v[j][k].x - mean, c = v[j][k].y - mean, d = v[j][k].z - mean, e = v[j][k].w - mean;
+          ss += a * a + c * c + d * d + e * e;
+        }
+      }
+      const float rstd = rsqrtf(warp_sum(ss) / (float)C + 1e-6f);
+#pragma unroll
+      for (int k = 0; k < KV; ++k) {
+        const int i = lane + 32 * k;
+        if (i < nvec) {
+          const float4 g = __ldg(reinterpret_cast<const float4*>(w) + i);
+          const float4 be = __ldg(reinterpret_cast<const float4*>(b) + i);
+          uint2 pk;
+          pk.x = pack_bf16((v[j][k].x - mean) * rstd * g.x + be.x, (v[j][k].y - mean) * rstd * g.y + be.y);
+          pk.y = pack_bf16((v[j][k].z - mean) * rstd * g.z + be.z, (v[j][k].w - mean) * rstd * g.w + be.w);
+          reinterpret_cast<uint2*>(out + (size_t)r * C)[i] = pk;
+        }
+      }
     }
   }
 }
@@ -101,7 +123,6 @@ vit_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant
   auto tfull_bar = [&](int s) { return bar0 + 8u * (2 * kStages + s); };
   auto tempty_bar = [&](int s) { return bar0 + 8u * (2 * kStages + 2 + s); };
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * kStages + 4);
-  int* ln_owner = reinterpret_cast<int*>(tmem_slot + 1);  // kEpiResidualLnF32: does this CTA own the row block?
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int nkb = p.K / BK;
@@ -317,24 +338,29 @@ vit_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant
         mbar_arrive(tempty_bar(as));
       }
       if (EPI == kEpiResidualLnF32) {
-        // tile stored: publish it, and normalise the 128-row block if this tile completed it
+        // tile stored: publish it; the CTA holding the block's last column tile normalises the block
         __threadfence();                                          // this thread's stores, device-wide
         asm volatile("bar.sync 1, 256;" ::: "memory");            // all 8 epilogue warps have stored
+        const bool owner = tn == tiles_n - 1;                      // CTA-uniform
         if (threadIdx.x == 128) {
-          const int done = atomicAdd(p.tile_counters + tm, 1) + 1;
-          *ln_owner = done == tiles_n;
-          if (done == tiles_n) p.tile_counters[tm] = 0;           // left zero for the next launch
-        }
-        asm volatile("bar.sync 1, 256;" ::: "memory");
-        if (*ln_owner) {                                          // CTA-uniform
-          __threadfence();                                        // order the reads after the counter
-          const int r_end = min(BM, p.M - tm * BM);
-          for (int r = warp - 4; r < r_end; r += 8) {
-            const size_t m = (size_t)tm * BM + r;
-            ln_row_bf16(static_cast<const float*>(p.out) + m * p.ldo, p.ln_w, p.ln_b, p.ln_out + m * p.N, p.N, lane);
+          if (!owner) {
+            atomicAdd(p.tile_counters + tm, 1);
+          } else {
+            volatile int* cnt = p.tile_counters + tm;
+            while (*cnt < tiles_n - 1) __nanosleep(64);            // the block's other column tiles
+            *cnt = 0;                                              // left zero for the next launch
           }
         }
-        asm volatile("bar.sync 1, 256;" ::: "memory");            // ln_owner is rewritten by the next tile
+        if (owner) {
+          asm volatile("bar.sync 1, 256;" ::: "memory");          // thread 128 has seen the full count
+          __threadfence();                                        // order the reads after the counter
+          const float* xb = static_cast<const float*>(p.out) + (size_t)tm * BM * p.ldo;
+          __nv_bfloat16* ob = p.ln_out + (size_t)tm * BM * p.N;
+          const int n_rows = min(BM, p.M - tm * BM);
+          if (p.N <= 384) ln_rows_bf16<3, 8>(xb, p.ldo, p.ln_w, p.ln_b, ob, p.N, warp - 4, 8, n_rows, lane);
+          else if (p.N <= 768) ln_rows_bf16<6, 4>(xb, p.ldo, p.ln_w, p.ln_b, ob, p.N, warp - 4, 8, n_rows, lane);
+          else ln_rows_bf16<8, 2>(xb, p.ldo, p.ln_w, p.ln_b, ob, p.N, warp - 4, 8, n_rows, lane);
+        }
       }
     }
   }
