@@ -469,3 +469,22 @@ def test_column_merge_paths_agree(matcher, monkeypatch):
             got = np.array(outs[0][0][k], np.uint32).reshape(-1, 2)
             differ = set(map(tuple, got.tolist())) ^ set(map(tuple, ref.tolist()))
             assert len(differ) <= 0.01 * len(ref) and len(ref) > 150   # fp32 near-ties only (accumulation order)
+
+
+def test_descriptor_width_not_a_multiple_of_8(matcher):
+    """ViTExtractor(descriptor_dim=100) writes 100-column blobs; match_descriptor_sets pads the rows with
+    zero columns (dot products unchanged) -- match lists equal the oracle on the unpadded rows, both rules."""
+    from oracle import matching as om
+    from vit_colmap_b200.matching import FeatureMatchingOptions, match_descriptor_sets
+    rng = np.random.default_rng(100)
+    counts, d = [260, 200, 0], 100
+    f = np.abs(_make_set(rng, 3, 260, d, counts))
+    descs = [om.to_uint8_colmap(om.l2_normalize(f[i, :n])) if n else np.zeros((0, d), np.uint8) for i, n in enumerate(counts)]
+    pairs = [(0, 1), (1, 0), (0, 2)]
+    for rule in ("angular", "l2"):
+        got = match_descriptor_sets(descs, pairs, FeatureMatchingOptions(max_ratio=0.9, max_distance=1.0, rule=rule), matcher)
+        for (i, j), m in zip(pairs, got):
+            ref = om.match_c(descs[i], descs[j], 0.9, 1.0, True) if rule == "angular" and counts[i] and counts[j] else \
+                om.match_l2_numpy(descs[i], descs[j], 0.9, 1.0, True)
+            assert m.tolist() == ref.tolist(), (rule, i, j)
+    assert len(got[0]) > 50

@@ -161,3 +161,25 @@ def test_decode_ahead_keeps_order_and_passes_failures_through():
     assert [g for k, _, g in out if k not in (3, 5)] == [i * i for i in range(30) if i not in (3, 5)]
     assert max(ahead) <= 6
     assert list(decode_ahead([], prepare)) == []
+
+
+def test_pad_descriptors_layout():
+    """matching.pad_descriptors: ragged lists -> one padded buffer; rows beyond each count and columns beyond
+    the descriptor width are zero (a width that is not a multiple of 8 is padded up), the row clamp follows
+    max_num_matches (SIFTGPU/SiftMatchCU.cpp:108), a staging list is reused when large enough."""
+    import numpy as np
+    from vit_colmap_b200.matching import pad_descriptors
+    rng = np.random.default_rng(0)
+    descs = [rng.integers(1, 256, (5, 100), dtype=np.uint8), np.zeros((0, 100), np.uint8),
+             rng.integers(1, 256, (9, 100), dtype=np.uint8)]
+    staging = []
+    buf, counts = pad_descriptors(descs, 7, pinned=False, staging=staging)
+    a = buf.numpy()
+    assert a.shape == (3, 7, 104) and counts.tolist() == [5, 0, 7]
+    assert np.array_equal(a[0, :5, :100], descs[0]) and not a[0, 5:].any() and not a[:, :, 100:].any()
+    assert not a[1].any() and np.array_equal(a[2, :, :100], descs[2][:7])
+    first = staging[0]
+    staging[0][:] = 255                                       # stale bytes from an earlier, larger upload
+    buf2, counts2 = pad_descriptors([d.astype(np.float32) for d in descs[:1]], 32768, pinned=False, staging=staging)
+    assert staging[0] is first and buf2.dtype.is_floating_point and tuple(buf2.shape) == (1, 5, 104)
+    assert np.array_equal(buf2.numpy()[0, :, :100], descs[0].astype(np.float32)) and not buf2.numpy()[0, :, 100:].any()

@@ -382,7 +382,8 @@ def pad_descriptors(descriptors: Sequence[np.ndarray], max_rows: int, pinned: bo
     augmentation takes its largest norm over every row, so padding must not be garbage)."""
     import torch
     n_images = len(descriptors)
-    d = max((int(x.shape[1]) for x in descriptors if x.ndim == 2 and x.shape[0] > 0), default=128)
+    d_in = max((int(x.shape[1]) for x in descriptors if x.ndim == 2 and x.shape[0] > 0), default=128)
+    d = -(-d_in // 8) * 8  # the kernels take rows of a multiple of 8 columns: zero columns leave every dot product unchanged
     is_u8 = all(x.dtype == np.uint8 for x in descriptors)
     kmax = max(max((int(x.shape[0]) for x in descriptors if x.ndim == 2), default=0), 1)
     kmax = min(kmax, max_rows)  # SIFTGPU/SiftMatchCU.cpp:108 clamps inputs likewise
@@ -401,7 +402,9 @@ def pad_descriptors(descriptors: Sequence[np.ndarray], max_rows: int, pinned: bo
         n = min(int(x.shape[0]), kmax) if x.ndim == 2 else 0
         counts[i] = n
         if n:
-            view[i, :n] = x[:n]
+            view[i, :n, : x.shape[1]] = x[:n]
+            if x.shape[1] < d:
+                view[i, :n, x.shape[1]:] = 0
         if n < kmax:
             view[i, n:] = 0
     return buf, counts
