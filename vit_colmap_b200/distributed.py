@@ -19,7 +19,7 @@ from typing import Callable, Dict, List, Optional, Sequence, Tuple
 
 import numpy as np
 
-from .pairing import ExhaustivePairGenerator, shard_blocks
+from .pairing import ExhaustivePairGenerator, shard_blocks, shard_blocks_local_first
 
 
 def _dist():
@@ -82,6 +82,71 @@ def all_gather_descriptors(desc_local, counts_local, n_total: int):
     return out_d.index_select(0, idx).contiguous(), out_c.index_select(0, idx).contiguous()
 
 
+class DescriptorExchange:
+    """The one all-gather of the path, started asynchronously: ``start`` enqueues the collective(s) on the
+    communication stream and returns at once; ``wait`` makes the current stream wait for them and returns
+    (desc [n_total, K, d], counts [n_total]).  Between the two the caller matches the pair blocks whose
+    images are all its own (pairing.shard_blocks_local_first), so the exchange costs no job time."""
+
+    def __init__(self, desc_local, counts_local, n_total: int):
+        import torch
+        dist = _dist()
+        self.rank, self.world = world_info()
+        self.n_total = int(n_total)
+        self.local = (desc_local, counts_local)
+        self.works = []
+        if self.world == 1:
+            return
+        n_max = -(-self.n_total // self.world)
+        K, d = desc_local.shape[1], desc_local.shape[2]
+        if desc_local.shape[0] == n_max:
+            pad_d, pad_c = desc_local.contiguous(), counts_local.contiguous()
+        else:  # shards are padded to the largest one so that the collective is regular
+            pad_d = torch.zeros((n_max, K, d), dtype=desc_local.dtype, device=desc_local.device)
+            pad_c = torch.zeros((n_max,), dtype=torch.int32, device=desc_local.device)
+            pad_d[: desc_local.shape[0]] = desc_local
+            pad_c[: counts_local.shape[0]] = counts_local
+        self.out_d = torch.empty((self.world * n_max, K, d), dtype=desc_local.dtype, device=desc_local.device)
+        self.out_c = torch.empty((self.world * n_max,), dtype=torch.int32, device=desc_local.device)
+        self._keep = (pad_d, pad_c)
+        self.n_max = n_max
+        self.works = [dist.all_gather_into_tensor(self.out_d, pad_d, async_op=True),
+                      dist.all_gather_into_tensor(self.out_c, pad_c, async_op=True)]
+
+    def wait(self):
+        import torch
+        if self.world == 1:
+            return self.local
+        for w in self.works:
+            w.wait()
+        if self.n_total == self.world * self.n_max:  # equal shards: the gathered buffer is the result
+            return self.out_d, self.out_c
+        keep = []
+        for r in range(self.world):
+            lo, hi = shard_range(self.n_total, r, self.world)
+            keep.extend(range(r * self.n_max, r * self.n_max + (hi - lo)))
+        idx = torch.tensor(keep, dtype=torch.long, device=self.out_d.device)
+        return self.out_d.index_select(0, idx).contiguous(), self.out_c.index_select(0, idx).contiguous()
+
+
+def block_owners(blocks: Sequence[Sequence[Tuple[int, int]]], index_of: Dict[int, int], n_total: int,
+                 world: int) -> List[int]:
+    """Rank that holds every image of a pair block under shard_range, or -1."""
+    bounds = [shard_range(n_total, r, world) for r in range(world)]
+
+    def owner_of(i: int) -> int:
+        for r, (lo, hi) in enumerate(bounds):
+            if lo <= i < hi:
+                return r
+        return -1
+
+    owners = []
+    for blk in blocks:
+        ranks = {owner_of(index_of[a]) for pr in blk for a in pr}
+        owners.append(ranks.pop() if len(ranks) == 1 else -1)
+    return owners
+
+
 def gather_to_writer(local: dict, dst: int = 0) -> Optional[dict]:
     """Merge per-rank {key: ndarray} dictionaries on the writer rank (None elsewhere)."""
     dist = _dist()
@@ -103,28 +168,41 @@ MatchFn = Callable[[np.ndarray], List[np.ndarray]]
 
 def match_exhaustive_sharded(image_ids: Sequence[int], match_fn: Callable[[np.ndarray], List[np.ndarray]],
                              block_size: int = 50, min_num_matches: int = 15,
-                             skip: Optional[Callable[[int, int], bool]] = None) -> Optional[Dict[Tuple[int, int], np.ndarray]]:
+                             skip: Optional[Callable[[int, int], bool]] = None,
+                             local_first: Optional[Tuple[Callable[[np.ndarray], List[np.ndarray]], Callable[[], None]]] = None
+                             ) -> Optional[Dict[Tuple[int, int], np.ndarray]]:
     """Exhaustive matching of the images `image_ids` (database order) sharded by pair block.
 
     `match_fn(index_pairs int32 [n,2]) -> list of [m,2] uint32` matches pairs given as indices into
     `image_ids` against the descriptors resident on this rank (GPU: Matcher.match_pairs on the
     all-gathered tensor).  Blocks follow ExhaustivePairGenerator (pairing.cc:202-236); pairs with
     fewer than `min_num_matches` matches are blanked (feature_matching_utils.cc:485-488).
+    `local_first = (match_fn_local, wait)`: the descriptor exchange is still in flight.  Blocks whose
+    images all sit in this rank's shard_range are matched first with `match_fn_local` (same index space,
+    only this rank's images are valid), then `wait()` is called once and the other blocks follow.
     Returns {(id1, id2): matches} on rank 0, None elsewhere."""
     rank, world = world_info()
     ids = [int(i) for i in image_ids]
     index_of = {i: k for k, i in enumerate(ids)}
     blocks = list(ExhaustivePairGenerator(ids, block_size).blocks())
-    mine = shard_blocks([len(b) for b in blocks], world)[rank]
+    sizes = [len(b) for b in blocks]
+    if local_first is None:
+        phases = [(shard_blocks(sizes, world)[rank], match_fn)]
+    else:
+        own, other = shard_blocks_local_first(sizes, block_owners(blocks, index_of, len(ids), world), world)
+        phases = [(own[rank], local_first[0]), (other[rank], match_fn)]
     local: Dict[Tuple[int, int], np.ndarray] = {}
-    for b in mine:
-        pairs = [p for p in blocks[b] if not (skip and skip(*p))]
-        if not pairs:
-            continue
-        idx = np.array([(index_of[a], index_of[c]) for a, c in pairs], dtype=np.int32)
-        for pair, m in zip(pairs, match_fn(idx)):
-            m = np.asarray(m, dtype=np.uint32).reshape(-1, 2)
-            local[pair] = m if m.shape[0] >= min_num_matches else np.zeros((0, 2), np.uint32)
+    for k, (mine, fn) in enumerate(phases):
+        if k == 1:
+            local_first[1]()
+        for b in mine:
+            pairs = [p for p in blocks[b] if not (skip and skip(*p))]
+            if not pairs:
+                continue
+            idx = np.array([(index_of[a], index_of[c]) for a, c in pairs], dtype=np.int32)
+            for pair, m in zip(pairs, fn(idx)):
+                m = np.asarray(m, dtype=np.uint32).reshape(-1, 2)
+                local[pair] = m if m.shape[0] >= min_num_matches else np.zeros((0, 2), np.uint32)
     return gather_to_writer(local, 0)
 
 

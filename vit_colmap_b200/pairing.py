@@ -95,6 +95,33 @@ def shard_blocks(block_sizes: Sequence[int], world_size: int) -> List[List[int]]
     return assign
 
 
+def shard_blocks_local_first(block_sizes: Sequence[int], block_owner: Sequence[int],
+                             world_size: int) -> Tuple[List[List[int]], List[List[int]]]:
+    """As shard_blocks, but a block whose images all live on one rank (block_owner[b] = that rank, -1
+    otherwise) goes to its owner: those pairs need no remote descriptors, so the owner matches them while
+    the all-gather is still in flight.  The remaining blocks are dealt by the same
+    longest-processing-time rule on top of the local loads.  Returns (local blocks per rank, other blocks
+    per rank); no collective -- every rank computes the same tables."""
+    loads = [0] * world_size
+    local: List[List[int]] = [[] for _ in range(world_size)]
+    rest = []
+    for b, size in enumerate(block_sizes):
+        r = int(block_owner[b])
+        if 0 <= r < world_size:
+            local[r].append(b)
+            loads[r] += int(size)
+        else:
+            rest.append(b)
+    other: List[List[int]] = [[] for _ in range(world_size)]
+    for b in sorted(rest, key=lambda b: (-int(block_sizes[b]), b)):
+        r = min(range(world_size), key=lambda k: (loads[k], k))
+        other[r].append(b)
+        loads[r] += int(block_sizes[b])
+    for a in other:
+        a.sort()
+    return local, other
+
+
 def shard_pairs(pairs: Sequence[Tuple[int, int]], rank: int, world_size: int) -> List[Tuple[int, int]]:
     """Contiguous split of a flat pair list (used when there are fewer blocks than ranks)."""
     n = len(pairs)
