@@ -61,6 +61,10 @@ def main():
     owners = vd.block_owners(blocks, {i: k for k, i in enumerate(ids)}, n_images, world)
     own, other = shard_blocks_local_first([len(b) for b in blocks], owners, world)
     n_pairs = n_rows = n_local_pairs = 0
+    overlap = os.environ.get("VC_JOB_NO_OVERLAP") != "1"   # =1: wait for the exchange first (comparison runs)
+    if not overlap:
+        exchange.wait()
+        torch.cuda.synchronize()
     for b in own[rank]:
         idx = np.array([(a - 1 - lo, c - 1 - lo) for a, c in blocks[b]], dtype=np.int32)
         for m in fn_local(idx):
@@ -91,7 +95,7 @@ def main():
         secs = float(mx[0].item())
         tf = 2.0 * kpts * kpts * d * total_pairs / secs / 1e12
         peak, _, src = _peaks()
-        print(json.dumps({"job": f"exhaustive matching of {n_images} images x {kpts} kpts x d={d}", "n_gpus": world,
+        print(json.dumps({"job": f"exhaustive matching of {n_images} images x {kpts} kpts x d={d}", "n_gpus": world, "exchange_overlapped": overlap,
                           "pairs": total_pairs, "match_rows": int(stats[3].item()), "seconds": secs,
                           "pairs_per_s": total_pairs / secs, "tflops_per_gpu": tf / world,
                           "frac_of_sustained_bf16_per_gpu": tf / world / peak, "peak_source": src,
