@@ -597,7 +597,6 @@ def run_db_e2e(torch, local):
     database (sqlite3 reads of the descriptor blobs, ONE upload, pair chunks on the resident set, batched
     write of the `matches` rows).  64 images x 2048 SIFT-like uint8 descriptors (d = 128), 2016 pairs."""
     import tempfile
-    from oracle import matching as om  # quantiser only (to_uint8_colmap): building inputs, not measured
     from vit_colmap_b200.database import ColmapDatabase
     from vit_colmap_b200.matching import FeatureMatchingOptions, Matcher, match_exhaustive
     n_images, k, d = 64, 2048, 128
@@ -611,7 +610,9 @@ def run_db_e2e(torch, local):
                 rows = np.abs(base[rng.permutation(4 * k)[:k]] + 0.15 * rng.standard_normal((k, d)).astype(np.float32))
                 image_id = db.add_image(f"im{i:03d}.png", camera_id=cam)
                 db.add_keypoints(image_id, rng.uniform(0, 480, (k, 2)).astype(np.float32))
-                db.add_descriptors(image_id, om.to_uint8_colmap(rows / np.linalg.norm(rows, axis=1, keepdims=True)))
+                unit = rows / np.linalg.norm(rows, axis=1, keepdims=True)
+                # COLMAP's quantiser, min(255, round(512 x)) (COLMAP/feature/utils.cc:56-71): input construction only
+                db.add_descriptors(image_id, np.clip(np.round(512.0 * unit), 0, 255).astype(np.uint8))
             db.close()
             return path
         matcher = Matcher(local)
