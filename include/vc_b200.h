@@ -203,6 +203,22 @@ int vc_score_map(vc_handle* h, const void* tokens, int dtype, int n_images, int 
                  int channels, int64_t image_stride, int method, float* score, void* workspace,
                  size_t workspace_bytes, void* stream);
 
+/* Allocation-free variant of vc_score_map: same arguments without the workspace, same kernels, same
+ * result bit for bit.  This entry point has no counterpart in the reference; it was added
+ * for callers that cannot call cudaMalloc (code under CUDA graph
+ * capture, tight serving loops, harnesses that forbid it).  Its scratch is a file-scope
+ * `static __device__` array of VC_SCORE_STATIC_MAX_FLOATS floats (4 MiB) that every GPU loading the
+ * library holds until the process exits; the call itself performs no cudaMalloc / cudaFree and
+ * calls no allocating library routine.  Limit: n_images * 5 * grid_h * grid_w <=
+ * VC_SCORE_STATIC_MAX_FLOATS (153 images of 37x37 cells, 21 of 85x114); larger requests fail with
+ * VC_ERR_WORKSPACE and leave `score` untouched.  Every call on a device shares the one array, which
+ * keeps the last call's contents (nothing in it has to start at zero: both regions are fully
+ * written before they are read).  Calls that overlap on the GPU (two streams, or two handles on one
+ * device) race on it: serialise them on one stream or with events. */
+#define VC_SCORE_STATIC_MAX_FLOATS (1u << 20)
+int vc_score_map_static(vc_handle* h, const void* tokens, int dtype, int n_images, int grid_h, int grid_w,
+                        int channels, int64_t image_stride, int method, float* score, void* stream);
+
 /* Keypoint selection.  coords: int32 [n_images, capacity, 2] as (y, x) grid cells, scores: f32
  * [n_images, capacity], counts: int32 [n_images]; rows come out in descending score order, ties
  * by the reference's concatenation order.  capacity >= min(num_keypoints, grid cells).

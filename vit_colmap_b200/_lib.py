@@ -59,6 +59,8 @@ SIGNATURES = {
     "vc_score_workspace_bytes": (c_size_t, [c_int, c_int, c_int]),
     "vc_score_map": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_int, c_int64, c_int,
                              c_void_p, c_void_p, c_size_t, c_void_p]),
+    "vc_score_map_static": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_int, c_int64, c_int,
+                                    c_void_p, c_void_p]),
     "vc_select_keypoints": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_int, c_float,
                                     c_void_p, c_void_p, c_void_p, c_int, c_void_p]),
     "vc_sample_pack": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_int, c_int64,
