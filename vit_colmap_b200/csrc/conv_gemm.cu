@@ -99,6 +99,7 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
+  griddep_wait();  // the set-up above overlaps the previous kernel's tail
 
   if (warp == 0 && lane == 0) {
     uint32_t stage = 0, phase = 0;
@@ -313,8 +314,7 @@ cudaError_t launch_one(const CUtensorMap& map_a, const CUtensorMap& map_w, const
                        cudaStream_t stream) {
   static SmemOptIn opt_in;  // one per EPI instantiation
   if (cudaError_t e = ensure_dynamic_smem(conv_gemm_kernel<EPI>, kSmemBytes, opt_in); e != cudaSuccess) return e;
-  conv_gemm_kernel<EPI><<<grid, kThreads, kSmemBytes, stream>>>(map_a, map_w, p);
-  return cudaGetLastError();
+  return launch_pdl(conv_gemm_kernel<EPI>, dim3(grid), dim3(kThreads), kSmemBytes, stream, map_a, map_w, p);
 }
 
 }  // namespace

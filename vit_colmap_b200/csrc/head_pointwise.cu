@@ -3,6 +3,8 @@
 // convolution 64 -> 4 with tanh(.)*pi on the orientation channel :112,222-223, and
 // F.normalize(dim=1, eps=1e-8) of the descriptor map :226.  Channels-last, 16-byte accesses.
 #include "head_kernels.cuh"
+#include "vc_launch.cuh"
+#include "vc_ptx.cuh"
 
 namespace vc {
 
@@ -36,6 +38,7 @@ __global__ void __launch_bounds__(256) resize_bilinear_kernel(const __nv_bfloat1
                                                               int Wi, int Ho, int Wo, int C, float sy, float sx) {
   const int cv = C >> 3;
   const long long total = (long long)B * Ho * Wo * cv;
+  griddep_wait();  // programmatic dependent launch: inputs belong to earlier kernels of the stream
   for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total;
        i += (long long)gridDim.x * blockDim.x) {
     const int v = (int)(i % cv);
@@ -77,6 +80,7 @@ __global__ void __launch_bounds__(256) kp_head_kernel(const __nv_bfloat16* __res
                                                       float* __restrict__ kp, long long pixels) {
   __shared__ float sw[4 * 64];
   __shared__ float sb[4];
+  griddep_wait();  // programmatic dependent launch: inputs belong to earlier kernels of the stream
   for (int i = threadIdx.x; i < 256; i += blockDim.x) sw[i] = w[i];
   if (threadIdx.x < 4) sb[threadIdx.x] = b[threadIdx.x];
   __syncthreads();
@@ -107,6 +111,7 @@ __global__ void __launch_bounds__(256) kp_head_kernel(const __nv_bfloat16* __res
 __global__ void __launch_bounds__(256) normalize_rows_kernel(float* __restrict__ desc, long long pixels, int d) {
   const int lane = threadIdx.x & 31;
   const int dv = d >> 2;
+  griddep_wait();  // programmatic dependent launch: inputs belong to earlier kernels of the stream
   for (long long px = ((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5; px < pixels;
        px += ((long long)gridDim.x * blockDim.x) >> 5) {
     float4* row = reinterpret_cast<float4*>(desc + px * d);
@@ -143,22 +148,20 @@ cudaError_t launch_resize_bilinear(const __nv_bfloat16* in, __nv_bfloat16* out, 
   const long long total = (long long)B * Ho * Wo * (C >> 3);
   // F.interpolate(size=...) uses in/out as the scale (fp32)
   const float sy = (float)Hi / (float)Ho, sx = (float)Wi / (float)Wo;
-  resize_bilinear_kernel<<<grid_for(total, 256, 148 * 64), 256, 0, stream>>>(in, out, B, Hi, Wi, Ho, Wo, C, sy, sx);
-  return cudaGetLastError();
+  return launch_pdl(resize_bilinear_kernel, dim3(grid_for(total, 256, 148 * 64)), dim3(256), 0, stream, in, out, B, Hi, Wi,
+                    Ho, Wo, C, sy, sx);
 }
 
 cudaError_t launch_kp_head(const __nv_bfloat16* hidden, const float* w, const float* b, float* kp,
                            long long pixels, cudaStream_t stream) {
   if (pixels <= 0) return cudaSuccess;
-  kp_head_kernel<<<grid_for(pixels, 256, 148 * 16), 256, 0, stream>>>(hidden, w, b, kp, pixels);
-  return cudaGetLastError();
+  return launch_pdl(kp_head_kernel, dim3(grid_for(pixels, 256, 148 * 16)), dim3(256), 0, stream, hidden, w, b, kp, pixels);
 }
 
 cudaError_t launch_normalize_rows(float* desc, long long pixels, int d, cudaStream_t stream) {
   if (pixels <= 0) return cudaSuccess;
   if (d % 4 != 0) return cudaErrorInvalidValue;
-  normalize_rows_kernel<<<grid_for(pixels * 32, 256, 148 * 32), 256, 0, stream>>>(desc, pixels, d);
-  return cudaGetLastError();
+  return launch_pdl(normalize_rows_kernel, dim3(grid_for(pixels * 32, 256, 148 * 32)), dim3(256), 0, stream, desc, pixels, d);
 }
 
 }  // namespace vc

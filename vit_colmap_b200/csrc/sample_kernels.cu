@@ -10,6 +10,7 @@
 //                        [C, d] projection streams through L2 once per CTA, fp32 SIMT FMAs.
 #include "extract_kernels.cuh"
 #include "vc_launch.cuh"
+#include "vc_ptx.cuh"
 
 namespace vc {
 
@@ -153,6 +154,7 @@ __global__ void __launch_bounds__(256) sample_pack_direct(const SampleParams p) 
   const int lane = threadIdx.x & 31;
   const long long wg = ((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
   const int b = (int)(wg / p.cap), k = (int)(wg - (long long)b * p.cap);
+  griddep_wait();  // programmatic dependent launch: inputs belong to earlier kernels of the stream
   if (b >= p.B) return;
   const size_t kp = (size_t)b * p.cap + k;
   if (k >= min(p.counts[b], p.cap)) {
@@ -228,6 +230,7 @@ __global__ void __launch_bounds__(256) sample_pack_project(const SampleParams p,
   extern __shared__ __align__(16) float sm[];
   float* vt = sm;                       // [C][kTile] sampled rows, channel-major
   float* outp = sm + (size_t)p.C * kTile;  // [kTile][d] projected rows
+  griddep_wait();  // programmatic dependent launch: inputs belong to earlier kernels of the stream
   const int b = blockIdx.x / tiles_per_image;
   const int k0 = (blockIdx.x - b * tiles_per_image) * kTile;
   const int cnt = min(p.counts[b], p.cap);
@@ -347,12 +350,13 @@ cudaError_t launch_sample_pack(const SampleParams& p, cudaStream_t stream) {
     const int blocks = (int)((warps * 32 + 255) / 256);
     if (blocks == 0) return cudaSuccess;
     const int kv = (p.C / 4 + 31) / 32;
+    cudaError_t le = cudaSuccess;
 #define VC_LAUNCH_DIRECT(KV)                                                    \
   do {                                                                          \
     if (p.is_bf16)                                                              \
-      sample_pack_direct<__nv_bfloat16, KV><<<blocks, 256, 0, stream>>>(p);     \
+      le = launch_pdl(sample_pack_direct<__nv_bfloat16, KV>, dim3(blocks), dim3(256), 0, stream, p); \
     else                                                                        \
-      sample_pack_direct<float, KV><<<blocks, 256, 0, stream>>>(p);             \
+      le = launch_pdl(sample_pack_direct<float, KV>, dim3(blocks), dim3(256), 0, stream, p); \
   } while (0)
     if (kv <= 1) VC_LAUNCH_DIRECT(1);
     else if (kv <= 2) VC_LAUNCH_DIRECT(2);
@@ -361,7 +365,7 @@ cudaError_t launch_sample_pack(const SampleParams& p, cudaStream_t stream) {
     else if (kv <= 6) VC_LAUNCH_DIRECT(6);
     else VC_LAUNCH_DIRECT(8);
 #undef VC_LAUNCH_DIRECT
-    return cudaGetLastError();
+    return le;
   }
   const int smem = (p.C * kTile + kTile * p.d) * (int)sizeof(float);
   static SmemOptIn opt_in[2];
@@ -372,10 +376,8 @@ cudaError_t launch_sample_pack(const SampleParams& p, cudaStream_t stream) {
   const int tiles = (p.cap + kTile - 1) / kTile;
   if (tiles == 0 || p.B == 0) return cudaSuccess;
   if (p.is_bf16)
-    sample_pack_project<__nv_bfloat16><<<p.B * tiles, 256, smem, stream>>>(p, tiles);
-  else
-    sample_pack_project<float><<<p.B * tiles, 256, smem, stream>>>(p, tiles);
-  return cudaGetLastError();
+    return launch_pdl(sample_pack_project<__nv_bfloat16>, dim3(p.B * tiles), dim3(256), smem, stream, p, tiles);
+  return launch_pdl(sample_pack_project<float>, dim3(p.B * tiles), dim3(256), smem, stream, p, tiles);
 }
 
 }  // namespace vc

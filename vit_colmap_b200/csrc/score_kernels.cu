@@ -10,6 +10,7 @@
 // zero-padded Gaussian stencils, corner/edge response, block-wide min / max, normalisation.
 #include "extract_kernels.cuh"
 #include "vc_launch.cuh"
+#include "vc_ptx.cuh"
 
 namespace vc {
 
@@ -46,6 +47,7 @@ moments_kernel(const T* __restrict__ tokens, int64_t image_stride, int B, int H,
                float* __restrict__ moments) {
   const int lane = threadIdx.x & 31;
   const int warp_global = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  griddep_wait();  // programmatic dependent launch: inputs belong to earlier kernels of the stream
   const int strips = (W + kStrip - 1) / kStrip;
   const int total = B * H * strips;
   if (warp_global >= total) return;
@@ -159,6 +161,7 @@ __device__ void minmax_inplace(float* s, int n, float* red) {
 __global__ void __launch_bounds__(1024, 1) response_kernel(const ScoreParams p) {
   extern __shared__ float s_avg[];  // [H*W] channel mean (DoG only)
   __shared__ float red[32];
+  griddep_wait();  // programmatic dependent launch: inputs belong to earlier kernels of the stream
   const int b = blockIdx.x;
   const int n = p.H * p.W;
   const size_t plane = (size_t)n;
@@ -227,14 +230,15 @@ cudaError_t launch_score_map(const ScoreParams& p, cudaStream_t stream) {
   const long long warps = (long long)p.B * p.H * strips;
   const int blocks = (int)((warps * 32 + 255) / 256);
   const int kv = (p.C / 4 + 31) / 32;
+  cudaError_t le = cudaSuccess;
 #define VC_LAUNCH_MOMENTS(KV)                                                                          \
   do {                                                                                                 \
     if (p.is_bf16)                                                                                     \
-      moments_kernel<__nv_bfloat16, KV><<<blocks, 256, 0, stream>>>(                                   \
-          static_cast<const __nv_bfloat16*>(p.tokens), p.image_stride, p.B, p.H, p.W, p.C, p.moments); \
+      le = launch_pdl(moments_kernel<__nv_bfloat16, KV>, dim3(blocks), dim3(256), 0, stream,           \
+                      static_cast<const __nv_bfloat16*>(p.tokens), p.image_stride, p.B, p.H, p.W, p.C, p.moments); \
     else                                                                                               \
-      moments_kernel<float, KV><<<blocks, 256, 0, stream>>>(static_cast<const float*>(p.tokens),       \
-                                                            p.image_stride, p.B, p.H, p.W, p.C, p.moments); \
+      le = launch_pdl(moments_kernel<float, KV>, dim3(blocks), dim3(256), 0, stream,                   \
+                      static_cast<const float*>(p.tokens), p.image_stride, p.B, p.H, p.W, p.C, p.moments); \
   } while (0)
   if (kv <= 1) VC_LAUNCH_MOMENTS(1);
   else if (kv <= 2) VC_LAUNCH_MOMENTS(2);
@@ -243,11 +247,9 @@ cudaError_t launch_score_map(const ScoreParams& p, cudaStream_t stream) {
   else if (kv <= 6) VC_LAUNCH_MOMENTS(6);
   else VC_LAUNCH_MOMENTS(8);
 #undef VC_LAUNCH_MOMENTS
-  cudaError_t e = cudaGetLastError();
-  if (e != cudaSuccess) return e;
+  if (le != cudaSuccess) return le;
   const int smem = (p.method == 0) ? 0 : p.H * p.W * (int)sizeof(float);
-  response_kernel<<<p.B, 1024, smem, stream>>>(p);
-  return cudaGetLastError();
+  return launch_pdl(response_kernel, dim3(p.B), dim3(1024), smem, stream, p);
 }
 
 }  // namespace vc

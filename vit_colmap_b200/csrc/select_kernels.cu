@@ -14,6 +14,7 @@
 //   4. block-wide exclusive scan -> (y, x), score in descending-score order.
 #include "extract_kernels.cuh"
 #include "vc_launch.cuh"
+#include "vc_ptx.cuh"
 
 namespace vc {
 
@@ -60,6 +61,7 @@ __global__ void __launch_bounds__(kThreads, 1) select_kernel(const SelectParams 
   extern __shared__ __align__(16) uint8_t smem[];
   __shared__ int s_scan[32];
   __shared__ int s_total;
+  griddep_wait();  // programmatic dependent launch: inputs belong to earlier kernels of the stream
   const int b = blockIdx.x;
   const int H = p.H, W = p.W, HW = H * W;
   const Geometry g = make_geometry(H, W, p.num_keypoints, p.bin_size);
@@ -217,8 +219,7 @@ cudaError_t launch_select_keypoints(const SelectParams& p, cudaStream_t stream) 
   const int smem = select_smem_bytes(p.H, p.W, p.num_keypoints, p.bin_size);
   static SmemOptIn opt_in;
   if (cudaError_t e = ensure_dynamic_smem(select_kernel, smem, opt_in); e != cudaSuccess) return e;
-  select_kernel<<<p.B, kThreads, smem, stream>>>(p);
-  return cudaGetLastError();
+  return launch_pdl(select_kernel, dim3(p.B), dim3(kThreads), smem, stream, p);
 }
 
 }  // namespace vc

@@ -12,6 +12,8 @@
 //      this CTA only, so it is L2-resident and block barriers suffice
 //   C. the first min(K, n) entries become keypoint rows.
 #include "extract_kernels.cuh"
+#include "vc_launch.cuh"
+#include "vc_ptx.cuh"
 
 #include <math.h>
 
@@ -23,6 +25,7 @@ constexpr int kThreads = 1024;
 
 __global__ void __launch_bounds__(kThreads, 1) trainable_select_kernel(const TrainableSelectParams p) {
   __shared__ int s_count;
+  griddep_wait();  // programmatic dependent launch: inputs belong to earlier kernels of the stream
   const int b = blockIdx.x;
   const int n = p.H * p.W;
   const float* kp = p.kp_map + (size_t)b * n * 4;
@@ -126,8 +129,7 @@ __global__ void __launch_bounds__(kThreads, 1) trainable_select_kernel(const Tra
 
 cudaError_t launch_trainable_select(const TrainableSelectParams& p, cudaStream_t stream) {
   if (p.B <= 0) return cudaSuccess;
-  trainable_select_kernel<<<p.B, kThreads, 0, stream>>>(p);
-  return cudaGetLastError();
+  return launch_pdl(trainable_select_kernel, dim3(p.B), dim3(kThreads), 0, stream, p);
 }
 
 }  // namespace vc

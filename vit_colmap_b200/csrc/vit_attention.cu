@@ -257,6 +257,7 @@ vit_attention_kernel(const __grid_constant__ CUtensorMap map_qkv, const AttnPara
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot + half * 256;
+  griddep_wait();  // qkv is written by the previous kernel; the set-up above overlaps its tail
 
   if (lw == 0) {
     if (lane == 0 && n_items > 0) {
@@ -423,8 +424,7 @@ static cudaError_t launch_items(const CUtensorMap& map_qkv, const AttnParams& p,
   const int q_tiles = (p.T + kTile - 1) / kTile;
   const int total = p.B * p.heads * q_tiles;
   const int grid = (total + 1) / 2 < num_sms ? (total + 1) / 2 : num_sms;
-  vit_attention_kernel<<<grid, 2 * kHalfThreads, kSmemBytes, stream>>>(map_qkv, p);
-  return cudaGetLastError();
+  return launch_pdl(vit_attention_kernel, dim3(grid), dim3(2 * kHalfThreads), kSmemBytes, stream, map_qkv, p);
 }
 
 cudaError_t launch_attention(const CUtensorMap& map_qkv, const AttnParams& p, cudaStream_t stream) {

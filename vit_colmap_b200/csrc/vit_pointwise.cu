@@ -2,6 +2,8 @@
 // normalisation + im2col of the 14x14/s14 patch convolution, vit_extractor.py:117-132 and
 // SURVEY.md Appendix A), LayerNorm (eps 1e-6) feeding the GEMMs in bf16, and the final norm that
 // also drops the cls token (x_norm_patchtokens).
+#include "vc_launch.cuh"
+#include "vc_ptx.cuh"
 #include "vit_kernels.cuh"
 
 namespace vc {
@@ -23,6 +25,7 @@ layernorm_kernel(const float* __restrict__ x, const float* __restrict__ w, const
                  void* __restrict__ out, int rows, int T, int C) {
   const int lane = threadIdx.x & 31;
   const int row = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  griddep_wait();  // x is the previous kernel's output
   if (row >= rows) return;
   size_t out_row = row;
   if (kFinal) {
@@ -91,6 +94,7 @@ patchify_kernel(const uint8_t* __restrict__ images, int B, int img_h, int img_w,
     lut[c][u] = __fdiv_rn(__fsub_rn(__fdiv_rn((float)u, 255.0f), mean), sd);
   }
   __syncthreads();
+  griddep_wait();  // the table above is built from constants; images / patches / x belong to other kernels
   const int gw = img_w / 14, gh = img_h / 14;
   const int vec_per_patch = kpad >> 3;
   const size_t total = (size_t)B * gh * gw * vec_per_patch;
@@ -140,8 +144,7 @@ cudaError_t launch_layernorm_bf16(const float* x, const float* w, const float* b
                                   int rows, int C, cudaStream_t stream) {
   if (rows <= 0) return cudaSuccess;
   const int blocks = (int)(((long long)rows * 32 + 255) / 256);
-  layernorm_kernel<false><<<blocks, 256, 0, stream>>>(x, w, b, out, rows, 1, C);
-  return cudaGetLastError();
+  return launch_pdl(layernorm_kernel<false>, dim3(blocks), dim3(256), 0, stream, x, w, b, out, rows, 1, C);
 }
 
 cudaError_t launch_layernorm_final(const float* x, const float* w, const float* b, float* out, int B,
@@ -149,8 +152,7 @@ cudaError_t launch_layernorm_final(const float* x, const float* w, const float* 
   const long long rows = (long long)B * T;
   if (rows <= 0) return cudaSuccess;
   const int blocks = (int)((rows * 32 + 255) / 256);
-  layernorm_kernel<true><<<blocks, 256, 0, stream>>>(x, w, b, out, (int)rows, T, C);
-  return cudaGetLastError();
+  return launch_pdl(layernorm_kernel<true>, dim3(blocks), dim3(256), 0, stream, x, w, b, out, (int)rows, T, C);
 }
 
 cudaError_t launch_patchify(const uint8_t* images, int B, int img_h, int img_w, int bgr,
@@ -159,9 +161,8 @@ cudaError_t launch_patchify(const uint8_t* images, int B, int img_h, int img_w, 
   const size_t total = (size_t)B * (img_h / 14) * (img_w / 14) * (kpad / 8);  // kpad is a multiple of 64
   if (total == 0) return cudaSuccess;
   const unsigned blocks = (unsigned)((total + 255) / 256);
-  patchify_kernel<<<blocks, 256, 0, stream>>>(images, B, img_h, img_w, bgr, patches, kpad, cls_token, pos,
-                                              x, C);
-  return cudaGetLastError();
+  return launch_pdl(patchify_kernel, dim3(blocks), dim3(256), 0, stream, images, B, img_h, img_w, bgr, patches, kpad,
+                    cls_token, pos, x, C);
 }
 
 }  // namespace vc
