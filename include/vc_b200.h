@@ -401,6 +401,62 @@ int vc_conv2d(vc_handle* h, const void* in, int n, int height, int width, int c_
 int vc_resize_bilinear(vc_handle* h, const void* in, int n, int in_h, int in_w, int out_h, int out_w,
                        int channels, void* out, void* stream);
 
+/* ------------------------------------------------------------------------------------------
+ * Training-time similarity and hard-negative mining on patch tokens.
+ * Reference: vit_colmap/dataloader/training_sampler.py TrainingSampler.select_invariant_points
+ * :56-181, sample_features_at_coords :183-211, generate_hard_negatives :452-534;
+ * vit_colmap/dataloader/homography_utils.py warp_patch_tokens :10-92, compute_feature_similarity
+ * :219-253.  Feature maps are fp32, token-major [n, grid_h*grid_w, channels] (the backbone's own
+ * layout), channels a multiple of 4 and <= 1024, at most 16384 cells; all buffers device memory.
+ * Everything is computed in fp32: the outputs are index lists, which only equal the reference's
+ * when the similarities agree to ~1e-6.
+ * ------------------------------------------------------------------------------------------ */
+
+/* [n, C, H, W] fp32 (the reference's layout) -> token-major [n, H*W, C].  Replaces nothing in the
+ * reference (its permutes are views); exists so that callers holding NCHW maps can use the entries
+ * below without a PyTorch copy. */
+int vc_nchw_to_tokens(vc_handle* h, const float* nchw, int n_images, int channels, int grid_h, int grid_w,
+                      float* tokens, void* stream);
+
+/* similarity[b, y, x] = cosine(warp(tokens1[b])[y, x], tokens2[b][y, x]): tokens1 is resampled at
+ * h_inv[b] * (patch centre (x+.5, y+.5) * patch_size) with F.grid_sample(bilinear, zeros,
+ * align_corners=False) semantics after normalising by (img_w, img_h); both vectors are L2-normalised
+ * with eps 1e-12.  h_inv: device f32 [n_pairs, 9] row-major = torch.linalg.inv(H) computed by the caller.
+ * Replaces: homography_utils.compute_feature_similarity :219-253 (= warp_patch_tokens :10-92 +
+ * F.normalize + channel sum), the first half of TrainingSampler.select_invariant_points :83-97. */
+int vc_warp_similarity(vc_handle* h, const float* tokens1, const float* tokens2, int n_pairs, int grid_h,
+                       int grid_w, int channels, const float* h_inv, float patch_size, float img_h, float img_w,
+                       float* similarity, void* stream);
+
+/* Per row of values [n_rows, n] (n <= 16384):
+ *   order   int32 [n_rows, k]: indices by value descending, lower index first among equal values
+ *           (torch.topk leaves tie order unspecified), -1 beyond n; may be NULL when k == 0
+ *   above   int32 [n_rows, n]: ascending indices with value >= threshold (torch.nonzero order), or NULL
+ *   n_above int32 [n_rows]: how many, or NULL
+ * Replaces: the topk / threshold / hybrid selections of select_invariant_points :100-166 (the mode
+ * logic on these three outputs stays on the host: vit_colmap_b200/dataloader/training_sampler.py). */
+int vc_topk_rows(vc_handle* h, const float* values, int n_rows, int n, int k, float threshold, int32_t* order,
+                 int32_t* above, int32_t* n_above, void* stream);
+
+/* Hard negatives: for every positive k of image b, the n_hard (<= 32) cells with the highest cosine
+ * similarity to pos_feat[b, k] among the cells at least `radius` (feature-map units, Euclidean) away
+ * from pos_xy[b, k] = (x, y).  idx int32 [n_images, n_pos, n_hard] by similarity descending (lower cell
+ * first on ties), -1 where fewer than n_hard cells qualify; counts int32 [n_images, n_pos].
+ * The n_pos x cells similarity matrix is never stored.
+ * Replaces: the double loop of TrainingSampler.generate_hard_negatives :489-512 (matmul per positive,
+ * distance mask, topk); the gather that follows is vc_sample_bilinear. */
+int vc_hard_negatives(vc_handle* h, const float* tokens, const float* pos_feat, const float* pos_xy, int n_images,
+                      int grid_h, int grid_w, int channels, int n_pos, int n_hard, float radius, int32_t* idx,
+                      int32_t* counts, void* stream);
+
+/* out[b, i, :] = bilinear sample of tokens[b] at xy[b, i] = (x, y) feature-map units, exactly as the
+ * reference does it: g = v / (size - 1) * 2 - 1 handed to F.grid_sample(bilinear, zeros,
+ * align_corners=False), i.e. source position v * size / (size - 1) - 0.5.  A NaN coordinate gives a
+ * zero row (padding entries).  out: f32 [n_images, n_points, channels].
+ * Replaces: TrainingSampler.sample_features_at_coords :183-211. */
+int vc_sample_bilinear(vc_handle* h, const float* tokens, int n_images, int grid_h, int grid_w, int channels,
+                       const float* xy, int n_points, float* out, void* stream);
+
 /* Number of kernels launched by this library on the calling thread since the last reset
  * (bench.py reports it as gpu_launches). */
 int64_t vc_launch_count(int reset);

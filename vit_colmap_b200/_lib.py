@@ -87,6 +87,15 @@ SIGNATURES = {
                           c_void_p, c_void_p, c_void_p, c_void_p]),
     "vc_resize_bilinear": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_int, c_int, c_void_p,
                                    c_void_p]),
+    "vc_nchw_to_tokens": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_void_p, c_void_p]),
+    "vc_warp_similarity": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_void_p, c_float,
+                                   c_float, c_float, c_void_p, c_void_p]),
+    "vc_topk_rows": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_float, c_void_p, c_void_p, c_void_p,
+                             c_void_p]),
+    "vc_hard_negatives": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_int, c_int,
+                                  c_float, c_void_p, c_void_p, c_void_p]),
+    "vc_sample_bilinear": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_void_p, c_int, c_void_p,
+                                   c_void_p]),
 }
 
 
