@@ -13,9 +13,9 @@
 //                            cosine with the target cell -- both maps are read once (HBM-bound).
 //   topk_rows_kernel       : CTA per row, bitonic sort of 64-bit keys (value desc, index asc) in
 //                            shared memory, plus the ascending list of entries >= threshold.
-//   hard_negatives_kernel  : CTA = 32 positives of one image against every cell: fp32 similarity
-//                            tiles through shared memory, distance mask, per-row top-n kept in
-//                            registers across the lanes of a warp -- the K x HW matrix is never stored.
+//   hard_negatives_kernel  : CTA = 32 positives of one image against every cell: fp32 SIMT GEMM tiles
+//                            (8 x 4 per thread) through shared memory, distance mask, per-row top-n kept
+//                            in registers across the lanes of a warp -- the K x HW matrix is never stored.
 //   sample_bilinear_kernel : warp per point, the reference's (x / (W-1)) * 2 - 1 normalisation fed to
 //                            an align_corners=False grid_sample with zero padding.
 #include "sampler_kernels.cuh"
@@ -34,6 +34,17 @@ __device__ __forceinline__ float warp_sum(float v) {
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
   return v;
+}
+
+// Blackwell packed fp32 pair FMA (FFMA2): two multiply-adds per instruction -- a 3-register FFMA issues
+// every other cycle per SM sub-partition, so the full fp32 rate needs the packed form.
+__device__ __forceinline__ float2 ffma2(float2 a, float2 b, float2 c) {
+  uint64_t d;
+  asm("fma.rn.f32x2 %0, %1, %2, %3;"
+      : "=l"(d)
+      : "l"(*reinterpret_cast<uint64_t*>(&a)), "l"(*reinterpret_cast<uint64_t*>(&b)),
+        "l"(*reinterpret_cast<uint64_t*>(&c)));
+  return *reinterpret_cast<float2*>(&d);
 }
 
 __device__ __forceinline__ unsigned orderable(float f) {
@@ -238,15 +249,22 @@ __global__ void __launch_bounds__(kTopkThreads, 1) topk_rows_kernel(const TopkPa
 }
 
 // ------------------------------------------------------------------ hard negatives
-constexpr int kHnRows = 32;     // positives per CTA (4 per warp)
-constexpr int kHnCells = 32;    // cells per tile (one per lane)
-constexpr int kHnChunk = 64;    // channels staged per step
-constexpr int kHnThreads = 256;
+// fp32 SIMT GEMM tile: CTA = 32 positives x 128 cells, 4 warps; warp = 8 positives, lane = 4 cells (lane + 32 j), so a
+// thread holds an 8 x 4 accumulator tile and per 4 channels issues 128 FMAs against 12 shared-memory loads
+// (8 broadcast reads of the positives, 4 vector reads of the cells), as 64 packed FFMA2: FMA-bound.  Both
+// operands are staged per 32-channel chunk (20 KB of shared memory per CTA, several CTAs per SM).
+constexpr int kHnRows = 32;      // positives per CTA
+constexpr int kHnRowsW = 8;      // positives per warp
+constexpr int kHnCells = 128;    // cells per tile (4 per lane)
+constexpr int kHnChunk = 32;     // channels staged per step
+constexpr int kHnThreads = 128;
 
-__global__ void __launch_bounds__(kHnThreads) hard_negatives_kernel(const HardNegParams p) {
-  extern __shared__ __align__(16) float hn_smem[];
-  float* s_pos = hn_smem;                               // [kHnRows][C]
-  float* s_cell = hn_smem + (size_t)kHnRows * p.C;      // [kHnChunk][kHnCells + 1]
+__global__ void __launch_bounds__(kHnThreads, 4) hard_negatives_kernel(const HardNegParams p) {
+  __shared__ __align__(16) float s_pos[kHnRows][kHnChunk];
+  __shared__ __align__(16) float s_cell[kHnCells][kHnChunk + 4];  // +4: a quarter-warp's 16-byte reads hit 32 banks
+  __shared__ float s_ss[4][kHnCells];   // per-warp partial squared norms of the tile's cells
+  __shared__ float s_pn[kHnRows];       // norms of the positives
+  __shared__ float2 s_pxy[kHnRows];     // their (x, y)
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int tiles_k = (p.K + kHnRows - 1) / kHnRows;
   const int b = blockIdx.x / tiles_k;
@@ -254,93 +272,122 @@ __global__ void __launch_bounds__(kHnThreads) hard_negatives_kernel(const HardNe
   const int HW = p.H * p.W;
   griddep_wait();
   const float* img = p.tokens + (int64_t)b * p.image_stride;
+  const float* pos = p.pos_feat + (size_t)b * p.K * p.C;
 
-  // stage this CTA's positives; each warp owns rows 4 warp .. 4 warp + 3
-  for (int i = threadIdx.x; i < kHnRows * (p.C >> 2); i += kHnThreads) {
-    const int r = i / (p.C >> 2), v = i - r * (p.C >> 2);
-    const int k = k0 + r;
-    float4 x = make_float4(0, 0, 0, 0);
-    if (k < p.K) x = ldf4(p.pos_feat + ((size_t)b * p.K + k) * p.C, v);
-    reinterpret_cast<float4*>(s_pos + (size_t)r * p.C)[v] = x;
-  }
-  __syncthreads();
-  float inv_p[4], pxr[4], pyr[4];
-  unsigned long long best[4];  // lane i holds entry i of the row's descending top-n list
-#pragma unroll
-  for (int q = 0; q < 4; ++q) {
-    const int r = 4 * warp + q;
+  // norms of this CTA's positives (F.normalize eps 1e-12, training_sampler.py:479-481): warp per 8 rows
+  for (int q = 0; q < kHnRowsW; ++q) {
+    const int k = k0 + kHnRowsW * warp + q;
     float ss = 0.f;
-    for (int c = lane; c < p.C; c += 32) ss += s_pos[(size_t)r * p.C + c] * s_pos[(size_t)r * p.C + c];
-    inv_p[q] = fmaxf(sqrtf(warp_sum(ss)), 1e-12f);  // F.normalize eps (training_sampler.py:479-481)
-    const int k = k0 + r;
-    const float2 xy = k < p.K ? reinterpret_cast<const float2*>(p.pos_xy)[(size_t)b * p.K + k] : make_float2(0.f, 0.f);
-    pxr[q] = xy.x;
-    pyr[q] = xy.y;
-    best[q] = 0ull;
+    if (k < p.K)
+      for (int v = lane; v < (p.C >> 2); v += 32) {
+        const float4 x = ldf4(pos + (size_t)k * p.C, v);
+        ss += x.x * x.x + x.y * x.y + x.z * x.z + x.w * x.w;
+      }
+    ss = warp_sum(ss);
+    if (lane == 0) s_pn[kHnRowsW * warp + q] = fmaxf(sqrtf(ss), 1e-12f);
   }
+  if (threadIdx.x < kHnRows) {
+    const int k = k0 + threadIdx.x;
+    s_pxy[threadIdx.x] =
+        k < p.K ? reinterpret_cast<const float2*>(p.pos_xy)[(size_t)b * p.K + k] : make_float2(0.f, 0.f);
+  }
+  unsigned long long best[kHnRowsW];  // lane i holds entry i of the row's descending top-n list
+#pragma unroll
+  for (int q = 0; q < kHnRowsW; ++q) best[q] = 0ull;
 
   for (int j0 = 0; j0 < HW; j0 += kHnCells) {
-    const int cell = j0 + lane;
-    float acc[4] = {0.f, 0.f, 0.f, 0.f};
-    float ssf = 0.f;
+    float2 acc[kHnRowsW][4];  // (even-channel sum, odd-channel sum) of positive q x cell j
+#pragma unroll
+    for (int q = 0; q < kHnRowsW; ++q)
+#pragma unroll
+      for (int e = 0; e < 4; ++e) acc[q][e] = make_float2(0.f, 0.f);
+    float ssf[4] = {0.f, 0.f, 0.f, 0.f};
     for (int c0 = 0; c0 < p.C; c0 += kHnChunk) {
       __syncthreads();  // previous chunk consumed
-      // stage [kHnChunk channels][kHnCells cells], transposed so that a lane reads its own cell
+      for (int i = threadIdx.x; i < kHnRows * (kHnChunk >> 2); i += kHnThreads) {
+        const int r = i / (kHnChunk >> 2), v = i - r * (kHnChunk >> 2);
+        float4 x = make_float4(0, 0, 0, 0);
+        if (k0 + r < p.K && c0 + 4 * v < p.C) x = ldf4(pos + (size_t)(k0 + r) * p.C + c0, v);
+        *reinterpret_cast<float4*>(&s_pos[r][4 * v]) = x;
+      }
+      // cells: eight lanes read the 128 contiguous bytes of one cell's chunk and store them as one row
       for (int i = threadIdx.x; i < kHnCells * (kHnChunk >> 2); i += kHnThreads) {
         const int jc = i / (kHnChunk >> 2), v = i - jc * (kHnChunk >> 2);
         float4 x = make_float4(0, 0, 0, 0);
         if (j0 + jc < HW && c0 + 4 * v < p.C) x = ldf4(img + (size_t)(j0 + jc) * p.C + c0, v);
-        float* dst = s_cell + (size_t)(4 * v) * (kHnCells + 1) + jc;
-        dst[0] = x.x;
-        dst[kHnCells + 1] = x.y;
-        dst[2 * (kHnCells + 1)] = x.z;
-        dst[3 * (kHnCells + 1)] = x.w;
+        *reinterpret_cast<float4*>(&s_cell[jc][4 * v]) = x;
       }
       __syncthreads();
-      const int cn = min(kHnChunk, p.C - c0);
-      for (int c = 0; c < cn; c += 4) {
-        float f[4];
+#pragma unroll 1
+      for (int c = 0; c < kHnChunk; c += 4) {
+        float4 f[4];  // f[j] = channels c .. c+3 of this lane's cell j (cells lane, lane + 32, lane + 64, lane + 96)
 #pragma unroll
-        for (int e = 0; e < 4; ++e) f[e] = s_cell[(size_t)(c + e) * (kHnCells + 1) + lane];
-        ssf += f[0] * f[0] + f[1] * f[1] + f[2] * f[2] + f[3] * f[3];
+        for (int j = 0; j < 4; ++j) f[j] = *reinterpret_cast<const float4*>(&s_cell[lane + 32 * j][c]);
+        if (((c >> 2) & 3) == warp) {  // warp-uniform: the four warps share the norm work by channel group
 #pragma unroll
-        for (int q = 0; q < 4; ++q) {
-          const float4 pv = *reinterpret_cast<const float4*>(s_pos + (size_t)(4 * warp + q) * p.C + c0 + c);
-          acc[q] += pv.x * f[0] + pv.y * f[1] + pv.z * f[2] + pv.w * f[3];
+          for (int j = 0; j < 4; ++j)
+            ssf[j] = fmaf(f[j].x, f[j].x, fmaf(f[j].y, f[j].y, fmaf(f[j].z, f[j].z, fmaf(f[j].w, f[j].w, ssf[j]))));
+        }
+#pragma unroll
+        for (int q = 0; q < kHnRowsW; ++q) {
+          const float4 pv = *reinterpret_cast<const float4*>(&s_pos[kHnRowsW * warp + q][c]);
+#pragma unroll
+          for (int j = 0; j < 4; ++j)  // operand pairs are the adjacent registers of the 16-byte loads
+            acc[q][j] = ffma2(make_float2(pv.z, pv.w), make_float2(f[j].z, f[j].w),
+                              ffma2(make_float2(pv.x, pv.y), make_float2(f[j].x, f[j].y), acc[q][j]));
         }
       }
     }
-    const float inv_f = fmaxf(sqrtf(ssf), 1e-12f);
-    const float cxf = (float)(cell % p.W), cyf = (float)(cell / p.W);
+    // cell norms: sum of the four warps' partials
+    __syncthreads();
 #pragma unroll
-    for (int q = 0; q < 4; ++q) {
-      // cosine with the positive; cells closer than the radius are not candidates (:497-503)
-      const float sim = __fdiv_rn(acc[q], __fmul_rn(inv_f, inv_p[q]));
-      const float dx = __fsub_rn(cxf, pxr[q]), dy = __fsub_rn(cyf, pyr[q]);
-      const float dist = __fsqrt_rn(__fadd_rn(__fmul_rn(dx, dx), __fmul_rn(dy, dy)));
-      const bool cand = cell < HW && (k0 + 4 * warp + q) < p.K && dist >= p.radius && sim == sim;
-      const unsigned long long key =
-          cand ? (((unsigned long long)orderable(sim) << 32) | (unsigned long long)(0xFFFFFFFFu - (unsigned)cell)) : 0ull;
+    for (int e = 0; e < 4; ++e) s_ss[warp][lane + 32 * e] = ssf[e];
+    __syncthreads();
+    float nf[4], cxf[4], cyf[4];
+#pragma unroll
+    for (int e = 0; e < 4; ++e) {
+      const int jc = lane + 32 * e;
+      nf[e] = fmaxf(sqrtf(s_ss[0][jc] + s_ss[1][jc] + s_ss[2][jc] + s_ss[3][jc]), 1e-12f);
+      const int cell = j0 + jc, cy = cell / p.W;
+      cxf[e] = (float)(cell - cy * p.W);
+      cyf[e] = (float)cy;
+    }
+#pragma unroll
+    for (int q = 0; q < kHnRowsW; ++q) {
+      const bool row_ok = (k0 + kHnRowsW * warp + q) < p.K;
+      const float np_ = s_pn[kHnRowsW * warp + q];
+      const float2 pxy = s_pxy[kHnRowsW * warp + q];
       unsigned long long thr = __shfl_sync(0xffffffffu, best[q], p.n_hard - 1);
-      unsigned m = __ballot_sync(0xffffffffu, key > thr);
-      while (m) {
-        const int src = __ffs(m) - 1;
-        m &= m - 1;
-        const unsigned long long kin = __shfl_sync(0xffffffffu, key, src);
-        if (kin > thr) {  // warp-uniform
-          const int pos = __popc(__ballot_sync(0xffffffffu, best[q] > kin && lane < p.n_hard));
-          const unsigned long long up = __shfl_up_sync(0xffffffffu, best[q], 1);
-          if (lane == pos) best[q] = kin;
-          else if (lane > pos) best[q] = up;
-          thr = __shfl_sync(0xffffffffu, best[q], p.n_hard - 1);
+#pragma unroll
+      for (int e = 0; e < 4; ++e) {
+        const int cell = j0 + lane + 32 * e;
+        // cosine with the positive; cells closer than the radius are not candidates (:497-503)
+        const float sim = __fdiv_rn(__fadd_rn(acc[q][e].x, acc[q][e].y), __fmul_rn(nf[e], np_));
+        const float dx = __fsub_rn(cxf[e], pxy.x), dy = __fsub_rn(cyf[e], pxy.y);
+        const float dist = __fsqrt_rn(__fadd_rn(__fmul_rn(dx, dx), __fmul_rn(dy, dy)));
+        const bool cand = row_ok && cell < HW && dist >= p.radius && sim == sim;
+        const unsigned long long key =
+            cand ? (((unsigned long long)orderable(sim) << 32) | (unsigned long long)(0xFFFFFFFFu - (unsigned)cell)) : 0ull;
+        unsigned m = __ballot_sync(0xffffffffu, key > thr);
+        while (m) {
+          const int src = __ffs(m) - 1;
+          m &= m - 1;
+          const unsigned long long kin = __shfl_sync(0xffffffffu, key, src);
+          if (kin > thr) {  // warp-uniform
+            const int at = __popc(__ballot_sync(0xffffffffu, best[q] > kin && lane < p.n_hard));
+            const unsigned long long up = __shfl_up_sync(0xffffffffu, best[q], 1);
+            if (lane == at) best[q] = kin;
+            else if (lane > at) best[q] = up;
+            thr = __shfl_sync(0xffffffffu, best[q], p.n_hard - 1);
+          }
         }
       }
     }
   }
 #pragma unroll
-  for (int q = 0; q < 4; ++q) {
-    const int k = k0 + 4 * warp + q;
-    if (k >= p.K) continue;
+  for (int q = 0; q < kHnRowsW; ++q) {
+    const int k = k0 + kHnRowsW * warp + q;
+    if (k >= p.K) continue;  // warp-uniform
     const bool have = lane < p.n_hard && best[q] != 0ull;
     if (lane < p.n_hard)
       p.idx[((size_t)b * p.K + k) * p.n_hard + lane] = have ? (int)(0xFFFFFFFFu - (unsigned)(best[q] & 0xFFFFFFFFull)) : -1;
@@ -415,17 +462,10 @@ cudaError_t launch_topk_rows(const TopkParams& p, cudaStream_t stream) {
   return launch_pdl(topk_rows_kernel, dim3(p.n_rows), dim3(kTopkThreads), smem, stream, p);
 }
 
-int hard_negatives_smem_bytes(int C) {
-  return (kHnRows * C + kHnChunk * (kHnCells + 1)) * (int)sizeof(float);
-}
-
 cudaError_t launch_hard_negatives(const HardNegParams& p, cudaStream_t stream) {
   if (p.B <= 0 || p.K <= 0) return cudaSuccess;
-  const int smem = hard_negatives_smem_bytes(p.C);
-  static SmemOptIn opt_in;
-  if (cudaError_t e = ensure_dynamic_smem(hard_negatives_kernel, smem, opt_in); e != cudaSuccess) return e;
   const int tiles_k = (p.K + kHnRows - 1) / kHnRows;
-  return launch_pdl(hard_negatives_kernel, dim3(p.B * tiles_k), dim3(kHnThreads), smem, stream, p);
+  return launch_pdl(hard_negatives_kernel, dim3(p.B * tiles_k), dim3(kHnThreads), 0, stream, p);
 }
 
 cudaError_t launch_nchw_to_tokens(const float* in, float* out, int B, int C, int HW, cudaStream_t stream) {

@@ -50,7 +50,6 @@ struct HardNegParams {
   int32_t* idx;           // out [B, K, n_hard] cell indices by similarity descending, -1 padded
   int32_t* counts;        // out [B, K]
 };
-int hard_negatives_smem_bytes(int C);
 cudaError_t launch_hard_negatives(const HardNegParams& p, cudaStream_t stream);
 
 cudaError_t launch_nchw_to_tokens(const float* in, float* out, int B, int C, int HW, cudaStream_t stream);

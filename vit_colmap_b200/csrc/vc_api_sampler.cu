@@ -96,7 +96,6 @@ int vc_hard_negatives(vc_handle* h, const float* tokens, const float* pos_feat, 
   if ((reinterpret_cast<uintptr_t>(pos_feat) & 15) != 0 || (reinterpret_cast<uintptr_t>(pos_xy) & 7) != 0)
     return fail(VC_ERR_INVALID, "pos_feat must be 16-byte and pos_xy 8-byte aligned");
   if (n_pos <= 0 || n_hard <= 0 || n_hard > 32) return fail(VC_ERR_INVALID, "bad n_pos=%d / n_hard=%d (1..32)", n_pos, n_hard);
-  if (vc::hard_negatives_smem_bytes(channels) > 227 * 1024) return fail(VC_ERR_INVALID, "positive tile does not fit in shared memory");
   VC_CUDA(cudaSetDevice(h->device));
   vc::HardNegParams p{};
   p.tokens = tokens;
