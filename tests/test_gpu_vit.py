@@ -211,6 +211,12 @@ def test_forward_fused_layernorm_equals_separate_launches(monkeypatch):
     separate = net.forward_patch_tokens(img).clone()
     monkeypatch.setenv("VC_VIT_FUSED_LN", "1")
     fused = net.forward_patch_tokens(img).clone()
+    # third placement: a LayerNorm kernel that follows the residual GEMM's row blocks while the GEMM still runs
+    # (VC_VIT_LN=follow, programmatic dependent launch + per-block counters; also measured slower)
+    monkeypatch.delenv("VC_VIT_FUSED_LN")
+    monkeypatch.setenv("VC_VIT_LN", "follow")
+    follow = [net.forward_patch_tokens(img).clone() for _ in range(2)]   # twice: the counters must come back to zero
     torch.cuda.synchronize()
     net.close()
     assert torch.equal(fused, separate) and torch.isfinite(fused).all()
+    assert torch.equal(follow[0], separate) and torch.equal(follow[1], separate)

@@ -59,14 +59,14 @@ struct VitWs {
   __nv_bfloat16* y;        // [B*T, C] LayerNorm-1 output / attention output
   __nv_bfloat16* y2;       // [B*T, C] LayerNorm-2 output (written by the proj GEMM while it still reads y)
   __nv_bfloat16* wide;     // [B*T, 4C] qkv (3C) / MLP hidden (4C) / patch rows (kpad)
-  int* counters;           // [ceil(B*T / 128)] row-block counters of the fused LayerNorm epilogue
+  int* counters;           // [2 * ceil(B*T / 128)] row-block counters (tiles stored | units normalised)
 };
 
 size_t ws_bytes(int B, int T, int C, VitWs* out, void* base) {
   const size_t rows = (size_t)B * T;
   const size_t bx = vc::align_up(rows * C * 4, 1024), by = vc::align_up(rows * C * 2, 1024);
   const size_t bw = vc::align_up(rows * (size_t)(4 * C > 640 ? 4 * C : 640) * 2, 1024);
-  const size_t bc = vc::align_up(((rows + 127) / 128) * sizeof(int), 1024);
+  const size_t bc = vc::align_up(2 * ((rows + 127) / 128) * sizeof(int), 1024);
   if (out) {
     uint8_t* p = static_cast<uint8_t*>(base);
     out->x = reinterpret_cast<float*>(p);
@@ -213,9 +213,18 @@ int vc_vit_forward(vc_handle* h, const vc_vit_weights* w, const uint8_t* images,
   // epilogue of its proj GEMM (into y2: the GEMM still reads its A operand from y) and LN1 of block l + 1 in
   // the epilogue of block l's fc2 GEMM (into y) -- bit-identical tokens, but measured SLOWER (13.95 vs
   // 11.96 ms per 32 images, see vit_gemm.cu), so it is not the default.
+  // VC_VIT_LN=follow: the residual GEMM publishes its row blocks and a small LayerNorm kernel launched right
+  // behind it (programmatic dependent launch) normalises them out of L2 while the GEMM runs -- bit-identical,
+  // measured SLOWER (12.9 vs 11.9 ms per 32 images: next to the GEMM's 384 x 144 registers only 4 warps of
+  // LayerNorm fit on an SM, a third of the stand-alone kernel's speed), so not the default.
   const char* fused_env = getenv("VC_VIT_FUSED_LN");
   const bool fused_ln = fused_env && fused_env[0] == '1';
-  VC_CUDA(cudaMemsetAsync(ws.counters, 0, ((size_t)rows + 127) / 128 * sizeof(int), s));
+  const char* ln_env = getenv("VC_VIT_LN");
+  const bool follow_ln = !fused_ln && ln_env && ln_env[0] == 'f';
+  const int n_blocks = (rows + 127) / 128;
+  int* done = ws.counters + n_blocks;
+  const int tiles_c = (C + 255) / 256;
+  VC_CUDA(cudaMemsetAsync(ws.counters, 0, (size_t)2 * n_blocks * sizeof(int), s));
   VC_CUDA(vc::launch_layernorm_bf16(ws.x, w->blocks[0].ln1_w, w->blocks[0].ln1_b, ws.y, rows, C, s));
   vc::add_launches(1);
   for (int l = 0; l < w->depth; ++l) {
@@ -237,7 +246,7 @@ int vc_vit_forward(vc_handle* h, const vc_vit_weights* w, const uint8_t* images,
     VC_CUDA(vc::launch_attention(map_qkv, ap, s));
     vc::add_launches(1);
     p = vc::GemmParams{};
-    p.epilogue = fused_ln ? vc::kEpiResidualLnF32 : vc::kEpiResidualF32;
+    p.epilogue = fused_ln ? vc::kEpiResidualLnF32 : (follow_ln ? vc::kEpiResidualPublishF32 : vc::kEpiResidualF32);
     p.bias = b.proj_b;
     p.gamma = b.ls1;
     p.out = ws.x;
@@ -248,7 +257,11 @@ int vc_vit_forward(vc_handle* h, const vc_vit_weights* w, const uint8_t* images,
     p.tile_counters = ws.counters;
     rc = run_linear(h, ws.y, b.proj_w, rows, C, C, p, s);
     if (rc != VC_OK) return rc;
-    if (!fused_ln) {
+    if (follow_ln) {
+      VC_CUDA(vc::launch_layernorm_follow(ws.x, b.ln2_w, b.ln2_b, ws.y2, rows, C, tiles_c, ws.counters, done,
+                                          h->num_sms, s));
+      vc::add_launches(1);
+    } else if (!fused_ln) {
       VC_CUDA(vc::launch_layernorm_bf16(ws.x, b.ln2_w, b.ln2_b, ws.y2, rows, C, s));
       vc::add_launches(1);
     }
@@ -260,7 +273,8 @@ int vc_vit_forward(vc_handle* h, const vc_vit_weights* w, const uint8_t* images,
     rc = run_linear(h, ws.y2, b.fc1_w, rows, 4 * C, C, p, s);
     if (rc != VC_OK) return rc;
     p = vc::GemmParams{};
-    p.epilogue = (fused_ln && !last) ? vc::kEpiResidualLnF32 : vc::kEpiResidualF32;
+    p.epilogue = (fused_ln && !last) ? vc::kEpiResidualLnF32
+                                     : ((follow_ln && !last) ? vc::kEpiResidualPublishF32 : vc::kEpiResidualF32);
     p.bias = b.fc2_b;
     p.gamma = b.ls2;
     p.out = ws.x;
@@ -273,7 +287,11 @@ int vc_vit_forward(vc_handle* h, const vc_vit_weights* w, const uint8_t* images,
       }
     rc = run_linear(h, ws.wide, b.fc2_w, rows, C, 4 * C, p, s);
     if (rc != VC_OK) return rc;
-    if (!fused_ln && !last) {
+    if (follow_ln && !last) {
+      VC_CUDA(vc::launch_layernorm_follow(ws.x, w->blocks[l + 1].ln1_w, w->blocks[l + 1].ln1_b, ws.y, rows, C, tiles_c,
+                                          ws.counters, done, h->num_sms, s));
+      vc::add_launches(1);
+    } else if (!fused_ln && !last) {
       VC_CUDA(vc::launch_layernorm_bf16(ws.x, w->blocks[l + 1].ln1_w, w->blocks[l + 1].ln1_b, ws.y, rows, C, s));
       vc::add_launches(1);
     }

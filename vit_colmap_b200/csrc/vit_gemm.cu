@@ -43,7 +43,9 @@ constexpr int kThreads = 384;
 constexpr int kTmemCols = 512;
 constexpr int kStageOutBytes = 32 * 128;  // per epilogue warp: 32 rows x 128 B transposition buffer
 constexpr int kSmemBytes = kStages * kStageBytes + 1024 + 256 + 8 * kStageOutBytes;
-constexpr bool is_residual(int epi) { return epi == kEpiResidualF32 || epi == kEpiResidualLnF32; }
+constexpr bool is_residual(int epi) {
+  return epi == kEpiResidualF32 || epi == kEpiResidualLnF32 || epi == kEpiResidualPublishF32;
+}
 
 __device__ __forceinline__ float warp_sum(float v) {
 #pragma unroll
@@ -107,9 +109,7 @@ __device__ __forceinline__ void ln_rows_bf16(const float* __restrict__ x, size_t
 }
 
 template <int EPI>
-__global__ void __launch_bounds__(kThreads, 1)
-vit_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_w,
-                const GemmParams p) {
+__device__ __forceinline__ void gemm_body(const CUtensorMap& map_a, const CUtensorMap& map_w, const GemmParams& p) {
   extern __shared__ uint8_t smem_raw[];
   const uint32_t raw_addr = smem_u32(smem_raw);
   const uint32_t base = (raw_addr + 1023u) & ~1023u;
@@ -156,6 +156,8 @@ vit_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant
   // everything above overlaps the previous kernel's tail; operands and the residual stream are only
   // touched below
   griddep_wait();
+  // the row-block consumer (launch_layernorm_follow) is the next kernel of the stream: let it become resident now
+  if (EPI == kEpiResidualPublishF32) asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
 
   if (warp == 0 && lane == 0) {
     uint32_t stage = 0, phase = 0;
@@ -203,12 +205,20 @@ vit_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant
     uint8_t* stg_row = stg + lane * 128;           // row layout: thread = row
     const int tc = lane & 7, tr = lane >> 3;        // transposed layout: 8 lanes per row, rows tr + 4 i
     uint32_t it = 0;
+    int pending_tm = -1;
     for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x, ++it) {
       const int tm = tile / tiles_n, tn = tile - tm * tiles_n;
       const int row0 = tm * BM + q * 32;
       const uint32_t as = it & 1, aph = (it >> 1) & 1;
       mbar_wait_sleep(tfull_bar(as), aph, 32);
       tc_fence_after();
+      if (EPI == kEpiResidualPublishF32 && pending_tm >= 0) {
+        // the previous tile's rows left this warp a whole main loop ago: the fence returns at once.  Every
+        // epilogue warp counts for itself (8 per tile), so no CTA-wide barrier is needed.
+        __threadfence();
+        if (lane == 0) atomicAdd(p.tile_counters + pending_tm, 1);
+        pending_tm = -1;
+      }
       const uint32_t t_addr = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + as * BN + h * 128;
       bool released = false;
       if (EPI == kEpiBiasBf16 || EPI == kEpiBiasGeluBf16) {
@@ -340,6 +350,7 @@ vit_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant
         tc_fence_before();
         mbar_arrive(tempty_bar(as));
       }
+      if (EPI == kEpiResidualPublishF32) pending_tm = tm;  // published one tile later, when the fence is free
       if (EPI == kEpiResidualLnF32) {
         // tile stored: publish it; the CTA holding the block's last column tile normalises the block
         __threadfence();                                          // this thread's stores, device-wide
@@ -366,11 +377,59 @@ vit_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant
         }
       }
     }
+    if (EPI == kEpiResidualPublishF32 && pending_tm >= 0) {  // the CTA's last tile
+      __threadfence();
+      if (lane == 0) atomicAdd(p.tile_counters + pending_tm, 1);
+    }
   }
 
   tc_fence_before();
   __syncthreads();
   if (warp == 2) tmem_dealloc(tmem_base, kTmemCols);
+}
+
+template <int EPI>
+__global__ void __launch_bounds__(kThreads, 1)
+vit_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_w,
+                const GemmParams p) {
+  gemm_body<EPI>(map_a, map_w, p);
+}
+// The publishing form shares its SM with one CTA of layernorm_follow_kernel (128 threads x 80 registers):
+// 384 x 144 + 128 x 80 registers fit the 64 K register file, 384 x 152 (what ptxas picks unconstrained) do not.
+__global__ void __maxnreg__(144)
+vit_gemm_publish_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_w,
+                        const GemmParams p) {
+  gemm_body<kEpiResidualPublishF32>(map_a, map_w, p);
+}
+
+// Row-block consumer of a kEpiResidualPublishF32 GEMM (see vit_kernels.cuh).  Small on purpose: 128 threads and
+// 80 registers, so that one CTA fits on an SM next to the GEMM's CTA (384 threads x 144 registers).  A unit is
+// 32 rows (a quarter of a row block): after the GEMM's last round 148 CTAs share the ~50 blocks that are left.
+// It must NOT wait for the producer grid at its start -- the counters are the dependency -- and does so at its
+// end, which orders every later kernel of the stream after the GEMM as well.
+template <int KV, int RIF>
+__global__ void __launch_bounds__(128, 6)
+layernorm_follow_kernel(const float* __restrict__ x, const float* __restrict__ w, const float* __restrict__ b,
+                        __nv_bfloat16* __restrict__ out, int rows, int C, int tiles_n, int* counters, int* done) {
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int units = ((rows + BM - 1) / BM) * 4;
+  for (int u = blockIdx.x; u < units; u += gridDim.x) {
+    const int tm = u >> 2, row0 = tm * BM + (u & 3) * 32;
+    if (threadIdx.x == 0) {
+      volatile int* cnt = counters + tm;
+      while (*cnt < 8 * tiles_n) __nanosleep(128);  // eight epilogue warps count each tile
+    }
+    __syncthreads();
+    __threadfence();  // order the row reads after the counter
+    const int n_rows = min(32, rows - row0);
+    if (n_rows > 0) ln_rows_bf16<KV, RIF>(x + (size_t)row0 * C, C, w, b, out + (size_t)row0 * C, C, warp, 4, n_rows, lane);
+    __syncthreads();
+    if (threadIdx.x == 0 && atomicAdd(done + tm, 1) == 3) {  // the block's last unit leaves both counters zero
+      done[tm] = 0;
+      counters[tm] = 0;
+    }
+  }
+  griddep_wait();
 }
 
 template <int EPI>
@@ -385,6 +444,17 @@ cudaError_t launch_one(const CUtensorMap& map_a, const CUtensorMap& map_w, const
 
 int gemm_smem_bytes() { return kSmemBytes; }
 
+cudaError_t launch_layernorm_follow(const float* x, const float* w, const float* b, __nv_bfloat16* out, int rows,
+                                    int C, int tiles_n, int* counters, int* done, int num_sms, cudaStream_t stream) {
+  if (rows <= 0) return cudaSuccess;
+  if (C % 4 != 0 || C > 1024 || !counters || !done) return cudaErrorInvalidValue;
+  const int units = ((rows + BM - 1) / BM) * 4;
+  const dim3 grid(units < num_sms ? units : num_sms), block(128);
+  if (C <= 384) return launch_pdl(layernorm_follow_kernel<3, 4>, grid, block, 0, stream, x, w, b, out, rows, C, tiles_n, counters, done);
+  if (C <= 768) return launch_pdl(layernorm_follow_kernel<6, 2>, grid, block, 0, stream, x, w, b, out, rows, C, tiles_n, counters, done);
+  return launch_pdl(layernorm_follow_kernel<8, 1>, grid, block, 0, stream, x, w, b, out, rows, C, tiles_n, counters, done);
+}
+
 cudaError_t launch_gemm(const CUtensorMap& map_a, const CUtensorMap& map_w, const GemmParams& p,
                         int num_sms, cudaStream_t stream) {
   if (p.M <= 0 || p.N <= 0) return cudaSuccess;
@@ -396,6 +466,12 @@ cudaError_t launch_gemm(const CUtensorMap& map_a, const CUtensorMap& map_w, cons
     case kEpiBiasGeluBf16: return launch_one<kEpiBiasGeluBf16>(map_a, map_w, p, grid, stream);
     case kEpiResidualF32: return launch_one<kEpiResidualF32>(map_a, map_w, p, grid, stream);
     case kEpiPatchEmbed: return launch_one<kEpiPatchEmbed>(map_a, map_w, p, grid, stream);
+    case kEpiResidualPublishF32: {
+      if (!p.tile_counters) return cudaErrorInvalidValue;
+      static SmemOptIn opt_in;
+      if (cudaError_t e = ensure_dynamic_smem(vit_gemm_publish_kernel, kSmemBytes, opt_in); e != cudaSuccess) return e;
+      return launch_pdl(vit_gemm_publish_kernel, dim3(grid), dim3(kThreads), kSmemBytes, stream, map_a, map_w, p);
+    }
     case kEpiResidualLnF32:
       if (!p.ln_w || !p.ln_b || !p.ln_out || !p.tile_counters || p.N != p.ldo || p.N > 1024 || p.N % 4 != 0)
         return cudaErrorInvalidValue;

@@ -18,7 +18,11 @@ enum GemmEpilogue {
   // kEpiResidualF32 followed, in the same kernel, by the LayerNorm of the rows it has completed: the CTA
   // that stores the LAST column tile of a 128-row block (per-block counter) normalises those rows straight
   // out of L2 and writes the bf16 operand of the next GEMM.  N must be the full row (N == ldo <= 1024).
-  kEpiResidualLnF32 = 4
+  kEpiResidualLnF32 = 4,
+  // kEpiResidualF32 whose eight epilogue warps each bump the counter of a tile's 128-row block once their part of
+  // the tile is visible device-wide (one tile late, when the fence costs nothing), and lets the next kernel of the stream start early (programmatic dependent launch): that
+  // kernel is launch_layernorm_follow, which normalises row blocks WHILE this GEMM is still running.
+  kEpiResidualPublishF32 = 5
 };
 
 struct GemmParams {
@@ -37,6 +41,13 @@ struct GemmParams {
   int* tile_counters;     // [ceil(M / 128)] zero before the launch; the kernel leaves them zero
 };
 int gemm_smem_bytes();
+// LayerNorm (f32 [rows, C] -> bf16) of the rows a kEpiResidualPublishF32 GEMM with `tiles_n` column tiles is
+// producing: launched right after that GEMM on the same stream, runs next to it (one small CTA per SM), takes
+// each 32-row unit as soon as the unit's 128-row block has been counted 8 * `tiles_n` times, reads it out of L2.
+// Same arithmetic as launch_layernorm_bf16 (bit-identical).  counters / done: [ceil(rows / 128)] ints each, zero
+// before the GEMM's launch; left zero.
+cudaError_t launch_layernorm_follow(const float* x, const float* w, const float* b, __nv_bfloat16* out, int rows,
+                                    int C, int tiles_n, int* counters, int* done, int num_sms, cudaStream_t stream);
 cudaError_t launch_gemm(const CUtensorMap& map_a, const CUtensorMap& map_w, const GemmParams& p,
                         int num_sms, cudaStream_t stream);
 
