@@ -54,6 +54,34 @@ def test_linear_matches_fp32_reference(lib_handle, shape, epilogue):
     assert err.max().item() <= tol, (err.max().item(), scale)
 
 
+@pytest.mark.parametrize("shape", [(1370, 2304, 768), (129, 768, 768), (257, 384, 768), (1, 3072, 768),
+                                   (5000, 768, 3072), (640, 1152, 1024)])
+@pytest.mark.parametrize("epilogue", [0, 1, 2])
+def test_two_sm_linear_equals_one_sm(lib_handle, monkeypatch, shape, epilogue):
+    """The cta_group::2 GEMM (vit_gemm2.cu, default for K >= 768) and the one-SM GEMM (VC_VIT_2CTA=0) share the
+    per-tile epilogue and the order of accumulation: identical outputs, bit for bit -- also when the second CTA
+    of a pair has one valid row (M = 129), none (M = 1), or a half-empty column tile (N = 384, 1152)."""
+    import torch
+    from vit_colmap_b200 import _lib
+    lib, h = lib_handle
+    m, n, k = shape
+    g = torch.Generator(device="cuda").manual_seed(m + n + k + epilogue)
+    a = torch.randn((m, k), generator=g, device="cuda").to(torch.bfloat16)
+    w = (torch.randn((n, k), generator=g, device="cuda") * 0.05).to(torch.bfloat16)
+    bias = torch.randn((n,), generator=g, device="cuda")
+    gamma = torch.randn((n,), generator=g, device="cuda")
+    x0 = torch.randn((m, n), generator=g, device="cuda")
+    outs = []
+    for env in ("1", "0"):
+        monkeypatch.setenv("VC_VIT_2CTA", env)
+        out = x0.clone() if epilogue == 2 else torch.full((m, n), float("nan"), dtype=torch.bfloat16, device="cuda")
+        _lib.check(lib.vc_vit_linear(h, a.data_ptr(), w.data_ptr(), bias.data_ptr(), gamma.data_ptr(), m, n, k,
+                                     epilogue, out.data_ptr(), _stream()))
+        outs.append(out)
+    torch.cuda.synchronize()
+    assert torch.isfinite(outs[0].float()).all() and torch.equal(outs[0], outs[1])
+
+
 @pytest.mark.parametrize("rows,C", [(1370, 768), (77, 384), (513, 1024)])
 def test_layernorm_matches_torch(lib_handle, rows, C):
     import torch

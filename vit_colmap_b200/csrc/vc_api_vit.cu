@@ -41,15 +41,23 @@ int make_map_qkv(vc_handle* h, CUtensorMap* map, const void* ptr, int B, int T, 
 
 int run_linear(vc_handle* h, const void* a, const void* w, int m, int n, int k, vc::GemmParams p,
                cudaStream_t s) {
+  // VC_VIT_2CTA=0 keeps every GEMM on the one-SM kernel (default: the two-SM kernel, vit_gemm2.cu, where it exists)
+  const char* env_2cta = getenv("VC_VIT_2CTA");
+  const bool two_sm_on = !(env_2cta && env_2cta[0] == '0');
+  // K < 768 (ViT-S): six k-steps per tile do not pay for the cluster's hand-over latency (measured 1 % slower)
+  const bool two_sm = two_sm_on && vc::gemm2_supports(p.epilogue) && k >= 768;
   CUtensorMap ma, mw;
   int rc = make_map_2d(h, &ma, a, (uint64_t)m, (uint64_t)k, 128);
   if (rc != VC_OK) return rc;
-  rc = make_map_2d(h, &mw, w, (uint64_t)n, (uint64_t)k, 256);
+  rc = make_map_2d(h, &mw, w, (uint64_t)n, (uint64_t)k, two_sm ? 128 : 256);
   if (rc != VC_OK) return rc;
   p.M = m;
   p.N = n;
   p.K = k;
-  VC_CUDA(vc::launch_gemm(ma, mw, p, h->num_sms, s));
+  if (two_sm)
+    VC_CUDA(vc::launch_gemm2(ma, mw, p, h->num_sms, s));
+  else
+    VC_CUDA(vc::launch_gemm(ma, mw, p, h->num_sms, s));
   vc::add_launches(1);
   return VC_OK;
 }

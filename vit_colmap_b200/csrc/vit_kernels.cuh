@@ -41,6 +41,11 @@ struct GemmParams {
   int* tile_counters;     // [ceil(M / 128)] zero before the launch; the kernel leaves them zero
 };
 int gemm_smem_bytes();
+// Two-SM (cta_group::2) form, vit_gemm2.cu: a cluster of two CTAs per 256 x 256 tile.  Same results bit for bit.
+// map_w must be built with a {64, 128} box (each CTA stages half of the 256 weight rows).
+bool gemm2_supports(int epilogue);
+cudaError_t launch_gemm2(const CUtensorMap& map_a, const CUtensorMap& map_w, const GemmParams& p,
+                         int num_sms, cudaStream_t stream);
 // LayerNorm (f32 [rows, C] -> bf16) of the rows a kEpiResidualPublishF32 GEMM with `tiles_n` column tiles is
 // producing: launched right after that GEMM on the same stream, runs next to it (one small CTA per SM), takes
 // each 32-row unit as soon as the unit's 128-row block has been counted 8 * `tiles_n` times, reads it out of L2.
