@@ -1,6 +1,9 @@
 """Aggregate the per-instruction stall samples of an ncu report by CUDA source line.
 
-    python tools/ncu_hot_lines.py gpurun_out/prof.ncu-rep vit_colmap_b200/build/match_fused2.o match_fused2_kernel [top]
+    python tools/ncu_hot_lines.py gpurun_out/prof.ncu-rep vit_colmap_b200/build/match_fused2.o match_fused2_kernel [top] [mangled]
+
+(`mangled`: substring of the kernel's section name in the cubin when it differs from the demangled name in the
+report, e.g. "vit_gemm2_kernel<(int)0>" and "vit_gemm2_kernelILi0".)
 
 ncu's `--page source --csv` lists SASS instructions with their sample counts but no source line; the
 line table comes from `nvdisasm -g` on the cubin of the object file built with -lineinfo.  The n-th
@@ -44,6 +47,7 @@ def sass_lines(obj: Path, kernel: str):
 def main():
     rep, obj, kernel = sys.argv[1], Path(sys.argv[2]), sys.argv[3]
     top = int(sys.argv[4]) if len(sys.argv) > 4 else 25
+    mangled = sys.argv[5] if len(sys.argv) > 5 else kernel
     raw = subprocess.run(["ncu", "-i", rep, "--page", "source", "--csv"], check=True, capture_output=True, text=True).stdout
     rows = list(csv.reader(io.StringIO(raw)))
     start = next(i for i, r in enumerate(rows) if r and r[0] == "Kernel Name" and kernel in r[1])
@@ -53,7 +57,7 @@ def main():
         if not r or r[0] == "Kernel Name":
             break
         body.append(r)
-    table = sass_lines(obj, kernel)
+    table = sass_lines(obj, mangled)
     if len(table) != len(body):
         print(f"warning: {len(body)} instructions in the report, {len(table)} in the cubin", file=sys.stderr)
     i_s, i_ns, i_ex = hdr.index("# Samples"), hdr.index("Warp Stall Sampling (Not-issued Samples)"), hdr.index("Instructions Executed")
