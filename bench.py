@@ -459,7 +459,9 @@ def run_extract(args, torch, dist, dev, local, world):
 
     for _ in range(max(args.warmup, 3)):
         out = step()
-    ms = timed(step, args.steps)
+    # three windows of K steps, median: this section starts right after the matcher has held the board at its
+    # power cap, and a single 120 ms window then swings by +- 8 % with the clock recovery
+    ms = sorted(timed(step, args.steps) for _ in range(3))[1]
     ms_fwd = timed(forward_only, max(2, min(args.steps, 5))) / max(2, min(args.steps, 5))
     # end to end: host uint8 images in, host keypoints + descriptors out (public extractor API)
     list(ex.extract_batches([(host, wh, wh, None)] * 4))  # warm-up: allocator pools for two batches in flight
@@ -485,6 +487,7 @@ def run_extract(args, torch, dist, dev, local, world):
         "config": {"workload": f"{EXTRACT_MODEL} forward + harris score + bin/NMS selection + PCA {EXTRACT_DIM}-d "
                                f"descriptors, batch {EXTRACT_BATCH} x {EXTRACT_SIZE}x{EXTRACT_SIZE} per GPU per step",
                    "mean_keypoints_per_image": float(out.counts.float().mean().item()),
+                   "timing": "median of three windows of K steps (CUDA events, max over ranks)",
                    "l2": "activations (134 MB residual stream, 269 MB qkv/MLP per batch) exceed the 126 MB L2"},
         "e2e": {"value": world * EXTRACT_BATCH * n_e2e / float(dt.item()), "unit": "images/s",
                 "h2d_bytes_per_step": int(imgs.numel()), "d2h_bytes_per_step": kp_bytes,
