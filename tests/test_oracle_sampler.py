@@ -69,3 +69,24 @@ def test_positive_pairs_and_hard_negatives_match_reference(path):
             assert abs(float(v[idx[b, k, j]]) - float(kth)) <= TIE
     if path.stem.endswith("wide_radius"):   # fewer cells than n_hard qualify somewhere: zero-padded rows
         assert (np.abs(ref).max(axis=-1) == 0).any()
+
+
+def test_host_side_of_the_sampler_mirror():
+    """The product's TrainingSampler keeps O(B*K) bookkeeping on the host: the coordinate transform must equal the
+    reference arithmetic (oracle), and without a CUDA device every device method must fail loudly (no CPU path)."""
+    from vit_colmap_b200 import _lib
+    from vit_colmap_b200.dataloader import TrainingSampler
+    s = TrainingSampler(patch_size=14)
+    rng = np.random.default_rng(3)
+    coords = torch.from_numpy(rng.uniform(0, 36, (2, 50, 2)).astype(np.float32))
+    _, _, H, _ = so.synthetic_pair(5, 2, 4, 37, 37)
+    for feature_space in (True, False):
+        got = s.transform_coords_with_homography(coords, H, from_feature_space=feature_space,
+                                                 feature_size=(37, 37) if feature_space else None)
+        ref = so.transform_coords(coords, H, 14, feature_space)
+        assert got.dtype == torch.float32 and np.abs(got.numpy() - ref.numpy()).max() < 1e-4
+    if not torch.cuda.is_available():
+        with pytest.raises(_lib.VcError):
+            s.sample_features_at_coords(torch.zeros(1, 8, 4, 4), torch.zeros(1, 3, 2))
+        with pytest.raises(_lib.VcError):
+            s.select_invariant_points(torch.zeros(1, 8, 4, 4), torch.zeros(1, 8, 4, 4), torch.eye(3)[None], (56, 56))
