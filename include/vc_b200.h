@@ -297,6 +297,13 @@ typedef struct {
   const void* fc2_w;   /* bf16 [C, 4C] */
   const float* fc2_b;
   const float* ls2;
+  /* Optional (all six or none, NULL otherwise): LayerNorm folded into the GEMMs around it (VC_VIT_LN=fold).
+   * qkv_wf = bf16(qkv_w * ln1_w) [3C, C], qkv_cs[n] = sum_k qkv_wf[n, k] (f32), qkv_bf = qkv_b + qkv_w ln1_b (f32);
+   * fc1_* likewise with ln2.  Built by vit_colmap_b200/vit.py from the same state dict. */
+  const void* qkv_wf;
+  const float *qkv_cs, *qkv_bf;
+  const void* fc1_wf;
+  const float *fc1_cs, *fc1_bf;
 } vc_vit_block;
 
 typedef struct {

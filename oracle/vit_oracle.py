@@ -101,11 +101,26 @@ def _r(t: torch.Tensor, emulate: bool) -> torch.Tensor:
     return t.to(torch.bfloat16).float() if emulate else t
 
 
-def forward_features(sd: Dict[str, torch.Tensor], x: torch.Tensor, heads: int, emulate_bf16: bool = False,
+def _folded_linear(t: torch.Tensor, W: torch.Tensor, b: torch.Tensor, ln_w: torch.Tensor, ln_b: torch.Tensor):
+    """LayerNorm (eps 1e-6) + Linear with the rounding points of the kernels' VC_VIT_LN=fold mode: the GEMM runs
+    on bf16(t) with weights bf16(W * ln_w); mean and 1/std of the fp32 rows (from sum x and sum x^2) are applied
+    after it: rstd * (acc - mean * colsum) + (b + W ln_b)."""
+    C = t.shape[-1]
+    wf = (W * ln_w[None, :]).to(torch.bfloat16).float()
+    acc = t.to(torch.bfloat16).float() @ wf.t()
+    mean = t.sum(dim=-1, keepdim=True) / C
+    var = ((t * t).sum(dim=-1, keepdim=True) / C - mean * mean).clamp(min=0)
+    rstd = torch.rsqrt(var + 1e-6)
+    return rstd * (acc - mean * wf.sum(dim=1)) + (b + W @ ln_b)
+
+
+def forward_features(sd: Dict[str, torch.Tensor], x: torch.Tensor, heads: int, emulate_bf16=False,
                      interpolate_offset: float = HUB_INTERPOLATE_OFFSET):
     """x: normalised f32 [B,3,14*gh,14*gw].  emulate_bf16 rounds every GEMM / attention operand to
-    bf16 at the points where the sm_100a kernels do (fp32 accumulation everywhere)."""
-    e = emulate_bf16
+    bf16 at the points where the sm_100a kernels do (fp32 accumulation everywhere); emulate_bf16="fold" does
+    so for the kernels' folded-LayerNorm mode (every LayerNorm but the first and the last: _folded_linear)."""
+    fold = emulate_bf16 == "fold"
+    e = bool(emulate_bf16)
     B, _, Hp, Wp = x.shape
     gh, gw = Hp // PATCH, Wp // PATCH
     C = sd["cls_token"].shape[-1]
@@ -121,8 +136,12 @@ def forward_features(sd: Dict[str, torch.Tensor], x: torch.Tensor, heads: int, e
     hd = C // heads
     for i in range(L):
         p = f"blocks.{i}."
-        y = F.layer_norm(t, (C,), sd[p + "norm1.weight"], sd[p + "norm1.bias"], eps=1e-6)
-        qkv = _r(_r(y, e) @ _r(sd[p + "attn.qkv.weight"], e).t() + sd[p + "attn.qkv.bias"], e)
+        if fold and i > 0:
+            qkv = _r(_folded_linear(t, sd[p + "attn.qkv.weight"], sd[p + "attn.qkv.bias"], sd[p + "norm1.weight"],
+                                    sd[p + "norm1.bias"]), e)
+        else:
+            y = F.layer_norm(t, (C,), sd[p + "norm1.weight"], sd[p + "norm1.bias"], eps=1e-6)
+            qkv = _r(_r(y, e) @ _r(sd[p + "attn.qkv.weight"], e).t() + sd[p + "attn.qkv.bias"], e)
         q, k, v = qkv.reshape(B, -1, 3, heads, hd).permute(2, 0, 3, 1, 4)           # [B, h, T, hd]
         s = (q @ k.transpose(-1, -2)) / math.sqrt(hd)
         if e:  # the kernel rounds un-normalised probabilities to bf16 and divides by the fp32 sum
@@ -133,8 +152,12 @@ def forward_features(sd: Dict[str, torch.Tensor], x: torch.Tensor, heads: int, e
         a = _r(a.transpose(1, 2).reshape(B, -1, C), e)
         y = a @ _r(sd[p + "attn.proj.weight"], e).t() + sd[p + "attn.proj.bias"]
         t = t + sd[p + "ls1.gamma"] * y
-        y = F.layer_norm(t, (C,), sd[p + "norm2.weight"], sd[p + "norm2.bias"], eps=1e-6)
-        hdn = F.gelu(_r(y, e) @ _r(sd[p + "mlp.fc1.weight"], e).t() + sd[p + "mlp.fc1.bias"])
+        if fold:
+            hdn = F.gelu(_folded_linear(t, sd[p + "mlp.fc1.weight"], sd[p + "mlp.fc1.bias"], sd[p + "norm2.weight"],
+                                        sd[p + "norm2.bias"]))
+        else:
+            y = F.layer_norm(t, (C,), sd[p + "norm2.weight"], sd[p + "norm2.bias"], eps=1e-6)
+            hdn = F.gelu(_r(y, e) @ _r(sd[p + "mlp.fc1.weight"], e).t() + sd[p + "mlp.fc1.bias"])
         y = _r(hdn, e) @ _r(sd[p + "mlp.fc2.weight"], e).t() + sd[p + "mlp.fc2.bias"]
         t = t + sd[p + "ls2.gamma"] * y
     out = F.layer_norm(t, (C,), sd["norm.weight"], sd["norm.bias"], eps=1e-6)

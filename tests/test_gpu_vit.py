@@ -149,6 +149,41 @@ def test_forward_matches_oracle(name, size, depth, B):
     assert cos.min().item() > 1 - 1e-4, cos.min().item()
 
 
+@pytest.mark.parametrize("name,size,depth,B", [("dinov2_vits14", (518, 518), 12, 2), ("dinov2_vitb14", (518, 518), 3, 3),
+                                                ("dinov2_vitb14", (588, 798), 2, 1), ("dinov2_vitl14", (224, 224), 3, 1)])
+def test_forward_with_folded_layernorm(monkeypatch, name, size, depth, B):
+    """VC_VIT_LN=fold: every LayerNorm between the first and the last is folded into the GEMMs around it (the residual
+    GEMM stores bf16(x) and per-slice row sums; the next GEMM multiplies by W * ln_w and applies mean / rstd in its
+    epilogue).  The rounding points differ from the default mode's, so the yardstick is the oracle emulating THIS
+    mode; the criteria are those of test_forward_matches_oracle, and the distance to the fp32 oracle must not be
+    worse than the default mode's own."""
+    import torch
+    from oracle import vit_oracle as vo
+    from vit_colmap_b200.vit import VitBackbone
+    sd = vo.synthetic_state_dict(name, seed=5, depth=depth)
+    rng = np.random.default_rng(7)
+    img = torch.from_numpy(rng.integers(0, 256, (B, size[0], size[1], 3), dtype=np.uint8))
+    x = vo.preprocess(img)
+    heads = vo.CONFIGS[name][2]
+    ref = vo.forward_features(sd, x, heads, emulate_bf16="fold")["x_norm_patchtokens"]
+    ref32 = vo.forward_features(sd, x, heads)["x_norm_patchtokens"]
+    net = VitBackbone(sd, name, 0)
+    default = net.forward_patch_tokens(img.cuda()).cpu()
+    monkeypatch.setenv("VC_VIT_LN", "fold")
+    got = net.forward_patch_tokens(img.cuda()).cpu()
+    again = net.forward_patch_tokens(img.cuda()).cpu()
+    net.close()
+    assert torch.equal(got, again)                      # deterministic: no atomics in the row statistics
+    assert not torch.equal(got, default)                # the mode is really on
+    bf16_gap = (ref - ref32).abs()
+    err = (got - ref).abs()
+    cos = torch.nn.functional.cosine_similarity(got, ref, dim=-1)
+    assert err.mean().item() < 0.75 * bf16_gap.mean().item(), (err.mean().item(), bf16_gap.mean().item())
+    assert (got - ref32).abs().max().item() < 2.0 * bf16_gap.max().item()
+    assert cos.min().item() > 1 - 1e-4, cos.min().item()
+    assert (got - ref32).abs().mean().item() < 1.1 * (default - ref32).abs().mean().item()
+
+
 def test_forward_bgr_flag_swaps_channels():
     import torch
     from oracle import vit_oracle as vo

@@ -102,7 +102,8 @@ SIGNATURES = {
 class VitBlock(ctypes.Structure):
     """vc_vit_block (include/vc_b200.h)."""
     _fields_ = [(n, c_void_p) for n in ("ln1_w", "ln1_b", "qkv_w", "qkv_b", "proj_w", "proj_b", "ls1",
-                                        "ln2_w", "ln2_b", "fc1_w", "fc1_b", "fc2_w", "fc2_b", "ls2")]
+                                        "ln2_w", "ln2_b", "fc1_w", "fc1_b", "fc2_w", "fc2_b", "ls2",
+                                        "qkv_wf", "qkv_cs", "qkv_bf", "fc1_wf", "fc1_cs", "fc1_bf")]
 
 
 class VitWeights(ctypes.Structure):

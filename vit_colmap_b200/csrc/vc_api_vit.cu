@@ -4,6 +4,7 @@
 #include "vit_kernels.cuh"
 
 #include <cstdlib>
+#include <cstring>
 
 using vc::fail;
 
@@ -68,6 +69,7 @@ struct VitWs {
   __nv_bfloat16* y2;       // [B*T, C] LayerNorm-2 output (written by the proj GEMM while it still reads y)
   __nv_bfloat16* wide;     // [B*T, 4C] qkv (3C) / MLP hidden (4C) / patch rows (kpad)
   int* counters;           // [2 * ceil(B*T / 128)] row-block counters (tiles stored | units normalised)
+  float* part;             // [2][B*T, C / 128, 2] per-slice row sums of the folded LayerNorms (ln1 | ln2)
 };
 
 size_t ws_bytes(int B, int T, int C, VitWs* out, void* base) {
@@ -75,6 +77,7 @@ size_t ws_bytes(int B, int T, int C, VitWs* out, void* base) {
   const size_t bx = vc::align_up(rows * C * 4, 1024), by = vc::align_up(rows * C * 2, 1024);
   const size_t bw = vc::align_up(rows * (size_t)(4 * C > 640 ? 4 * C : 640) * 2, 1024);
   const size_t bc = vc::align_up(2 * ((rows + 127) / 128) * sizeof(int), 1024);
+  const size_t bp = vc::align_up(rows * (size_t)((C + 127) / 128) * 2 * sizeof(float), 1024);
   if (out) {
     uint8_t* p = static_cast<uint8_t*>(base);
     out->x = reinterpret_cast<float*>(p);
@@ -82,8 +85,9 @@ size_t ws_bytes(int B, int T, int C, VitWs* out, void* base) {
     out->y2 = reinterpret_cast<__nv_bfloat16*>(p + bx + by);
     out->wide = reinterpret_cast<__nv_bfloat16*>(p + bx + 2 * by);
     out->counters = reinterpret_cast<int*>(p + bx + 2 * by + bw);
+    out->part = reinterpret_cast<float*>(p + bx + 2 * by + bw + bc);
   }
-  return bx + 2 * by + bw + bc;
+  return bx + 2 * by + bw + bc + 2 * bp;
 }
 
 }  // namespace
@@ -228,7 +232,18 @@ int vc_vit_forward(vc_handle* h, const vc_vit_weights* w, const uint8_t* images,
   const char* fused_env = getenv("VC_VIT_FUSED_LN");
   const bool fused_ln = fused_env && fused_env[0] == '1';
   const char* ln_env = getenv("VC_VIT_LN");
-  const bool follow_ln = !fused_ln && ln_env && ln_env[0] == 'f';
+  const bool follow_ln = !fused_ln && ln_env && strcmp(ln_env, "follow") == 0;
+  // VC_VIT_LN=fold: no LayerNorm launches between the first and the last one -- the residual GEMMs store a bf16
+  // copy of the stream and per-slice row sums, the next GEMM runs on that copy with ln_w folded into its weights
+  // and applies mean / rstd in its epilogue (vit_kernels.cuh).  Needs the folded weights and C % 128 == 0.
+  bool fold_ln = !fused_ln && ln_env && strcmp(ln_env, "fold") == 0 && C % 128 == 0;
+  for (int l = 0; fold_ln && l < w->depth; ++l) {
+    const vc_vit_block& b = w->blocks[l];
+    fold_ln = b.qkv_wf && b.qkv_cs && b.qkv_bf && b.fc1_wf && b.fc1_cs && b.fc1_bf;
+  }
+  const int slices = C / 128;
+  float* part1 = ws.part;                                         // statistics of x before a block's LN1
+  float* part2 = ws.part + (size_t)rows * ((C + 127) / 128) * 2;  // ... before its LN2
   const int n_blocks = (rows + 127) / 128;
   int* done = ws.counters + n_blocks;
   const int tiles_c = (C + 255) / 256;
@@ -239,11 +254,15 @@ int vc_vit_forward(vc_handle* h, const vc_vit_weights* w, const uint8_t* images,
     const vc_vit_block& b = w->blocks[l];
     const bool last = l + 1 == w->depth;
     vc::GemmParams p{};
-    p.epilogue = vc::kEpiBiasBf16;
-    p.bias = b.qkv_b;
+    const bool fold_qkv = fold_ln && l > 0;  // block 0's LN1 follows the patch embedding: a plain launch
+    p.epilogue = fold_qkv ? vc::kEpiFoldBiasBf16 : vc::kEpiBiasBf16;
+    p.bias = fold_qkv ? b.qkv_bf : b.qkv_b;
+    p.ln_part = part1;
+    p.ln_slices = slices;
+    p.colsum = b.qkv_cs;
     p.out = ws.wide;
     p.ldo = 3 * C;
-    rc = run_linear(h, ws.y, b.qkv_w, rows, 3 * C, C, p, s);
+    rc = run_linear(h, ws.y, fold_qkv ? b.qkv_wf : b.qkv_w, rows, 3 * C, C, p, s);
     if (rc != VC_OK) return rc;
     vc::AttnParams ap{};
     ap.B = n_images;
@@ -255,6 +274,9 @@ int vc_vit_forward(vc_handle* h, const vc_vit_weights* w, const uint8_t* images,
     vc::add_launches(1);
     p = vc::GemmParams{};
     p.epilogue = fused_ln ? vc::kEpiResidualLnF32 : (follow_ln ? vc::kEpiResidualPublishF32 : vc::kEpiResidualF32);
+    if (fold_ln) p.epilogue = vc::kEpiResidualStatsF32;
+    p.xb_out = ws.y2;
+    p.part_out = part2;
     p.bias = b.proj_b;
     p.gamma = b.ls1;
     p.out = ws.x;
@@ -269,20 +291,26 @@ int vc_vit_forward(vc_handle* h, const vc_vit_weights* w, const uint8_t* images,
       VC_CUDA(vc::launch_layernorm_follow(ws.x, b.ln2_w, b.ln2_b, ws.y2, rows, C, tiles_c, ws.counters, done,
                                           h->num_sms, s));
       vc::add_launches(1);
-    } else if (!fused_ln) {
+    } else if (!fused_ln && !fold_ln) {
       VC_CUDA(vc::launch_layernorm_bf16(ws.x, b.ln2_w, b.ln2_b, ws.y2, rows, C, s));
       vc::add_launches(1);
     }
     p = vc::GemmParams{};
-    p.epilogue = vc::kEpiBiasGeluBf16;
-    p.bias = b.fc1_b;
+    p.epilogue = fold_ln ? vc::kEpiFoldBiasGeluBf16 : vc::kEpiBiasGeluBf16;
+    p.bias = fold_ln ? b.fc1_bf : b.fc1_b;
+    p.ln_part = part2;
+    p.ln_slices = slices;
+    p.colsum = b.fc1_cs;
     p.out = ws.wide;
     p.ldo = 4 * C;
-    rc = run_linear(h, ws.y2, b.fc1_w, rows, 4 * C, C, p, s);
+    rc = run_linear(h, ws.y2, fold_ln ? b.fc1_wf : b.fc1_w, rows, 4 * C, C, p, s);
     if (rc != VC_OK) return rc;
     p = vc::GemmParams{};
     p.epilogue = (fused_ln && !last) ? vc::kEpiResidualLnF32
                                      : ((follow_ln && !last) ? vc::kEpiResidualPublishF32 : vc::kEpiResidualF32);
+    if (fold_ln && !last) p.epilogue = vc::kEpiResidualStatsF32;
+    p.xb_out = ws.y;
+    p.part_out = part1;
     p.bias = b.fc2_b;
     p.gamma = b.ls2;
     p.out = ws.x;
@@ -299,7 +327,7 @@ int vc_vit_forward(vc_handle* h, const vc_vit_weights* w, const uint8_t* images,
       VC_CUDA(vc::launch_layernorm_follow(ws.x, w->blocks[l + 1].ln1_w, w->blocks[l + 1].ln1_b, ws.y, rows, C, tiles_c,
                                           ws.counters, done, h->num_sms, s));
       vc::add_launches(1);
-    } else if (!fused_ln && !last) {
+    } else if (!fused_ln && !fold_ln && !last) {
       VC_CUDA(vc::launch_layernorm_bf16(ws.x, w->blocks[l + 1].ln1_w, w->blocks[l + 1].ln1_b, ws.y, rows, C, s));
       vc::add_launches(1);
     }

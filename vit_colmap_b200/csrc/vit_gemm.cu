@@ -338,6 +338,14 @@ cudaError_t launch_gemm(const CUtensorMap& map_a, const CUtensorMap& map_w, cons
     case kEpiBiasGeluBf16: return launch_one<kEpiBiasGeluBf16>(map_a, map_w, p, grid, stream);
     case kEpiResidualF32: return launch_one<kEpiResidualF32>(map_a, map_w, p, grid, stream);
     case kEpiPatchEmbed: return launch_one<kEpiPatchEmbed>(map_a, map_w, p, grid, stream);
+    case kEpiFoldBiasBf16:
+    case kEpiFoldBiasGeluBf16:
+      if (!p.ln_part || !p.colsum || p.ln_slices <= 0 || p.ln_slices * 128 != p.K) return cudaErrorInvalidValue;
+      return p.epilogue == kEpiFoldBiasBf16 ? launch_one<kEpiFoldBiasBf16>(map_a, map_w, p, grid, stream)
+                                            : launch_one<kEpiFoldBiasGeluBf16>(map_a, map_w, p, grid, stream);
+    case kEpiResidualStatsF32:
+      if (!p.xb_out || !p.part_out || p.N % 128 != 0 || p.N != p.ldo) return cudaErrorInvalidValue;
+      return launch_one<kEpiResidualStatsF32>(map_a, map_w, p, grid, stream);
     case kEpiResidualPublishF32: {
       if (!p.tile_counters) return cudaErrorInvalidValue;
       static SmemOptIn opt_in;

@@ -210,7 +210,8 @@ cudaError_t launch_one2(const CUtensorMap& map_a, const CUtensorMap& map_w, cons
 
 bool gemm2_supports(int epilogue) {
   return epilogue == kEpiBiasBf16 || epilogue == kEpiBiasGeluBf16 || epilogue == kEpiResidualF32 ||
-         epilogue == kEpiPatchEmbed;
+         epilogue == kEpiPatchEmbed || epilogue == kEpiFoldBiasBf16 || epilogue == kEpiFoldBiasGeluBf16 ||
+         epilogue == kEpiResidualStatsF32;
 }
 
 // map_w must have a {64, 128} box (half of the 256 weight rows per CTA); map_a the usual {64, 128}.
@@ -224,6 +225,14 @@ cudaError_t launch_gemm2(const CUtensorMap& map_a, const CUtensorMap& map_w, con
     case kEpiBiasBf16: return launch_one2<kEpiBiasBf16>(map_a, map_w, p, clusters, stream);
     case kEpiBiasGeluBf16: return launch_one2<kEpiBiasGeluBf16>(map_a, map_w, p, clusters, stream);
     case kEpiResidualF32: return launch_one2<kEpiResidualF32>(map_a, map_w, p, clusters, stream);
+    case kEpiFoldBiasBf16:
+    case kEpiFoldBiasGeluBf16:
+      if (!p.ln_part || !p.colsum || p.ln_slices <= 0 || p.ln_slices * 128 != p.K) return cudaErrorInvalidValue;
+      return p.epilogue == kEpiFoldBiasBf16 ? launch_one2<kEpiFoldBiasBf16>(map_a, map_w, p, clusters, stream)
+                                            : launch_one2<kEpiFoldBiasGeluBf16>(map_a, map_w, p, clusters, stream);
+    case kEpiResidualStatsF32:
+      if (!p.xb_out || !p.part_out || p.N % 128 != 0 || p.N != p.ldo) return cudaErrorInvalidValue;
+      return launch_one2<kEpiResidualStatsF32>(map_a, map_w, p, clusters, stream);
     default: return launch_one2<kEpiPatchEmbed>(map_a, map_w, p, clusters, stream);
   }
 }

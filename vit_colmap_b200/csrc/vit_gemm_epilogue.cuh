@@ -11,8 +11,14 @@ namespace vc {
 
 constexpr int kGemmBM = 128, kGemmBN = 256;
 constexpr bool gemm_is_residual(int epi) {
-  return epi == kEpiResidualF32 || epi == kEpiResidualLnF32 || epi == kEpiResidualPublishF32;
+  return epi == kEpiResidualF32 || epi == kEpiResidualLnF32 || epi == kEpiResidualPublishF32 ||
+         epi == kEpiResidualStatsF32;
 }
+constexpr bool gemm_is_bf16_out(int epi) {
+  return epi == kEpiBiasBf16 || epi == kEpiBiasGeluBf16 || epi == kEpiFoldBiasBf16 || epi == kEpiFoldBiasGeluBf16;
+}
+constexpr bool gemm_is_fold(int epi) { return epi == kEpiFoldBiasBf16 || epi == kEpiFoldBiasGeluBf16; }
+constexpr bool gemm_has_gelu(int epi) { return epi == kEpiBiasGeluBf16 || epi == kEpiFoldBiasGeluBf16; }
 
 // t_addr: TMEM address of the warp's first column (lane quarter q, column half h of the tile's accumulator).
 // tm / tn: 128-row block and 256-column block of D.  stg: this warp's 32 x 128 B transposition buffer.
@@ -25,7 +31,24 @@ __device__ __forceinline__ void gemm_epilogue_tile(const GemmParams& p, uint32_t
   const int tc = lane & 7, tr = lane >> 3;       // transposed layout: 8 lanes per row, rows tr + 4 i
   const int row0 = tm * BM + q * 32;
   bool released = false;
-  if (EPI == kEpiBiasBf16 || EPI == kEpiBiasGeluBf16) {
+  if (gemm_is_bf16_out(EPI)) {
+    // folded LayerNorm: this thread's row statistics from the producing GEMM's per-slice sums (fixed order)
+    float ln_mean = 0.f, ln_rstd = 1.f;
+    if (gemm_is_fold(EPI)) {
+      const int m = row0 + lane;
+      if (m < p.M) {
+        const float2* part = reinterpret_cast<const float2*>(p.ln_part) + (size_t)m * p.ln_slices;
+        float s1 = 0.f, s2 = 0.f;
+        for (int j = 0; j < p.ln_slices; ++j) {
+          const float2 v = __ldcg(part + j);
+          s1 += v.x;
+          s2 += v.y;
+        }
+        const float inv_c = 1.0f / (float)p.K;
+        ln_mean = s1 * inv_c;
+        ln_rstd = rsqrtf(fmaxf(s2 * inv_c - ln_mean * ln_mean, 0.f) + 1e-6f);
+      }
+    }
     // bf16 outputs: 64 columns (= 128 B per row) per round
 #pragma unroll 1
     for (int c = 0; c < 2; ++c) {
@@ -52,12 +75,20 @@ __device__ __forceinline__ void gemm_epilogue_tile(const GemmParams& p, uint32_t
 #pragma unroll
         for (int g = 0; g < 8; ++g) {
           const float4 b = __ldg(b4 + g);
-          v[4 * g + 0] += b.x;
-          v[4 * g + 1] += b.y;
-          v[4 * g + 2] += b.z;
-          v[4 * g + 3] += b.w;
+          if (gemm_is_fold(EPI)) {
+            const float4 cs = __ldg(reinterpret_cast<const float4*>(p.colsum + nh) + g);
+            v[4 * g + 0] = fmaf(ln_rstd, fmaf(-ln_mean, cs.x, v[4 * g + 0]), b.x);
+            v[4 * g + 1] = fmaf(ln_rstd, fmaf(-ln_mean, cs.y, v[4 * g + 1]), b.y);
+            v[4 * g + 2] = fmaf(ln_rstd, fmaf(-ln_mean, cs.z, v[4 * g + 2]), b.z);
+            v[4 * g + 3] = fmaf(ln_rstd, fmaf(-ln_mean, cs.w, v[4 * g + 3]), b.w);
+          } else {
+            v[4 * g + 0] += b.x;
+            v[4 * g + 1] += b.y;
+            v[4 * g + 2] += b.z;
+            v[4 * g + 3] += b.w;
+          }
         }
-        if (EPI == kEpiBiasGeluBf16) {
+        if (gemm_has_gelu(EPI)) {
 #pragma unroll
           for (int e = 0; e < 32; e += 2) {
             const float2 g = gelu_erf2(make_float2(v[e], v[e + 1]));
@@ -93,6 +124,11 @@ __device__ __forceinline__ void gemm_epilogue_tile(const GemmParams& p, uint32_t
     // fp32 outputs (residual update / patch embedding): 32 columns (= 128 B per row) per round;
     // bias, LayerScale and position embedding are applied in the transposed layout, where a
     // lane's 4 columns are fixed
+    float st1[8], st2[8];  // kEpiResidualStatsF32: sums of x and x^2 of this lane's columns, rows tr + 4 i
+    if (EPI == kEpiResidualStatsF32) {
+#pragma unroll
+      for (int i = 0; i < 8; ++i) st1[i] = st2[i] = 0.f;
+    }
 #pragma unroll 1
     for (int c = 0; c < 4; ++c) {
       const int n0 = tn * BN + h * 128 + c * 32;
@@ -136,6 +172,11 @@ __device__ __forceinline__ void gemm_epilogue_tile(const GemmParams& p, uint32_t
             y.z = fmaf(ga.z, a.z + b.z, y.z);
             y.w = fmaf(ga.w, a.w + b.w, y.w);
             *reinterpret_cast<float4*>(static_cast<float*>(p.out) + (size_t)m * p.ldo + col) = y;
+            if (EPI == kEpiResidualStatsF32) {
+              st1[i] += (y.x + y.y) + (y.z + y.w);
+              st2[i] = fmaf(y.x, y.x, fmaf(y.y, y.y, fmaf(y.z, y.z, fmaf(y.w, y.w, st2[i]))));
+              *reinterpret_cast<uint2*>(p.xb_out + (size_t)m * p.N + col) = make_uint2(pack_bf16(y.x, y.y), pack_bf16(y.z, y.w));
+            }
           } else {
             const int img = m / p.tokens_per_image, t = m - img * p.tokens_per_image;
             const size_t out_row = (size_t)img * (p.tokens_per_image + 1) + 1 + t;
@@ -146,6 +187,24 @@ __device__ __forceinline__ void gemm_epilogue_tile(const GemmParams& p, uint32_t
         }
       }
       __syncwarp();
+    }
+    if (EPI == kEpiResidualStatsF32) {
+      // the eight lanes of a row (tc = 0 .. 7) add up in a fixed order; lane tc == 0 stores the slice's pair
+      const int slice = tn * (BN / 128) + h;
+      if (slice * 128 < p.N) {  // warp-uniform
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+          float a = st1[i], b = st2[i];
+#pragma unroll
+          for (int o = 1; o < 8; o <<= 1) {
+            a += __shfl_xor_sync(0xffffffffu, a, o);
+            b += __shfl_xor_sync(0xffffffffu, b, o);
+          }
+          const int m = row0 + tr + 4 * i;
+          if (tc == 0 && m < p.M)
+            reinterpret_cast<float2*>(p.part_out)[(size_t)m * (p.N >> 7) + slice] = make_float2(a, b);
+        }
+      }
     }
   }
   if (!released) release();  // this warp's columns lie entirely beyond N

@@ -22,7 +22,15 @@ enum GemmEpilogue {
   // kEpiResidualF32 whose eight epilogue warps each bump the counter of a tile's 128-row block once their part of
   // the tile is visible device-wide (one tile late, when the fence costs nothing), and lets the next kernel of the stream start early (programmatic dependent launch): that
   // kernel is launch_layernorm_follow, which normalises row blocks WHILE this GEMM is still running.
-  kEpiResidualPublishF32 = 5
+  kEpiResidualPublishF32 = 5,
+  // LayerNorm folded into the GEMMs on either side of it (VC_VIT_LN=fold).  The residual GEMM (kEpiResidualStatsF32)
+  // also stores a bf16 copy of the updated rows and, per row and 128-column slice, the sums of x and x^2.  The next
+  // GEMM takes that bf16 copy as its A operand with weights W' = W * ln_w (folded on the host) and finishes the
+  // normalisation per row in its epilogue: out = rstd * (acc - mean * colsum[n]) + bias'[n]
+  // (colsum[n] = sum_k W'[n,k], bias' = bias + W ln_b; kEpiFoldBiasBf16 / kEpiFoldBiasGeluBf16).
+  kEpiFoldBiasBf16 = 6,
+  kEpiFoldBiasGeluBf16 = 7,
+  kEpiResidualStatsF32 = 8
 };
 
 struct GemmParams {
@@ -39,6 +47,13 @@ struct GemmParams {
   const float* ln_b;
   __nv_bfloat16* ln_out;  // bf16 [M, N]; must not alias the A operand
   int* tile_counters;     // [ceil(M / 128)] zero before the launch; the kernel leaves them zero
+  // kEpiResidualStatsF32 (N % 128 == 0)
+  __nv_bfloat16* xb_out;  // bf16 [M, N]: copy of the updated rows
+  float* part_out;        // f32 [M, N / 128, 2]: per row and 128-column slice, sum x and sum x^2
+  // kEpiFoldBias*Bf16
+  const float* ln_part;   // f32 [M, ln_slices, 2] written by the producing GEMM (row statistics over K columns)
+  int ln_slices;          // K / 128
+  const float* colsum;    // f32 [N]
 };
 int gemm_smem_bytes();
 // Two-SM (cta_group::2) form, vit_gemm2.cu: a cluster of two CTAs per 256 x 256 tile.  Same results bit for bit.

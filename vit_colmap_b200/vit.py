@@ -74,6 +74,14 @@ class VitBackbone:
                      fc1_w=bf16(sd[p + "mlp.fc1.weight"]), fc1_b=f32(sd[p + "mlp.fc1.bias"]),
                      fc2_w=bf16(sd[p + "mlp.fc2.weight"]), fc2_b=f32(sd[p + "mlp.fc2.bias"]),
                      ls2=f32(sd[p + "ls2.gamma"]))
+            # LayerNorm folded into the next GEMM (VC_VIT_LN=fold, vit_kernels.cuh): W' = bf16(W * ln_w),
+            # colsum over the ROUNDED W' (what the tensor core multiplies), bias' = bias + W ln_b
+            for nm, wk, bk, lw, lb in (("qkv", "attn.qkv", "attn.qkv", "norm1", "norm1"), ("fc1", "mlp.fc1", "mlp.fc1", "norm2", "norm2")):
+                W = sd[p + wk + ".weight"].detach().float().cpu()
+                wf = (W * sd[p + lw + ".weight"].detach().float().cpu()[None, :]).to(torch.bfloat16)
+                t[nm + "_wf"] = wf.to(dev).contiguous()
+                t[nm + "_cs"] = f32(wf.float().sum(dim=1))
+                t[nm + "_bf"] = f32(sd[p + bk + ".bias"].detach().float().cpu() + W @ sd[p + lb + ".bias"].detach().float().cpu())
             self._keep.append(t)
             for k, v in t.items():
                 setattr(self._blocks[i], k, _ptr(v))
