@@ -208,6 +208,8 @@ __device__ __forceinline__ void gemm_body(const CUtensorMap& map_a, const CUtens
     for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x, ++it) {
       const int tm = tile / tiles_n, tn = tile - tm * tiles_n;
       const uint32_t as = it & 1, aph = (it >> 1) & 1;
+      float ln_mean = 0.f, ln_rstd = 1.f;
+      if (gemm_is_fold(EPI)) gemm_row_stats(p, tm * BM + q * 32 + lane, ln_mean, ln_rstd);
       mbar_wait_sleep(tfull_bar(as), aph, 32);
       tc_fence_after();
       if (EPI == kEpiResidualPublishF32 && pending_tm >= 0) {
@@ -221,7 +223,7 @@ __device__ __forceinline__ void gemm_body(const CUtensorMap& map_a, const CUtens
       gemm_epilogue_tile<EPI>(p, t_addr, tm, tn, q, h, lane, stg, [&] {
         tc_fence_before();
         mbar_arrive(tempty_bar(as));
-      });
+      }, ln_mean, ln_rstd);
       if (EPI == kEpiResidualPublishF32) pending_tm = tm;  // published one tile later, when the fence is free
       if (EPI == kEpiResidualLnF32) {
         // tile stored: publish it; the CTA holding the block's last column tile normalises the block

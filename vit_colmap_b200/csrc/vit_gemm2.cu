@@ -182,6 +182,8 @@ vit_gemm2_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
       const int tm2 = tile / tiles_n, tn = tile - tm2 * tiles_n;
       const int tm = 2 * tm2 + (int)rank;
       const uint32_t as = it & 1, aph = (it >> 1) & 1;
+      float ln_mean = 0.f, ln_rstd = 1.f;
+      if (gemm_is_fold(EPI)) gemm_row_stats(p, tm * BM + q * 32 + lane, ln_mean, ln_rstd);
       mbar_wait_sleep(tfull_bar(as), aph, 32);
       tc_fence_after();
       const uint32_t t_addr = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + as * BN + h * 128;
@@ -189,7 +191,7 @@ vit_gemm2_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
         tc_fence_before();
         __syncwarp();
         if (lane == 0) mbar_arrive_cluster(lead_tempty[as]);
-      });
+      }, ln_mean, ln_rstd);
     }
   }
 

@@ -20,35 +20,38 @@ constexpr bool gemm_is_bf16_out(int epi) {
 constexpr bool gemm_is_fold(int epi) { return epi == kEpiFoldBiasBf16 || epi == kEpiFoldBiasGeluBf16; }
 constexpr bool gemm_has_gelu(int epi) { return epi == kEpiBiasGeluBf16 || epi == kEpiFoldBiasGeluBf16; }
 
+// Folded LayerNorm (kEpiFoldBias*Bf16): mean and 1 / std of row m from the producing GEMM's per-slice sums, added
+// in slice order.  Callers ask for it BEFORE they wait for the accumulator, so the L2 latency is hidden.
+__device__ __forceinline__ void gemm_row_stats(const GemmParams& p, int m, float& mean, float& rstd) {
+  mean = 0.f;
+  rstd = 1.f;
+  if (m >= p.M) return;
+  const float2* part = reinterpret_cast<const float2*>(p.ln_part) + (size_t)m * p.ln_slices;
+  float s1 = 0.f, s2 = 0.f;
+  for (int j = 0; j < p.ln_slices; ++j) {
+    const float2 v = __ldcg(part + j);
+    s1 += v.x;
+    s2 += v.y;
+  }
+  const float inv_c = 1.0f / (float)p.K;
+  mean = s1 * inv_c;
+  rstd = rsqrtf(fmaxf(s2 * inv_c - mean * mean, 0.f) + 1e-6f);
+}
+
 // t_addr: TMEM address of the warp's first column (lane quarter q, column half h of the tile's accumulator).
 // tm / tn: 128-row block and 256-column block of D.  stg: this warp's 32 x 128 B transposition buffer.
 // release(): called once, as soon as the accumulator has been read (hands the TMEM buffer back).
 template <int EPI, typename Release>
 __device__ __forceinline__ void gemm_epilogue_tile(const GemmParams& p, uint32_t t_addr, int tm, int tn, int q, int h,
-                                                   int lane, uint8_t* stg, Release release) {
+                                                   int lane, uint8_t* stg, Release release, float ln_mean = 0.f,
+                                                   float ln_rstd = 1.f) {
   constexpr int BM = kGemmBM, BN = kGemmBN;
   uint8_t* stg_row = stg + lane * 128;          // row layout: thread = row
   const int tc = lane & 7, tr = lane >> 3;       // transposed layout: 8 lanes per row, rows tr + 4 i
   const int row0 = tm * BM + q * 32;
   bool released = false;
   if (gemm_is_bf16_out(EPI)) {
-    // folded LayerNorm: this thread's row statistics from the producing GEMM's per-slice sums (fixed order)
-    float ln_mean = 0.f, ln_rstd = 1.f;
-    if (gemm_is_fold(EPI)) {
-      const int m = row0 + lane;
-      if (m < p.M) {
-        const float2* part = reinterpret_cast<const float2*>(p.ln_part) + (size_t)m * p.ln_slices;
-        float s1 = 0.f, s2 = 0.f;
-        for (int j = 0; j < p.ln_slices; ++j) {
-          const float2 v = __ldcg(part + j);
-          s1 += v.x;
-          s2 += v.y;
-        }
-        const float inv_c = 1.0f / (float)p.K;
-        ln_mean = s1 * inv_c;
-        ln_rstd = rsqrtf(fmaxf(s2 * inv_c - ln_mean * ln_mean, 0.f) + 1e-6f);
-      }
-    }
+
     // bf16 outputs: 64 columns (= 128 B per row) per round
 #pragma unroll 1
     for (int c = 0; c < 2; ++c) {
