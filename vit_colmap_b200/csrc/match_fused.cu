@@ -32,7 +32,7 @@ constexpr int kABytes = BM * BK * 2, kBBytes = BN * BK * 2, kStageBytes = kAByte
 // warp0 TMA, warp1 MMA, warp2 TMEM alloc, warps 4-15 epilogue: three warps per TMEM lane quarter, each
 // on 3 / 3 / 2 of the tile's eight 32-column chunks (the epilogue, not the MMA, paced the kernel with
 // two warps per quarter: profiles/r01_v8_match_fused_ncu_summary.json)
-constexpr int kEpiGroups = 3;
+constexpr int kEpiGroups = kMatchEpiGroups;  // epilogue warps per TMEM lane quarter
 constexpr int kEpiThreads = kEpiGroups * 128;
 constexpr int kThreads = 128 + kEpiThreads;
 constexpr int kTmemCols = 512;
@@ -178,8 +178,8 @@ match_fused_kernel(const __grid_constant__ CUtensorMap tmap, const MatchParams p
       epi_bar_sync();
       const int ncols = min(BN, it.n2 - it.cb * BN);  // valid columns of this block
       // this warp's chunks (32 columns each): group 0 -> 0..2, group 1 -> 3..5, group 2 -> 6..7
-      const int c_begin = h * 3;
-      const int c_end = min(min(c_begin + 3, BN / 32), (ncols + 31) >> 5);
+      const int c_begin = h * kMatchChunksPerGroup;
+      const int c_end = min(min(c_begin + kMatchChunksPerGroup, BN / 32), (ncols + 31) >> 5);
       const size_t pair_row0 = (size_t)it.pair * p.kmax;
       // hint: lower bound of a row's final second-best (L2 load, may be stale).  The load for the NEXT row
       // tile is issued before this tile's chunks are processed, so its latency is off the critical path.

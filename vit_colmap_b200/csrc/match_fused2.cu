@@ -39,7 +39,7 @@ namespace {
 
 constexpr int BM = 128, BN = 256, BK = 64, kStages = 6;
 constexpr int kABytes = BM * BK * 2, kBBytes = (BN / 2) * BK * 2, kStageBytes = kABytes + kBBytes;
-constexpr int kEpiGroups = 3;   // epilogue warps per TMEM lane quarter: 3 / 3 / 2 of the eight 32-column chunks
+constexpr int kEpiGroups = kMatchEpiGroups;  // epilogue warps per TMEM lane quarter
 constexpr int kEpiWarps = 4 * kEpiGroups;
 constexpr int kEpiThreads = 32 * kEpiWarps;
 constexpr int kThreads = 128 + kEpiThreads;  // warp0 TMA, warp1 MMA, warp2 TMEM alloc, warps 4-15 epilogue
@@ -248,8 +248,8 @@ match_fused2_kernel(const __grid_constant__ CUtensorMap tmap, const MatchParams 
       epi_bar_sync();
       const int ncols = min(BN, it.n2 - it.cb * BN);  // valid columns of this block
       // this warp's chunks: columns [h*128, h*128+128) of the block, 32 per chunk
-      const int c_begin = h * 3;
-      const int c_end = min(min(c_begin + 3, BN / 32), (ncols + 31) >> 5);
+      const int c_begin = h * kMatchChunksPerGroup;
+      const int c_end = min(min(c_begin + kMatchChunksPerGroup, BN / 32), (ncols + 31) >> 5);
       const size_t pair_row0 = (size_t)it.pair * p.kmax;
       // hint: lower bound of a row's final second-best (L2 load, may be stale).  The load for the NEXT row
       // tile is issued before this tile's chunks are processed, so its latency is off the critical path.

@@ -16,6 +16,15 @@ struct GuidedGeometry {
   float max_h, max_f;  // squared residual bounds
 };
 
+// Epilogue warps per TMEM lane quarter in the single-pass kernels (match_fused.cu, match_fused2.cu): each owns
+// 8 / kMatchEpiGroups (rounded up) of a tile's eight 32-column chunks and writes its own row partial, so the
+// row-partial buffers are sized with it (vc_api.cu part_bytes).  4 = two chunks per warp, no idle third group.
+#ifndef VC_MATCH_EPI_GROUPS
+#define VC_MATCH_EPI_GROUPS 4
+#endif
+constexpr int kMatchEpiGroups = VC_MATCH_EPI_GROUPS;
+constexpr int kMatchChunksPerGroup = (8 + kMatchEpiGroups - 1) / kMatchEpiGroups;
+
 struct MatchParams {
   const int32_t* counts;  // [n_images] valid descriptors per image
   const int32_t* pairs;   // [n_pairs, 2] image indices

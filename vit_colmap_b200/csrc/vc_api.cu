@@ -77,8 +77,8 @@ size_t colstate_bytes(int n_pairs, int kmax) {  // two-SM kernel: u64 key + u32 
   return align_up((size_t)n_pairs * 2 * kmax * 8, 256) + align_up((size_t)n_pairs * 2 * kmax * 4, 256);
 }
 size_t part_bytes(int n_pairs, int kmax) {
-  // row partials: one per (column block, epilogue column group); up to 3 groups per 256-column block
-  return align_up((size_t)n_pairs * 3 * ((kmax + 255) / 256) * (size_t)kmax * 4, 256);
+  // row partials: one per (column block, epilogue column group)
+  return align_up((size_t)n_pairs * vc::kMatchEpiGroups * ((kmax + 255) / 256) * (size_t)kmax * 4, 256);
 }
 
 // Kernel choice: the single-pass kernel halves the tensor work; its heavier epilogue used to lose to
