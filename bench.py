@@ -29,8 +29,8 @@ UNIT = "pairs/s"
 N_IMAGES, KPTS, DIM = 32, 8192, 768
 FLOP_PER_PAIR = 2.0 * KPTS * KPTS * DIM  # 2*N*M*d
 # dram__bytes_read.sum + dram__bytes_write.sum of one match_fused2_kernel launch (496 pairs), ncu --set full
-# (profiles/r02_match_fused2_ncu_summary.json)
-NCU_TRAFFIC_BYTES = 6.901551e9 + 4.766794e9
+# (profiles/r02c_match_fused2_ncu_summary.json: the shipped kernel with sixteen epilogue warps)
+NCU_TRAFFIC_BYTES = 7.056956e9 + 6.324735e9
 
 
 def _peaks():
@@ -377,8 +377,8 @@ def run_ours(args):
                          "kernel": "match_fused2_kernel (two-SM cta_group::2 form of match_fused_kernel)", "kernel_ms": kern_ms,
                          "note": "achieved = 2*N*M*d per pair (one MMA sweep gives row and column top-2) "
                                  "over the top-2 stage (memset + fused kernel + row / column partial merges); traffic "
-                                 "from profiles/r02_match_fused2_ncu_summary.json (dram read+write of one launch of the "
-                                 "shipped kernel; tensor pipe 84.3 % active in that capture)"},
+                                 "from profiles/r02c_match_fused2_ncu_summary.json (dram read+write of one launch of the "
+                                 "shipped kernel; tensor pipe 82.7 % active in that capture)"},
             "clocks": clocks,
         }
         if extract is not None:
