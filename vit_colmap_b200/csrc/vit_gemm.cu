@@ -44,9 +44,6 @@ constexpr int kThreads = 384;
 constexpr int kTmemCols = 512;
 constexpr int kStageOutBytes = 32 * 128;  // per epilogue warp: 32 rows x 128 B transposition buffer
 constexpr int kSmemBytes = kStages * kStageBytes + 1024 + 256 + 8 * kStageOutBytes;
-constexpr bool is_residual(int epi) {
-  return epi == kEpiResidualF32 || epi == kEpiResidualLnF32 || epi == kEpiResidualPublishF32;
-}
 
 __device__ __forceinline__ float warp_sum(float v) {
 #pragma unroll
