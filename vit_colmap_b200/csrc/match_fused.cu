@@ -29,9 +29,10 @@ namespace {
 
 constexpr int BM = 128, BN = 256, BK = 64, kStages = 4;
 constexpr int kABytes = BM * BK * 2, kBBytes = BN * BK * 2, kStageBytes = kABytes + kBBytes;
-// warp0 TMA, warp1 MMA, warp2 TMEM alloc, warps 4-15 epilogue: three warps per TMEM lane quarter, each
-// on 3 / 3 / 2 of the tile's eight 32-column chunks (the epilogue, not the MMA, paced the kernel with
-// two warps per quarter: profiles/r01_v8_match_fused_ncu_summary.json)
+// warp0 TMA, warp1 MMA, warp2 TMEM alloc, warps 4-19 epilogue: kMatchEpiGroups (4) warps per TMEM lane quarter,
+// each on two of the tile's eight 32-column chunks.  The epilogue, not the MMA, paces the kernel below d = 768: two
+// warps per quarter were too few (profiles/r01_v8_match_fused_ncu_summary.json), three left the 2-chunk warp idle a
+// third of every tile (3 / 3 / 2).
 constexpr int kEpiGroups = kMatchEpiGroups;  // epilogue warps per TMEM lane quarter
 constexpr int kEpiThreads = kEpiGroups * 128;
 constexpr int kThreads = 128 + kEpiThreads;

@@ -42,7 +42,7 @@ constexpr int kABytes = BM * BK * 2, kBBytes = (BN / 2) * BK * 2, kStageBytes = 
 constexpr int kEpiGroups = kMatchEpiGroups;  // epilogue warps per TMEM lane quarter
 constexpr int kEpiWarps = 4 * kEpiGroups;
 constexpr int kEpiThreads = 32 * kEpiWarps;
-constexpr int kThreads = 128 + kEpiThreads;  // warp0 TMA, warp1 MMA, warp2 TMEM alloc, warps 4-15 epilogue
+constexpr int kThreads = 128 + kEpiThreads;  // warp0 TMA, warp1 MMA, warp2 TMEM alloc, warps 4-19 epilogue
 constexpr int kTmemCols = 512;
 constexpr int kColStateBytes = BN * 8 + BN * 4 + (BN / 8) * 4;  // keys, seconds, per-8-column minima
 constexpr int kSmemBytes = kStages * kStageBytes + 1024 + 256 + kColStateBytes;
