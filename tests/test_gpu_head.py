@@ -69,6 +69,40 @@ def test_conv3x3_matches_fp32_reference(lib_handle, shape, epilogue):
     assert err <= tol, (err, s)
 
 
+@pytest.mark.parametrize("shape", [(1, 37, 37, 384, 512), (3, 5, 7, 128, 192), (1, 1, 1, 64, 32), (2, 13, 31, 256, 64),
+                                   (1, 17, 16, 64, 256)], ids=lambda s: "x".join(map(str, s)))
+@pytest.mark.parametrize("kind,epilogue", [(0, 1), (0, 2), (1, 0)])
+def test_two_sm_conv_equals_one_sm(lib_handle, monkeypatch, shape, kind, epilogue):
+    """The cta_group::2 convolution (conv_gemm2.cu, default) and the one-SM kernel (VC_CONV_2CTA=0) share the per-tile
+    epilogue and the accumulation order: identical outputs, bit for bit -- also with an odd number of 8 x 16 patches
+    (the last pair's second CTA works on nothing) and channel blocks of 192 / 64 / 32."""
+    import torch
+    from vit_colmap_b200 import _lib
+    from vit_colmap_b200.head import pack_conv3x3, pack_deconv4x4s2
+    lib, h = lib_handle
+    B, H, W, Cin, Cout = shape
+    g = torch.Generator(device="cuda").manual_seed(sum(shape) + kind)
+    x = _nhwc(torch.randn((B, Cin, H, W), generator=g, device="cuda").to(torch.bfloat16))
+    if kind == 0:
+        wp = pack_conv3x3((torch.randn((Cout, Cin, 3, 3), generator=g, device="cuda") / (3 * Cin ** 0.5)).to(torch.bfloat16))
+        oh, ow = H, W
+    else:
+        wp = pack_deconv4x4s2((torch.randn((Cin, Cout, 4, 4), generator=g, device="cuda") / (2 * Cin ** 0.5)).to(torch.bfloat16))
+        oh, ow = 2 * H, 2 * W
+    wp = wp.contiguous()
+    scale = 1 + 0.2 * torch.randn((Cout,), generator=g, device="cuda")
+    shift = torch.randn((Cout,), generator=g, device="cuda")
+    outs = []
+    for env in ("1", "0"):
+        monkeypatch.setenv("VC_CONV_2CTA", env)
+        out = torch.full((B, oh, ow, Cout), float("nan"), dtype=torch.float32 if epilogue == 2 else torch.bfloat16, device="cuda")
+        _lib.check(lib.vc_conv2d(h, x.data_ptr(), B, H, W, Cin, wp.data_ptr(), Cout, kind, epilogue,
+                                 scale.data_ptr() if epilogue == 1 else None, shift.data_ptr(), out.data_ptr(), _stream()))
+        outs.append(out)
+    torch.cuda.synchronize()
+    assert torch.isfinite(outs[0].float()).all() and torch.equal(outs[0], outs[1])
+
+
 @pytest.mark.parametrize("shape", [(2, 8, 16, 64, 256), (1, 37, 37, 768, 512), (3, 5, 7, 128, 64), (1, 74, 74, 512, 512),
                                    (1, 3, 3, 384, 512)], ids=lambda s: "x".join(map(str, s)))
 def test_deconv_matches_conv_transpose2d(lib_handle, shape):

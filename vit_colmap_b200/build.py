@@ -18,7 +18,7 @@ CSRC = PKG / "csrc"
 OUT = PKG / "_vc_b200.so"
 SOURCES = ["match_kernel.cu", "match_fused.cu", "match_fused2.cu", "vc_api.cu", "score_kernels.cu", "select_kernels.cu",
            "sample_kernels.cu", "vc_api_extract.cu", "vc_api_noalloc.cu", "vc_api_sampler.cu", "vit_gemm.cu", "vit_gemm2.cu", "vit_attention.cu",
-           "vit_pointwise.cu", "vc_api_vit.cu", "conv_gemm.cu", "head_pointwise.cu", "vc_api_head.cu"]
+           "vit_pointwise.cu", "vc_api_vit.cu", "conv_gemm.cu", "conv_gemm2.cu", "head_pointwise.cu", "vc_api_head.cu"]
 EXTRA_SOURCES_GLOB = "*_kernels.cu"
 
 NVCC_FLAGS = [

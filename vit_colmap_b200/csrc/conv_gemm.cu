@@ -14,6 +14,7 @@
 //     split over two output tensors: merged keypoint/descriptor head conv); +bias -> f32.
 #include "head_kernels.cuh"
 
+#include "conv_gemm_epilogue.cuh"
 #include "vc_epilogue.cuh"
 #include "vc_ptx.cuh"
 #include "vc_launch.cuh"
@@ -28,26 +29,16 @@ constexpr int kThreads = 384;
 constexpr int kTmemCols = 512;
 constexpr int kStageOutBytes = 32 * 128;  // per epilogue warp: 32 rows x 128 B transposition buffer
 constexpr int kSmemBytes = kStages * kStageBytes + 1024 + 256 + 8 * kStageOutBytes;
-static_assert(kConvTileH * kConvTileW == BM, "M tile is one 8x16 pixel patch");
+static_assert(kConvTileH * kConvTileW == BM && BM == kConvBM && BN == kConvBN, "M tile is one 8x16 pixel patch");
 
-struct TileCoord {
-  int b, y0, x0, ph, n0;
-};
+using TileCoord = ConvTileCoord;
 
+// tile -> (256-channel block fastest, then sub-pixel phase, then patch)
 __device__ __forceinline__ TileCoord decode_tile(int tile, const ConvParams& p, int tiles_n, int tiles_x,
                                                  int tiles_per_image) {
-  TileCoord t;
   const int tn = tile % tiles_n;
-  int r = tile / tiles_n;
-  t.ph = r % p.phases;
-  r /= p.phases;
-  t.b = r / tiles_per_image;
-  r -= t.b * tiles_per_image;
-  const int ty = r / tiles_x;
-  t.y0 = ty * kConvTileH;
-  t.x0 = (r - ty * tiles_x) * kConvTileW;
-  t.n0 = tn * BN;
-  return t;
+  const int r = tile / tiles_n;
+  return conv_tile_coord(p, r / p.phases, r % p.phases, tn, tiles_x, tiles_per_image);
 }
 
 template <int EPI>
@@ -153,154 +144,18 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
     // tcgen05.ld gives thread t pixel t of the warp's 32; stores then run with 8 lanes per pixel so a
     // warp instruction covers whole 128-byte lines (see vit_gemm.cu)
     uint8_t* stg = smem + kStages * kStageBytes + 256 + (warp - 4) * kStageOutBytes;
-    uint8_t* stg_row = stg + lane * 128;
-    const int tc = lane & 7, tr = lane >> 3;
     uint32_t it = 0;
     for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x, ++it) {
       const TileCoord t = decode_tile(tile, p, tiles_n, tiles_x, tiles_per_image);
-      // output pixel of the 8 rows this lane stores (rows tr + 4 i of the warp's 32)
-      size_t out_pix[8];
-      bool ok[8];
-#pragma unroll
-      for (int i = 0; i < 8; ++i) {
-        const int r = q * 32 + tr + 4 * i;
-        const int y = t.y0 + r / kConvTileW, x = t.x0 + r % kConvTileW;
-        ok[i] = y < p.H && x < p.W;
-        out_pix[i] = ((size_t)t.b * p.Ho + (size_t)(y * p.sy + p.oy[t.ph])) * p.Wo + (size_t)(x * p.sx + p.ox[t.ph]);
-      }
+      const ConvLanePixels px = conv_lane_pixels(p, t, q, lane);
       const uint32_t as = it & 1, aph = (it >> 1) & 1;
       mbar_wait_sleep(tfull_bar(as), aph, 32);
       tc_fence_after();
       const uint32_t t_addr = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + as * BN + h * 128;
-      bool released = false;
-      if (EPI != kConvBiasF32) {
-        // bf16 outputs: 64 channels (= 128 B per pixel) per round
-#pragma unroll 1
-        for (int c = 0; c < 2; ++c) {
-          const int n0 = t.n0 + h * 128 + c * 64;
-          if (n0 >= p.Cout) break;  // warp-uniform
-          const bool last = (c == 1) || (n0 + 64 >= p.Cout);
-#pragma unroll
-          for (int half = 0; half < 2; ++half) {
-            const int nh = n0 + half * 32;
-            uint32_t vr[32];
-            if (nh < p.Cout) {  // warp-uniform (Cout % 32 == 0)
-              tmem_ld_32x32(t_addr + c * 64 + half * 32, vr);
-              tmem_wait_ld();
-            }
-            if (half == 1 && last) {  // accumulator fully read: hand the TMEM buffer back early
-              tc_fence_before();
-              mbar_arrive(tempty_bar(as));
-              released = true;
-            }
-            if (nh >= p.Cout) break;
-            float v[32];
-#pragma unroll
-            for (int e = 0; e < 32; ++e) v[e] = __uint_as_float(vr[e]);
-            const float4* b4 = reinterpret_cast<const float4*>(p.shift + nh);
-            if (EPI == kConvBnGeluBf16) {
-              const float4* s4 = reinterpret_cast<const float4*>(p.scale + nh);
-#pragma unroll
-              for (int g = 0; g < 8; ++g) {
-                const float4 sc = __ldg(s4 + g), b = __ldg(b4 + g);
-                v[4 * g + 0] = fmaf(v[4 * g + 0], sc.x, b.x);
-                v[4 * g + 1] = fmaf(v[4 * g + 1], sc.y, b.y);
-                v[4 * g + 2] = fmaf(v[4 * g + 2], sc.z, b.z);
-                v[4 * g + 3] = fmaf(v[4 * g + 3], sc.w, b.w);
-              }
-#pragma unroll
-              for (int e = 0; e < 32; e += 2) {
-                const float2 g = gelu_erf2(make_float2(v[e], v[e + 1]));
-                v[e] = g.x;
-                v[e + 1] = g.y;
-              }
-            } else {
-#pragma unroll
-              for (int g = 0; g < 8; ++g) {
-                const float4 b = __ldg(b4 + g);
-                v[4 * g + 0] += b.x;
-                v[4 * g + 1] += b.y;
-                v[4 * g + 2] += b.z;
-                v[4 * g + 3] += b.w;
-              }
-            }
-#pragma unroll
-            for (int g = 0; g < 4; ++g) {
-              uint4 w;
-              w.x = pack_bf16(v[8 * g + 0], v[8 * g + 1]);
-              w.y = pack_bf16(v[8 * g + 2], v[8 * g + 3]);
-              w.z = pack_bf16(v[8 * g + 4], v[8 * g + 5]);
-              w.w = pack_bf16(v[8 * g + 6], v[8 * g + 7]);
-              *reinterpret_cast<uint4*>(stg_row + (((half * 4 + g) ^ (lane & 7)) << 4)) = w;
-            }
-          }
-          __syncwarp();
-          int col = n0 + tc * 8;
-          if (col < p.Cout) {
-            __nv_bfloat16* dst = static_cast<__nv_bfloat16*>(p.out);
-            int ld = p.ldo;
-            if (p.split_n > 0 && col >= p.split_n) {
-              dst = static_cast<__nv_bfloat16*>(p.out2);
-              ld = p.ldo2;
-              col -= p.split_n;
-            }
-#pragma unroll
-            for (int i = 0; i < 8; ++i) {
-              if (ok[i]) {
-                const int r = tr + 4 * i;
-                const uint4 w = *reinterpret_cast<const uint4*>(stg + r * 128 + ((tc ^ (r & 7)) << 4));
-                *reinterpret_cast<uint4*>(dst + out_pix[i] * ld + col) = w;
-              }
-            }
-          }
-          __syncwarp();
-        }
-      } else {
-        // fp32 outputs (1x1 projection): 32 channels (= 128 B per pixel) per round, bias added in the
-        // transposed layout where a lane's 4 channels are fixed
-#pragma unroll 1
-        for (int c = 0; c < 4; ++c) {
-          const int n0 = t.n0 + h * 128 + c * 32;
-          if (n0 >= p.Cout) break;  // warp-uniform
-          const bool last = (c == 3) || (n0 + 32 >= p.Cout);
-          uint32_t vr[32];
-          tmem_ld_32x32(t_addr + c * 32, vr);
-          tmem_wait_ld();
-          if (last) {
-            tc_fence_before();
-            mbar_arrive(tempty_bar(as));
-            released = true;
-          }
-#pragma unroll
-          for (int g = 0; g < 8; ++g)
-            *reinterpret_cast<uint4*>(stg_row + ((g ^ (lane & 7)) << 4)) =
-                make_uint4(vr[4 * g], vr[4 * g + 1], vr[4 * g + 2], vr[4 * g + 3]);
-          __syncwarp();
-          int col = n0 + tc * 4;
-          const float4 b = __ldg(reinterpret_cast<const float4*>(p.shift + col));
-          float* dst = static_cast<float*>(p.out);
-          int ld = p.ldo;
-          if (p.split_n > 0 && col >= p.split_n) {
-            dst = static_cast<float*>(p.out2);
-            ld = p.ldo2;
-            col -= p.split_n;
-          }
-#pragma unroll
-          for (int i = 0; i < 8; ++i) {
-            if (ok[i]) {
-              const int r = tr + 4 * i;
-              const float4 a = *reinterpret_cast<const float4*>(stg + r * 128 + ((tc ^ (r & 7)) << 4));
-              *reinterpret_cast<float4*>(dst + out_pix[i] * ld + col) =
-                  make_float4(a.x + b.x, a.y + b.y, a.z + b.z, a.w + b.w);
-            }
-          }
-          __syncwarp();
-        }
-      }
-      if (!released) {  // this warp's channels lie entirely beyond Cout
+      conv_epilogue_tile<EPI>(p, t, px, t_addr, h, lane, stg, [&] {
         tc_fence_before();
         mbar_arrive(tempty_bar(as));
-      }
+      });
     }
   }
 

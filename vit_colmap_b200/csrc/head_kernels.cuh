@@ -48,6 +48,11 @@ int conv_smem_bytes();
 cudaError_t launch_conv(const CUtensorMap& map_a, const CUtensorMap& map_w, const ConvParams& p,
                         int num_sms, cudaStream_t stream);
 
+// Two-SM (cta_group::2) form, conv_gemm2.cu: a cluster of two CTAs per pair of patches.  Same results bit for bit.
+// map_w must be built with a {64, 128} box (each CTA stages half of a block's weight rows).
+cudaError_t launch_conv2(const CUtensorMap& map_a, const CUtensorMap& map_w, const ConvParams& p,
+                         int num_sms, cudaStream_t stream);
+
 // Bilinear resize, align_corners=False (F.interpolate, vit_feature_model.py:205-212), bf16
 // channels-last [B, Hi, Wi, C] -> [B, Ho, Wo, C]; C % 8 == 0.
 cudaError_t launch_resize_bilinear(const __nv_bfloat16* in, __nv_bfloat16* out, int B, int Hi, int Wi,

@@ -1,6 +1,8 @@
 // C ABI, ViTFeatureModel convolutional head (see include/vc_b200.h): tensor-map creation,
 // workspace carving and the launch sequence of vit_feature_model.py:234-295.  No CPU path.
 #include "vc_internal.cuh"
+#include <cstdlib>
+
 #include "head_kernels.cuh"
 
 using vc::fail;
@@ -22,12 +24,12 @@ int make_map_act(vc_handle* h, CUtensorMap* map, const void* ptr, int B, int H, 
   return VC_OK;
 }
 
-int make_map_w(vc_handle* h, CUtensorMap* map, const void* ptr, uint64_t rows, uint64_t cols) {
+int make_map_w(vc_handle* h, CUtensorMap* map, const void* ptr, uint64_t rows, uint64_t cols, uint32_t box_rows) {
   if ((reinterpret_cast<uintptr_t>(ptr) & 15) != 0 || cols % 64 != 0)
     return fail(VC_ERR_INVALID, "conv weights must be 16-byte aligned with K %% 64 == 0");
   cuuint64_t gdim[2] = {cols, rows};
   cuuint64_t gstride[1] = {cols * 2};
-  cuuint32_t box[2] = {64, 256};
+  cuuint32_t box[2] = {64, box_rows};
   cuuint32_t estr[2] = {1, 1};
   CUresult r = h->encode(map, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(ptr), gdim, gstride,
                          box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
@@ -97,9 +99,15 @@ int run_conv(vc_handle* h, const void* in, int in_ld, int B, int H, int W, int C
   CUtensorMap ma, mw;
   int rc = make_map_act(h, &ma, in, B, H, W, Cin, in_ld);
   if (rc != VC_OK) return rc;
-  rc = make_map_w(h, &mw, w, (uint64_t)p.phases * Cout, (uint64_t)p.taps * Cin);
+  // VC_CONV_2CTA=0 keeps the convolutions on the one-SM kernel (default: the two-SM kernel, conv_gemm2.cu)
+  const char* env_2cta = getenv("VC_CONV_2CTA");
+  const bool two_sm = !(env_2cta && env_2cta[0] == '0');
+  rc = make_map_w(h, &mw, w, (uint64_t)p.phases * Cout, (uint64_t)p.taps * Cin, two_sm ? 128 : 256);
   if (rc != VC_OK) return rc;
-  VC_CUDA(vc::launch_conv(ma, mw, p, h->num_sms, s));
+  if (two_sm)
+    VC_CUDA(vc::launch_conv2(ma, mw, p, h->num_sms, s));
+  else
+    VC_CUDA(vc::launch_conv(ma, mw, p, h->num_sms, s));
   vc::add_launches(1);
   return VC_OK;
 }
