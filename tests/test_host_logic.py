@@ -24,6 +24,19 @@ def test_c_abi_exports_every_declared_symbol():
     assert b"sm_100a" in _lib.load().vc_version()
 
 
+def test_c_abi_header_is_plain_c(tmp_path):
+    """include/vc_b200.h is what a C / cgo / JNI binding would include: it must compile as C99 on its own."""
+    import shutil
+    import subprocess
+    if shutil.which("gcc") is None:
+        pytest.skip("no gcc")
+    src = tmp_path / "t.c"
+    src.write_text('#include "vc_b200.h"\nint main(void) { return 0; }\n')
+    r = subprocess.run(["gcc", "-std=c99", "-Wall", "-Wextra", "-pedantic", "-Werror", "-fsyntax-only",
+                        "-I", str(ROOT / "include"), str(src)], capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr
+
+
 def test_no_device_fails_loudly():
     import torch
     if torch.cuda.is_available():
