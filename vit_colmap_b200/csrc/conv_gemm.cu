@@ -12,6 +12,8 @@
 //     8 epilogue warps; UMMA N is min(256, Cout - n0) so Cout = 192 / 128 / 64 waste no MMA work.
 //   - epilogues: +bias -> bf16; eval-BatchNorm scale/shift + exact-erf GELU -> bf16 (optionally
 //     split over two output tensors: merged keypoint/descriptor head conv); +bias -> f32.
+// The per-tile epilogue lives in conv_gemm_epilogue.cuh and is shared with the two-SM kernel (conv_gemm2.cu, the
+// default); this kernel runs under VC_CONV_2CTA=0.
 #include "head_kernels.cuh"
 
 #include "conv_gemm_epilogue.cuh"

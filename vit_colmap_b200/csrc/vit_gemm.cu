@@ -24,6 +24,9 @@
 //     (8 warps per SM cover far less L2 latency than the stand-alone kernel's 64) and owners wait on their
 //     neighbours' tiles, so delays chain through a round.  vc_vit_forward therefore keeps the stand-alone
 //     LayerNorm launches; this epilogue stays available (vc_vit_linear_ln, VC_VIT_FUSED_LN=1), bit-identical.
+//   - the per-tile epilogue lives in vit_gemm_epilogue.cuh and is shared with the two-SM kernel (vit_gemm2.cu,
+//     the default for K >= 768); this kernel serves K < 768, VC_VIT_2CTA=0 and the LayerNorm-placement options
+//     (kEpiResidualLnF32, kEpiResidualPublishF32 + layernorm_follow_kernel below)
 // Activations are bf16, accumulation and the residual stream are fp32.
 #include "vit_kernels.cuh"
 
